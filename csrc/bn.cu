@@ -1,0 +1,306 @@
+// BatchNorm (training) fused with ReLU and the residual add, NHWC bf16, fp32 statistics.
+//
+// The per-channel sum / sum-of-squares come from the convolution epilogue (igemm.cu), so the
+// forward needs exactly one pass over the activation: read y (+ identity), write z.  The backward
+// is the usual two passes: reduce (sum g, sum g*xhat), then apply.  The masked gradient
+// g = dz * (z > 0) of a residual block's last BN is also the gradient of the identity branch and is
+// written out by the apply pass when asked for.
+// Reference behaviour: nn.BatchNorm2d in torchvision Bottleneck (momentum 0.1, eps 1e-5),
+// reached from R/03 模型并行/03_model_parallel.ipynb#cell5.
+#include "common.cuh"
+#include "ptdb200.h"
+
+namespace {
+
+constexpr int BN_THREADS = 256;
+
+struct alignas(16) Pack8 {
+    uint4 u;
+};
+
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+    float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+    uint4 u;
+    u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]);
+    u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
+    return u;
+}
+
+// Per-channel sums of a [M][C] bf16 matrix (used when the producer did not fuse them, e.g. tests).
+__global__ void __launch_bounds__(BN_THREADS) bn_stats_kernel(const bf16* __restrict__ y, float* __restrict__ sum,
+                                                              float* __restrict__ sq, long long M, int C) {
+    const int cg = C >> 3;
+    const int rows_per_iter = BN_THREADS / cg;
+    const int g = threadIdx.x % cg;
+    long long row = (long long)blockIdx.x * rows_per_iter + threadIdx.x / cg;
+    const long long row_step = (long long)gridDim.x * rows_per_iter;
+    float s[8], q[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s[i] = q[i] = 0.f;
+    for (; row < M; row += row_step) {
+        float f[8];
+        unpack8(*reinterpret_cast<const uint4*>(y + row * C + g * 8), f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] += f[i] * f[i]; }
+    }
+    __shared__ float red[2][BN_THREADS][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { red[0][threadIdx.x][i] = s[i]; red[1][threadIdx.x][i] = q[i]; }
+    __syncthreads();
+    if (threadIdx.x < cg) {
+        for (int r = 1; r < rows_per_iter; ++r)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { s[i] += red[0][threadIdx.x + r * cg][i]; q[i] += red[1][threadIdx.x + r * cg][i]; }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { atomicAdd(sum + g * 8 + i, s[i]); atomicAdd(sq + g * 8 + i, q[i]); }
+    }
+}
+
+// z = act( (y - mean) * invstd * gamma + beta  [+ residual] ), plus running-stat update by block 0.
+template <bool RELU, bool RES>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_apply_kernel(const bf16* __restrict__ y, const bf16* __restrict__ res, bf16* __restrict__ z,
+                const float* __restrict__ sum, const float* __restrict__ sq, const float* __restrict__ gamma,
+                const float* __restrict__ beta, float* __restrict__ running_mean, float* __restrict__ running_var,
+                float* __restrict__ save_mean, float* __restrict__ save_invstd, long long M, int C, float eps,
+                float momentum) {
+    const int cg = C >> 3;
+    const int rows_per_iter = BN_THREADS / cg;
+    const int g = threadIdx.x % cg;
+    float scale[8], shift[8];
+    const float inv_m = 1.f / (float)M;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = g * 8 + i;
+        const float mean = sum[c] * inv_m;
+        const float var = fmaxf(sq[c] * inv_m - mean * mean, 0.f);
+        const float invstd = rsqrtf(var + eps);
+        scale[i] = gamma[c] * invstd;
+        shift[i] = beta[c] - mean * scale[i];
+        if (blockIdx.x == 0 && threadIdx.x < cg) {
+            save_mean[c] = mean;
+            save_invstd[c] = invstd;
+            if (running_mean != nullptr) {
+                const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
+                running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+                running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+            }
+        }
+    }
+    long long row = (long long)blockIdx.x * rows_per_iter + threadIdx.x / cg;
+    const long long row_step = (long long)gridDim.x * rows_per_iter;
+    for (; row < M; row += row_step) {
+        const size_t off = (size_t)row * C + g * 8;
+        float f[8];
+        unpack8(*reinterpret_cast<const uint4*>(y + off), f);
+        float r[8];
+        if (RES) unpack8(*reinterpret_cast<const uint4*>(res + off), r);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            float v = fmaf(f[i], scale[i], shift[i]);
+            if (RES) v += r[i];
+            if (RELU) v = fmaxf(v, 0.f);
+            f[i] = v;
+        }
+        *reinterpret_cast<uint4*>(z + off) = pack8(f);
+    }
+}
+
+// z = act(y * scale[c] + shift[c] [+ residual])  (inference-mode BN, or any per-channel affine)
+template <bool RELU, bool RES>
+__global__ void __launch_bounds__(BN_THREADS)
+affine_act_kernel(const bf16* __restrict__ y, const bf16* __restrict__ res, bf16* __restrict__ z,
+                  const float* __restrict__ scale_, const float* __restrict__ shift_, long long M, int C) {
+    const int cg = C >> 3;
+    const int rows_per_iter = BN_THREADS / cg;
+    const int g = threadIdx.x % cg;
+    float scale[8], shift[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { scale[i] = scale_[g * 8 + i]; shift[i] = shift_[g * 8 + i]; }
+    long long row = (long long)blockIdx.x * rows_per_iter + threadIdx.x / cg;
+    const long long row_step = (long long)gridDim.x * rows_per_iter;
+    for (; row < M; row += row_step) {
+        const size_t off = (size_t)row * C + g * 8;
+        float f[8], r[8];
+        unpack8(*reinterpret_cast<const uint4*>(y + off), f);
+        if (RES) unpack8(*reinterpret_cast<const uint4*>(res + off), r);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            float v = fmaf(f[i], scale[i], shift[i]);
+            if (RES) v += r[i];
+            if (RELU) v = fmaxf(v, 0.f);
+            f[i] = v;
+        }
+        *reinterpret_cast<uint4*>(z + off) = pack8(f);
+    }
+}
+
+// Backward pass 1: sum_g[c] += g, sum_gx[c] += g * xhat with g = dz * (z > 0 if RELU).
+template <bool RELU>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_reduce_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ z, const bf16* __restrict__ y,
+                     const float* __restrict__ mean, const float* __restrict__ invstd, float* __restrict__ sum_g,
+                     float* __restrict__ sum_gx, long long M, int C) {
+    const int cg = C >> 3;
+    const int rows_per_iter = BN_THREADS / cg;
+    const int g = threadIdx.x % cg;
+    float mu[8], is[8], s[8], q[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { mu[i] = mean[g * 8 + i]; is[i] = invstd[g * 8 + i]; s[i] = q[i] = 0.f; }
+    long long row = (long long)blockIdx.x * rows_per_iter + threadIdx.x / cg;
+    const long long row_step = (long long)gridDim.x * rows_per_iter;
+    for (; row < M; row += row_step) {
+        const size_t off = (size_t)row * C + g * 8;
+        float d[8], a[8], x[8];
+        unpack8(*reinterpret_cast<const uint4*>(dz + off), d);
+        unpack8(*reinterpret_cast<const uint4*>(y + off), x);
+        if (RELU) unpack8(*reinterpret_cast<const uint4*>(z + off), a);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float gi = (RELU && !(a[i] > 0.f)) ? 0.f : d[i];
+            s[i] += gi;
+            q[i] += gi * (x[i] - mu[i]) * is[i];
+        }
+    }
+    __shared__ float red[2][BN_THREADS][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { red[0][threadIdx.x][i] = s[i]; red[1][threadIdx.x][i] = q[i]; }
+    __syncthreads();
+    if (threadIdx.x < cg) {
+        for (int r = 1; r < rows_per_iter; ++r)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { s[i] += red[0][threadIdx.x + r * cg][i]; q[i] += red[1][threadIdx.x + r * cg][i]; }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { atomicAdd(sum_g + g * 8 + i, s[i]); atomicAdd(sum_gx + g * 8 + i, q[i]); }
+    }
+}
+
+// Backward pass 2: dy = gamma*invstd * (g - sum_g/M - xhat*sum_gx/M); optionally g_out = g.
+template <bool RELU, bool GOUT>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ z, const bf16* __restrict__ y,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                    const float* __restrict__ sum_g, const float* __restrict__ sum_gx, bf16* __restrict__ dy,
+                    bf16* __restrict__ g_out, long long M, int C) {
+    const int cg = C >> 3;
+    const int rows_per_iter = BN_THREADS / cg;
+    const int g = threadIdx.x % cg;
+    float mu[8], is[8], k[8], mg[8], mgx[8];
+    const float inv_m = 1.f / (float)M;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = g * 8 + i;
+        mu[i] = mean[c]; is[i] = invstd[c]; k[i] = gamma[c] * is[i];
+        mg[i] = sum_g[c] * inv_m; mgx[i] = sum_gx[c] * inv_m;
+    }
+    long long row = (long long)blockIdx.x * rows_per_iter + threadIdx.x / cg;
+    const long long row_step = (long long)gridDim.x * rows_per_iter;
+    for (; row < M; row += row_step) {
+        const size_t off = (size_t)row * C + g * 8;
+        float d[8], a[8], x[8], o[8];
+        unpack8(*reinterpret_cast<const uint4*>(dz + off), d);
+        unpack8(*reinterpret_cast<const uint4*>(y + off), x);
+        if (RELU) unpack8(*reinterpret_cast<const uint4*>(z + off), a);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float gi = (RELU && !(a[i] > 0.f)) ? 0.f : d[i];
+            d[i] = gi;
+            const float xhat = (x[i] - mu[i]) * is[i];
+            o[i] = k[i] * (gi - mg[i] - xhat * mgx[i]);
+        }
+        *reinterpret_cast<uint4*>(dy + off) = pack8(o);
+        if (GOUT) *reinterpret_cast<uint4*>(g_out + off) = pack8(d);
+    }
+}
+
+int bn_grid(long long M, int C) {
+    const int rows_per_iter = BN_THREADS / (C >> 3);
+    long long blocks = (M + rows_per_iter - 1) / rows_per_iter;
+    const long long cap = (long long)ptd_num_sms() * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+bool bn_shape_ok(int C) { return C >= 64 && C <= 2048 && (C & (C - 1)) == 0; }
+
+}  // namespace
+
+extern "C" int ptd_bn_stats(const void* y, float* sum, float* sq, long long M, int C, void* stream) {
+    PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
+    bn_stats_kernel<<<bn_grid(M, C), BN_THREADS, 0, (cudaStream_t)stream>>>((const bf16*)y, sum, sq, M, C);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+extern "C" int ptd_bn_apply(const void* y, const void* residual, void* z, const float* sum, const float* sq,
+                            const float* gamma, const float* beta, float* running_mean, float* running_var,
+                            float* save_mean, float* save_invstd, long long M, int C, float eps, float momentum,
+                            int relu, void* stream) {
+    PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
+    const int grid = bn_grid(M, C);
+    cudaStream_t st = (cudaStream_t)stream;
+#define PTD_BN_APPLY(RELU, RES)                                                                                     \
+    bn_apply_kernel<RELU, RES><<<grid, BN_THREADS, 0, st>>>((const bf16*)y, (const bf16*)residual, (bf16*)z, sum, sq, \
+                                                           gamma, beta, running_mean, running_var, save_mean,      \
+                                                           save_invstd, M, C, eps, momentum)
+    if (relu && residual) PTD_BN_APPLY(true, true);
+    else if (relu) PTD_BN_APPLY(true, false);
+    else if (residual) PTD_BN_APPLY(false, true);
+    else PTD_BN_APPLY(false, false);
+#undef PTD_BN_APPLY
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+extern "C" int ptd_affine_act(const void* y, const void* residual, void* z, const float* scale, const float* shift,
+                              long long M, int C, int relu, void* stream) {
+    PTD_REQUIRE(bn_shape_ok(C), "affine_act: C (%d) must be a power of two in [64, 2048]", C);
+    const int grid = bn_grid(M, C);
+    cudaStream_t st = (cudaStream_t)stream;
+#define PTD_AFF(RELU, RES) \
+    affine_act_kernel<RELU, RES><<<grid, BN_THREADS, 0, st>>>((const bf16*)y, (const bf16*)residual, (bf16*)z, scale, shift, M, C)
+    if (relu && residual) PTD_AFF(true, true);
+    else if (relu) PTD_AFF(true, false);
+    else if (residual) PTD_AFF(false, true);
+    else PTD_AFF(false, false);
+#undef PTD_AFF
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+extern "C" int ptd_bn_bwd_reduce(const void* dz, const void* z, const void* y, const float* mean, const float* invstd,
+                                 float* sum_g, float* sum_gx, long long M, int C, int relu, void* stream) {
+    PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
+    const int grid = bn_grid(M, C);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (relu)
+        bn_bwd_reduce_kernel<true><<<grid, BN_THREADS, 0, st>>>((const bf16*)dz, (const bf16*)z, (const bf16*)y, mean,
+                                                                invstd, sum_g, sum_gx, M, C);
+    else
+        bn_bwd_reduce_kernel<false><<<grid, BN_THREADS, 0, st>>>((const bf16*)dz, (const bf16*)z, (const bf16*)y, mean,
+                                                                 invstd, sum_g, sum_gx, M, C);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+extern "C" int ptd_bn_bwd_apply(const void* dz, const void* z, const void* y, const float* mean, const float* invstd,
+                                const float* gamma, const float* sum_g, const float* sum_gx, void* dy, void* g_out,
+                                long long M, int C, int relu, void* stream) {
+    PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
+    const int grid = bn_grid(M, C);
+    cudaStream_t st = (cudaStream_t)stream;
+#define PTD_BWD(RELU, GOUT)                                                                                         \
+    bn_bwd_apply_kernel<RELU, GOUT><<<grid, BN_THREADS, 0, st>>>((const bf16*)dz, (const bf16*)z, (const bf16*)y, mean, \
+                                                                invstd, gamma, sum_g, sum_gx, (bf16*)dy, (bf16*)g_out, M, C)
+    if (relu && g_out) PTD_BWD(true, true);
+    else if (relu) PTD_BWD(true, false);
+    else if (g_out) PTD_BWD(false, true);
+    else PTD_BWD(false, false);
+#undef PTD_BWD
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}

@@ -1,0 +1,816 @@
+// Implicit-GEMM engine on tcgen05 / TMEM / TMA for sm_100a.
+//
+// Two warp-specialised kernels cover every GEMM-shaped op of the framework:
+//
+//   igemm_f  ("forward-like", persistent):  D[M,N] = A[M,K] * B[N,K]^T
+//       A rows are output pixels.  A is either a plain K-major matrix fetched by TMA (1x1 stride-1
+//       convolutions, FC) or gathered on the fly from an NHWC tensor by four producer warps with
+//       cp.async into the same 128-byte-swizzled image TMA would have written (3x3/7x7/strided
+//       convolutions, data-gradient).  B (weights) always arrives by TMA, K-major (fprop) or
+//       MN-major (dgrad reads the forward weight tensor in place - no transposed copy exists).
+//       Epilogue: TMEM -> registers -> bf16 NHWC store, fused per-channel sum / sum-of-squares
+//       for BatchNorm, optional residual addend, or fp32 + bias for the classifier.
+//
+//   igemm_w  ("weight-gradient", split-K):  dW[Cout,Kw] += dY[P,Cout]^T * Xcol[P,Kw]
+//       Both operands are MN-major (the reduction runs over pixels).  dY arrives by TMA, Xcol by
+//       TMA (1x1) or gather.  fp32 partial tiles are reduced with vector red.global.add.
+//
+// Roles per CTA: warps 0-7 epilogue (TMEM lane quarter = warp % 4), warp 8 TMA producer,
+// warp 9 TMEM allocator + single-thread MMA issuer, warps 10-13 gather producers.
+// The reference reaches these ops through cuDNN/cuBLAS (call sites
+// R/03 模型并行/03_model_parallel.ipynb#cell4-7,12).
+#include "common.cuh"
+#include "ptdb200.h"
+#include "tensormap.h"
+
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;              // 64 bf16 = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int A_TILE_BYTES = BLOCK_M * BLOCK_K * 2;   // 16 KiB
+constexpr int SUB_TILE_BYTES = 64 * 64 * 2;           // 8 KiB : [64 rows][64 elems] swizzled image
+constexpr int NUM_EPI_WARPS = 8;
+constexpr int TMA_WARP = 8;
+constexpr int MMA_WARP = 9;
+constexpr int GATHER_WARP0 = 10;
+constexpr int NUM_GATHER_THREADS = 128;
+
+enum { GM_FPROP = 0, GM_DGRAD = 1, GM_STEM = 2 };
+
+struct ConvGeom {
+    const bf16* src;     // NHWC tensor the rows are gathered from
+    int H, W, C;         // its spatial size and channel count
+    int OH, OW;          // row space: row = (n*OH + oh)*OW + ow
+    int R, S;            // filter taps
+    int stride, pad;
+    int mode;            // GM_*
+    int cblocks;         // C / 64
+};
+
+struct alignas(64) FParams {
+    CUtensorMap tmA;
+    CUtensorMap tmB;
+    ConvGeom g;
+    int M, N, num_kb;
+    int n_blocks, m_blocks;
+    int b_tap_cols;      // MN-major B: column offset per filter tap (= N of the full weight slice)
+    int b_cblocks;       // MN-major B: k-blocks per tap
+    bf16* out;
+    const bf16* addend;
+    float* stat_sum;
+    float* stat_sq;
+    float* out_f32;
+    const float* bias;
+    int ldo;
+};
+
+struct alignas(64) WParams {
+    CUtensorMap tmA;     // dY  [P][Cout], box 64x64
+    CUtensorMap tmB;     // X   [P][Cin],  box 64x64 (1x1 stride-1 only)
+    ConvGeom g;
+    int P, Cout, Kw;
+    int m_blocks, n_blocks, splits, kb_per_split, num_kb;
+    float* dw;
+};
+
+// ------------------------------------------------------------------------------------------
+// Gather producers
+// ------------------------------------------------------------------------------------------
+struct RowCtx {
+    int n, oh, ow;
+    bool valid;
+};
+
+__device__ __forceinline__ RowCtx decode_row(const ConvGeom& g, long long row, long long nrows) {
+    RowCtx rc;
+    rc.valid = row < nrows;
+    long long r = rc.valid ? row : 0;
+    int hw = g.OH * g.OW;
+    rc.n = (int)(r / hw);
+    int rem = (int)(r - (long long)rc.n * hw);
+    rc.oh = rem / g.OW;
+    rc.ow = rem - rc.oh * g.OW;
+    return rc;
+}
+
+// One 128-byte row segment (chunks [c_begin, c_end) of 16 B) of k-block (tap, cb) for row context rc.
+__device__ __forceinline__ void gather_row_16B(const ConvGeom& g, const RowCtx& rc, int tap, int cb, uint32_t dst_row,
+                                               int row_in_tile, int c_begin, int c_end) {
+    int r = tap / g.S;
+    int s = tap - r * g.S;
+    int hi, wi;
+    bool ok = rc.valid;
+    if (g.mode == GM_FPROP) {
+        hi = rc.oh * g.stride - g.pad + r;
+        wi = rc.ow * g.stride - g.pad + s;
+        ok = ok && hi >= 0 && hi < g.H && wi >= 0 && wi < g.W;
+    } else {
+        int th = rc.oh + g.pad - r;
+        int tw = rc.ow + g.pad - s;
+        ok = ok && th >= 0 && tw >= 0;
+        hi = th / g.stride;
+        wi = tw / g.stride;
+        ok = ok && hi * g.stride == th && wi * g.stride == tw && hi < g.H && wi < g.W;
+    }
+    const bf16* src = g.src;
+    if (ok) src += ((size_t)((size_t)rc.n * g.H + hi) * g.W + wi) * g.C + (size_t)cb * 64;
+    const uint32_t nbytes = ok ? 16u : 0u;
+    const int sw = row_in_tile & 7;
+#pragma unroll
+    for (int c = c_begin; c < c_end; ++c) cp_async_16(dst_row + ((uint32_t)(c ^ sw) << 4), src + c * 8, nbytes);
+}
+
+// Stem (7x7 stride 2 pad 3 on an NHWC4 image): k-block kb holds filter rows 2kb, 2kb+1; each filter
+// row is 8 taps x 4 channels = 64 bytes (tap 7 and filter row 7 are zero padding).
+__device__ __forceinline__ void gather_row_stem(const ConvGeom& g, const RowCtx& rc, int kb, uint32_t dst_row,
+                                                int row_in_tile, int c_begin, int c_end) {
+    const int sw = row_in_tile & 7;
+#pragma unroll
+    for (int c = c_begin; c < c_end; ++c) {      // 16-byte chunk c: filter row rl = c / 4, taps 2*(c%4), +1
+        int rl = c >> 2;
+        int r = 2 * kb + rl;
+        int hi = rc.oh * 2 - 3 + r;
+        bool row_ok = rc.valid && r < 7 && hi >= 0 && hi < g.H;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            int s = 2 * (c & 3) + h;
+            int wi = rc.ow * 2 - 3 + s;
+            bool ok = row_ok && s < 7 && wi >= 0 && wi < g.W;
+            const bf16* src = g.src;
+            if (ok) src += ((size_t)((size_t)rc.n * g.H + hi) * g.W + wi) * 4;
+            cp_async_8(dst_row + ((uint32_t)(c ^ sw) << 4) + h * 8, src, ok ? 8u : 0u);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Shared-memory carve-up
+// ------------------------------------------------------------------------------------------
+template <int STAGES>
+struct Barriers {
+    uint64_t full[STAGES];
+    uint64_t empty[STAGES];
+    uint64_t tmem_full[2];
+    uint64_t tmem_empty[2];
+    uint32_t tmem_base;
+};
+
+// ------------------------------------------------------------------------------------------
+// Column sums across the 32 rows held by a warp (one row per lane, 32 columns per lane):
+// recursive halving, 31 shuffles; on return v[0] of lane l is the sum of column l.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float transpose_reduce32(float (&v)[32], uint32_t lane) {
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+        const bool up = (lane & o) != 0;
+#pragma unroll
+        for (int i = 0; i < o; ++i) {
+            float send = up ? v[i] : v[i + o];
+            float keep = up ? v[i + o] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+    }
+    return v[0];
+}
+
+// ------------------------------------------------------------------------------------------
+// igemm_f
+// ------------------------------------------------------------------------------------------
+template <int BLOCK_N, bool A_TMA, bool B_MN, int EPI /*0 = bf16 (+stats/+addend), 1 = fp32 + bias*/>
+struct FCfg {
+    static constexpr int B_TILE_BYTES = BLOCK_N * BLOCK_K * 2;
+    static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
+    static constexpr int STAGES = (BLOCK_N == 256) ? 4 : (BLOCK_N == 128 ? 6 : 8);
+    static constexpr int THREADS = A_TMA ? (MMA_WARP + 1) * 32 : (GATHER_WARP0 + 4) * 32;
+    static constexpr int TMEM_COLS = 2 * BLOCK_N;
+    static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + sizeof(Barriers<STAGES>);
+    static constexpr int CHUNKS_PER_WARP = BLOCK_N / 64;   // 32-column chunks per epilogue warp
+};
+
+template <int BLOCK_N, bool A_TMA, bool B_MN, int EPI>
+__global__ void __launch_bounds__(FCfg<BLOCK_N, A_TMA, B_MN, EPI>::THREADS, 1)
+igemm_f_kernel(const __grid_constant__ FParams p) {
+    using Cfg = FCfg<BLOCK_N, A_TMA, B_MN, EPI>;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    Barriers<STAGES>* bars = reinterpret_cast<Barriers<STAGES>*>(smem + (size_t)STAGES * Cfg::STAGE_BYTES);
+    const uint32_t smem_base = smem_u32(smem);
+
+    const int warp = threadIdx.x >> 5;
+    const uint32_t lane = lane_id();
+    const int num_tiles = p.m_blocks * p.n_blocks;
+    const int n_blk = blockIdx.x % p.n_blocks;      // grid is a multiple of n_blocks: fixed per CTA
+    const int n0 = n_blk * BLOCK_N;
+
+    if (warp == TMA_WARP && lane == 0) {
+        if (A_TMA) tma_prefetch_desc(&p.tmA);
+        tma_prefetch_desc(&p.tmB);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&bars->full[s], A_TMA ? 1 : 1 + NUM_GATHER_THREADS);
+            mbar_init(&bars->empty[s], 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(&bars->tmem_full[a], 1);
+            mbar_init(&bars->tmem_empty[a], NUM_EPI_WARPS * 32);
+        }
+        mbar_fence_init();
+    }
+    if (warp == MMA_WARP) tmem_alloc<Cfg::TMEM_COLS>(&bars->tmem_base);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == TMA_WARP) {
+        // ===================== TMA producer (one lane) =====================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                const int m0 = (t / p.n_blocks) * BLOCK_M;
+                for (int kb = 0; kb < p.num_kb; ++kb) {
+                    mbar_wait(&bars->empty[stage], phase ^ 1);
+                    const uint32_t a_dst = smem_base + stage * Cfg::STAGE_BYTES;
+                    const uint32_t b_dst = a_dst + A_TILE_BYTES;
+                    mbar_arrive_expect_tx(&bars->full[stage], Cfg::B_TILE_BYTES + (A_TMA ? A_TILE_BYTES : 0));
+                    if (A_TMA) tma_load_2d(a_dst, &p.tmA, &bars->full[stage], kb * BLOCK_K, m0);
+                    if (!B_MN) {
+                        tma_load_2d(b_dst, &p.tmB, &bars->full[stage], kb * BLOCK_K, n0);
+                    } else {
+                        const int tap = kb / p.b_cblocks;
+                        const int cb = kb - tap * p.b_cblocks;
+#pragma unroll
+                        for (int j = 0; j < BLOCK_N / 64; ++j)
+                            tma_load_2d(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage],
+                                        tap * p.b_tap_cols + n0 + j * 64, cb * 64);
+                    }
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        // ===================== MMA issuer (one lane) =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BLOCK_N, 0, B_MN ? 1 : 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+                const int acc = it & 1;
+                const uint32_t acc_phase = (it >> 1) & 1;
+                mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+                for (int kb = 0; kb < p.num_kb; ++kb) {
+                    mbar_wait(&bars->full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_base + stage * Cfg::STAGE_BYTES;
+                    const uint32_t b_addr = a_addr + A_TILE_BYTES;
+#pragma unroll
+                    for (int kk = 0; kk < BLOCK_K / UMMA_K; ++kk) {
+                        const uint64_t adesc = umma_smem_desc(a_addr + kk * 32, 16, 1024);
+                        const uint64_t bdesc = B_MN ? umma_smem_desc(b_addr + kk * 2048, SUB_TILE_BYTES, 1024)
+                                                    : umma_smem_desc(b_addr + kk * 32, 16, 1024);
+                        umma_f16(d_tmem, adesc, bdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&bars->empty[stage]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&bars->tmem_full[acc]);
+            }
+        }
+    } else if (warp < NUM_EPI_WARPS) {
+        // ===================== Epilogue =====================
+        const int q = warp & 3;
+        const int half = warp >> 2;
+        float acc_sum[Cfg::CHUNKS_PER_WARP], acc_sq[Cfg::CHUNKS_PER_WARP];
+#pragma unroll
+        for (int c = 0; c < Cfg::CHUNKS_PER_WARP; ++c) acc_sum[c] = acc_sq[c] = 0.f;
+        const bool do_stats = (EPI == 0) && p.stat_sum != nullptr;
+        int it = 0;
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+            const int acc = it & 1;
+            const uint32_t acc_phase = (it >> 1) & 1;
+            const long long m = (long long)(t / p.n_blocks) * BLOCK_M + q * 32 + lane;
+            const bool row_ok = m < p.M;
+            mbar_wait(&bars->tmem_full[acc], acc_phase);
+            tc_fence_after();
+#pragma unroll
+            for (int c = 0; c < Cfg::CHUNKS_PER_WARP; ++c) {
+                const int col = half * (BLOCK_N / 2) + c * 32;
+                uint32_t raw[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BLOCK_N + col, raw);
+                tmem_ld_wait();
+                float v[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
+                if (EPI == 0) {
+                    bf16* dst = p.out + (size_t)m * p.ldo + n0 + col;
+                    if (p.addend != nullptr && row_ok) {
+                        const uint4* ad = reinterpret_cast<const uint4*>(p.addend + (size_t)m * p.ldo + n0 + col);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            uint4 a4 = ad[j];
+                            const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                float2 f = unpack_bf16x2(aw[e]);
+                                v[j * 8 + e * 2] += f.x;
+                                v[j * 8 + e * 2 + 1] += f.y;
+                            }
+                        }
+                    }
+                    if (row_ok) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            uint4 o;
+                            o.x = pack_bf16x2(v[j * 8 + 0], v[j * 8 + 1]);
+                            o.y = pack_bf16x2(v[j * 8 + 2], v[j * 8 + 3]);
+                            o.z = pack_bf16x2(v[j * 8 + 4], v[j * 8 + 5]);
+                            o.w = pack_bf16x2(v[j * 8 + 6], v[j * 8 + 7]);
+                            reinterpret_cast<uint4*>(dst)[j] = o;
+                        }
+                    }
+                    if (do_stats) {
+                        // Rows past M were zero-filled by the producers, so they add nothing.
+                        float sq[32];
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) sq[i] = v[i] * v[i];
+                        acc_sum[c] += transpose_reduce32(v, lane);
+                        acc_sq[c] += transpose_reduce32(sq, lane);
+                    }
+                } else {
+                    if (row_ok) {
+                        float* dst = p.out_f32 + (size_t)m * p.ldo + n0 + col;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            const int n = n0 + col + i;
+                            if (n < p.N) dst[i] = v[i] + (p.bias ? p.bias[n] : 0.f);
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            mbar_arrive(&bars->tmem_empty[acc]);
+        }
+        if (do_stats) {
+#pragma unroll
+            for (int c = 0; c < Cfg::CHUNKS_PER_WARP; ++c) {
+                const int n = n0 + half * (BLOCK_N / 2) + c * 32 + lane;
+                atomicAdd(p.stat_sum + n, acc_sum[c]);
+                atomicAdd(p.stat_sq + n, acc_sq[c]);
+            }
+        }
+    } else if (!A_TMA) {
+        // ===================== Gather producers (128 threads, one tile row each) =====================
+        const int row = threadIdx.x - GATHER_WARP0 * 32;
+        int stage = 0;
+        uint32_t phase = 0;
+        constexpr int LAG = STAGES >= 6 ? 3 : 2;   // k-blocks of cp.async in flight; must stay < STAGES
+        int arrive_stage = 0;                       // oldest stage whose copies are still in flight
+        int npend = 0;
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            const long long m = (long long)(t / p.n_blocks) * BLOCK_M + row;
+            const RowCtx rc = decode_row(p.g, m, p.M);
+            for (int kb = 0; kb < p.num_kb; ++kb) {
+                mbar_wait(&bars->empty[stage], phase ^ 1);
+                const uint32_t dst_row = smem_base + stage * Cfg::STAGE_BYTES + row * 128;
+                if (p.g.mode == GM_STEM) {
+                    gather_row_stem(p.g, rc, kb, dst_row, row, 0, 8);
+                } else {
+                    const int tap = kb / p.g.cblocks;
+                    gather_row_16B(p.g, rc, tap, kb - tap * p.g.cblocks, dst_row, row, 0, 8);
+                }
+                cp_async_commit();
+                if (npend == LAG) {
+                    cp_async_wait<LAG>();             // the oldest group has landed
+                    fence_proxy_async_smem();         // generic-proxy writes -> visible to the tensor core
+                    mbar_arrive(&bars->full[arrive_stage]);
+                    if (++arrive_stage == STAGES) arrive_stage = 0;
+                } else {
+                    ++npend;
+                }
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+        cp_async_wait<0>();
+        fence_proxy_async_smem();
+        for (int i = 0; i < npend; ++i) {
+            mbar_arrive(&bars->full[arrive_stage]);
+            if (++arrive_stage == STAGES) arrive_stage = 0;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------
+// igemm_w
+// ------------------------------------------------------------------------------------------
+template <int NSUB, bool B_TMA>
+struct WCfg {
+    static constexpr int BLOCK_N = 64 * NSUB;
+    static constexpr int A_BYTES = 2 * SUB_TILE_BYTES;                 // [64 pixels][128 cout]
+    static constexpr int B_BYTES = NSUB * SUB_TILE_BYTES;              // [64 pixels][64*NSUB]
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = NSUB >= 3 ? 4 : 6;
+    static constexpr int THREADS = B_TMA ? (MMA_WARP + 1) * 32 : (GATHER_WARP0 + 4) * 32;
+    static constexpr int TMEM_COLS = NSUB == 1 ? 64 : (NSUB == 2 ? 128 : 256);
+    static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + sizeof(Barriers<STAGES>);
+};
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
+}
+
+template <int NSUB, bool B_TMA>
+__global__ void __launch_bounds__(WCfg<NSUB, B_TMA>::THREADS, 1) igemm_w_kernel(const __grid_constant__ WParams p) {
+    using Cfg = WCfg<NSUB, B_TMA>;
+    constexpr int STAGES = Cfg::STAGES;
+    constexpr int BLOCK_N = Cfg::BLOCK_N;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    Barriers<STAGES>* bars = reinterpret_cast<Barriers<STAGES>*>(smem + (size_t)STAGES * Cfg::STAGE_BYTES);
+    const uint32_t smem_base = smem_u32(smem);
+    const int warp = threadIdx.x >> 5;
+    const uint32_t lane = lane_id();
+
+    // CTA -> (split, m block, n block)
+    int bid = blockIdx.x;
+    const int n_blk = bid % p.n_blocks; bid /= p.n_blocks;
+    const int m_blk = bid % p.m_blocks; bid /= p.m_blocks;
+    const int split = bid;
+    const int kb_begin = split * p.kb_per_split;
+    const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
+    const int nkb = kb_end - kb_begin;     // host guarantees >= 1
+
+    if (warp == TMA_WARP && lane == 0) {
+        tma_prefetch_desc(&p.tmA);
+        if (B_TMA) tma_prefetch_desc(&p.tmB);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&bars->full[s], B_TMA ? 1 : 1 + NUM_GATHER_THREADS);
+            mbar_init(&bars->empty[s], 1);
+        }
+        mbar_init(&bars->tmem_full[0], 1);
+        mbar_fence_init();
+    }
+    if (warp == MMA_WARP) tmem_alloc<Cfg::TMEM_COLS>(&bars->tmem_base);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == TMA_WARP) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int kb = kb_begin; kb < kb_end; ++kb) {
+                mbar_wait(&bars->empty[stage], phase ^ 1);
+                const uint32_t a_dst = smem_base + stage * Cfg::STAGE_BYTES;
+                const uint32_t b_dst = a_dst + Cfg::A_BYTES;
+                mbar_arrive_expect_tx(&bars->full[stage], Cfg::A_BYTES + (B_TMA ? Cfg::B_BYTES : 0));
+                tma_load_2d(a_dst, &p.tmA, &bars->full[stage], m_blk * 128, kb * 64);
+                tma_load_2d(a_dst + SUB_TILE_BYTES, &p.tmA, &bars->full[stage], m_blk * 128 + 64, kb * 64);
+                if (B_TMA) {
+#pragma unroll
+                    for (int j = 0; j < NSUB; ++j)
+                        tma_load_2d(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage],
+                                    (n_blk * NSUB + j) * 64, kb * 64);
+                }
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 1, 1);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int i = 0; i < nkb; ++i) {
+                mbar_wait(&bars->full[stage], phase);
+                tc_fence_after();
+                const uint32_t a_addr = smem_base + stage * Cfg::STAGE_BYTES;
+                const uint32_t b_addr = a_addr + Cfg::A_BYTES;
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {
+                    const uint64_t adesc = umma_smem_desc(a_addr + kk * 2048, SUB_TILE_BYTES, 1024);
+                    const uint64_t bdesc = umma_smem_desc(b_addr + kk * 2048, SUB_TILE_BYTES, 1024);
+                    umma_f16(tmem_base, adesc, bdesc, idesc, (i | kk) != 0 ? 1u : 0u);
+                }
+                umma_commit(&bars->empty[stage]);
+                if (++stage == STAGES) { stage = 0; phase ^= 1; }
+            }
+            umma_commit(&bars->tmem_full[0]);
+        }
+    } else if (warp < NUM_EPI_WARPS) {
+        const int q = warp & 3;
+        const int half = warp >> 2;
+        const int cout = m_blk * 128 + q * 32 + lane;
+        mbar_wait(&bars->tmem_full[0], 0);
+        tc_fence_after();
+        // 32-column chunks split between the two warps sharing a lane quarter
+        constexpr int NCHUNK = BLOCK_N / 32;
+        for (int c = half; c < NCHUNK; c += 2) {
+            uint32_t raw[32];
+            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, raw);
+            tmem_ld_wait();
+            if (cout < p.Cout) {
+                float* dst = p.dw + (size_t)cout * p.Kw + (size_t)n_blk * BLOCK_N + c * 32;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    red_add_v4(dst + j * 4, __uint_as_float(raw[j * 4]), __uint_as_float(raw[j * 4 + 1]),
+                               __uint_as_float(raw[j * 4 + 2]), __uint_as_float(raw[j * 4 + 3]));
+            }
+        }
+        tc_fence_before();
+    } else if (!B_TMA) {
+        // gather: 128 threads; thread -> (pixel row = tid % 64, chunk half = tid / 64) for every sub-tile
+        const int tid = threadIdx.x - GATHER_WARP0 * 32;
+        const int row = tid & 63;
+        const int ch = tid >> 6;
+        int stage = 0;
+        uint32_t phase = 0;
+        constexpr int LAG = STAGES >= 6 ? 3 : 2;
+        int arrive_stage = 0;
+        int npend = 0;
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
+            const RowCtx rc = decode_row(p.g, (long long)kb * 64 + row, p.P);
+            mbar_wait(&bars->empty[stage], phase ^ 1);
+            const uint32_t b_dst = smem_base + stage * Cfg::STAGE_BYTES + Cfg::A_BYTES;
+#pragma unroll
+            for (int j = 0; j < NSUB; ++j) {
+                const int sj = n_blk * NSUB + j;
+                const uint32_t dst_row = b_dst + j * SUB_TILE_BYTES + row * 128;
+                if (p.g.mode == GM_STEM) {
+                    gather_row_stem(p.g, rc, sj, dst_row, row, ch * 4, ch * 4 + 4);
+                } else {
+                    const int tap = sj / p.g.cblocks;
+                    gather_row_16B(p.g, rc, tap, sj - tap * p.g.cblocks, dst_row, row, ch * 4, ch * 4 + 4);
+                }
+            }
+            cp_async_commit();
+            if (npend == LAG) {
+                cp_async_wait<LAG>();
+                fence_proxy_async_smem();
+                mbar_arrive(&bars->full[arrive_stage]);
+                if (++arrive_stage == STAGES) arrive_stage = 0;
+            } else {
+                ++npend;
+            }
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        cp_async_wait<0>();
+        fence_proxy_async_smem();
+        for (int i = 0; i < npend; ++i) {
+            mbar_arrive(&bars->full[arrive_stage]);
+            if (++arrive_stage == STAGES) arrive_stage = 0;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == MMA_WARP) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------
+// Host launchers
+// ------------------------------------------------------------------------------------------
+template <int BLOCK_N, bool A_TMA, bool B_MN, int EPI>
+int launch_f(FParams& p, cudaStream_t stream) {
+    using Cfg = FCfg<BLOCK_N, A_TMA, B_MN, EPI>;
+    auto kern = igemm_f_kernel<BLOCK_N, A_TMA, B_MN, EPI>;
+    static bool configured[64] = {false};
+    int dev = 0;
+    PTD_CUDA_CHECK(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        PTD_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
+        configured[dev & 63] = true;
+    }
+    p.m_blocks = ceil_div_i(p.M, BLOCK_M);
+    p.n_blocks = ceil_div_i(p.N, BLOCK_N);
+    const int tiles = p.m_blocks * p.n_blocks;
+    int grid = ptd_num_sms();
+    grid = (grid / p.n_blocks) * p.n_blocks;      // fixed n block per CTA (register-resident BN partial sums)
+    if (grid < p.n_blocks) grid = p.n_blocks;
+    if (grid > tiles) grid = tiles;               // tiles is a multiple of n_blocks
+    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>(p);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+template <bool A_TMA, bool B_MN, int EPI>
+int dispatch_f(FParams& p, int block_n, cudaStream_t stream) {
+    switch (block_n) {
+        case 64: return launch_f<64, A_TMA, B_MN, EPI>(p, stream);
+        case 128: return launch_f<128, A_TMA, B_MN, EPI>(p, stream);
+        case 256: return launch_f<256, A_TMA, B_MN, EPI>(p, stream);
+    }
+    ptd_set_error("igemm_f: unsupported BLOCK_N %d", block_n);
+    return PTD_ERR_ARG;
+}
+
+int pick_block_n(int n) {
+    if (n % 256 == 0) return 256;
+    if (n % 128 == 0) return 128;
+    return 64;
+}
+
+template <int NSUB, bool B_TMA>
+int launch_w(WParams& p, cudaStream_t stream) {
+    using Cfg = WCfg<NSUB, B_TMA>;
+    auto kern = igemm_w_kernel<NSUB, B_TMA>;
+    static bool configured[64] = {false};
+    int dev = 0;
+    PTD_CUDA_CHECK(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        PTD_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
+        configured[dev & 63] = true;
+    }
+    p.m_blocks = ceil_div_i(p.Cout, 128);
+    p.n_blocks = p.Kw / (64 * NSUB);
+    p.num_kb = ceil_div_i(p.P, 64);
+    const int tiles = p.m_blocks * p.n_blocks;
+    int splits = ceil_div_i(2 * ptd_num_sms(), tiles);          // ~2 CTAs per SM keeps the tail short
+    if (splits > p.num_kb) splits = p.num_kb;
+    if (splits < 1) splits = 1;
+    p.kb_per_split = ceil_div_i(p.num_kb, splits);
+    p.splits = ceil_div_i(p.num_kb, p.kb_per_split);            // no empty split
+    kern<<<tiles * p.splits, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>(p);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+template <bool B_TMA>
+int dispatch_w(WParams& p, int nsub, cudaStream_t stream) {
+    switch (nsub) {
+        case 1: return launch_w<1, B_TMA>(p, stream);
+        case 2: return launch_w<2, B_TMA>(p, stream);
+        case 3: return launch_w<3, B_TMA>(p, stream);
+        case 4: return launch_w<4, B_TMA>(p, stream);
+    }
+    ptd_set_error("igemm_w: unsupported sub-tile count %d", nsub);
+    return PTD_ERR_ARG;
+}
+
+int pick_nsub(int ksub) {   // ksub = Kw / 64
+    if (ksub % 4 == 0) return 4;
+    if (ksub % 3 == 0) return 3;
+    if (ksub % 2 == 0) return 2;
+    return 1;
+}
+
+void fill_geom(ConvGeom& g, const bf16* src, int H, int W, int C, int OH, int OW, int R, int S, int stride, int pad,
+               int mode) {
+    g.src = src; g.H = H; g.W = W; g.C = C; g.OH = OH; g.OW = OW; g.R = R; g.S = S;
+    g.stride = stride; g.pad = pad; g.mode = mode; g.cblocks = C / 64;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------
+extern "C" int ptd_conv_fprop(const void* x, const void* w, void* y, float* stat_sum, float* stat_sq, int N, int H,
+                              int W, int Cin, int Cout, int R, int S, int stride, int pad, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
+    PTD_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "conv_fprop: Cin (%d) and Cout (%d) must be multiples of 64", Cin, Cout);
+    FParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = N * OH * OW; p.N = Cout; p.num_kb = R * S * Cin / 64;
+    p.out = (bf16*)y; p.ldo = Cout; p.stat_sum = stat_sum; p.stat_sq = stat_sq;
+    const int bn = pick_block_n(Cout);
+    int rc = ptd_make_tmap_2d_bf16(&p.tmB, w, (uint64_t)R * S * Cin, Cout, (uint64_t)R * S * Cin * 2, 64, bn);
+    if (rc) return rc;
+    const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
+    if (plain) {
+        rc = ptd_make_tmap_2d_bf16(&p.tmA, x, Cin, p.M, (uint64_t)Cin * 2, 64, BLOCK_M);
+        if (rc) return rc;
+        return dispatch_f<true, false, 0>(p, bn, stream);
+    }
+    fill_geom(p.g, (const bf16*)x, H, W, Cin, OH, OW, R, S, stride, pad, GM_FPROP);
+    return dispatch_f<false, false, 0>(p, bn, stream);
+}
+
+extern "C" int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const void* addend, int N, int H, int W,
+                              int Cin, int Cout, int R, int S, int stride, int pad, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
+    PTD_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "conv_dgrad: Cin (%d) and Cout (%d) must be multiples of 64", Cin, Cout);
+    FParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = N * H * W; p.N = Cin; p.num_kb = R * S * Cout / 64;
+    p.out = (bf16*)dx; p.ldo = Cin; p.addend = (const bf16*)addend;
+    p.b_tap_cols = Cin; p.b_cblocks = Cout / 64;
+    const int bn = pick_block_n(Cin);
+    // forward weight tensor viewed as [Cout rows][R*S*Cin cols]; a 64x64 box at (tap*Cin + n, cout) is the
+    // MN-major B sub-tile of that tap.
+    int rc = ptd_make_tmap_2d_bf16(&p.tmB, w, (uint64_t)R * S * Cin, Cout, (uint64_t)R * S * Cin * 2, 64, 64);
+    if (rc) return rc;
+    const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
+    if (plain) {
+        rc = ptd_make_tmap_2d_bf16(&p.tmA, dy, Cout, p.M, (uint64_t)Cout * 2, 64, BLOCK_M);
+        if (rc) return rc;
+        return dispatch_f<true, true, 0>(p, bn, stream);
+    }
+    fill_geom(p.g, (const bf16*)dy, OH, OW, Cout, H, W, R, S, stride, pad, GM_DGRAD);
+    return dispatch_f<false, true, 0>(p, bn, stream);
+}
+
+extern "C" int ptd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int R,
+                              int S, int stride, int pad, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
+    PTD_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "conv_wgrad: Cin (%d) and Cout (%d) must be multiples of 64", Cin, Cout);
+    WParams p;
+    memset(&p, 0, sizeof(p));
+    p.P = N * OH * OW; p.Cout = Cout; p.Kw = R * S * Cin; p.dw = dw;
+    int rc = ptd_make_tmap_2d_bf16(&p.tmA, dy, Cout, p.P, (uint64_t)Cout * 2, 64, 64);
+    if (rc) return rc;
+    const int nsub = pick_nsub(p.Kw / 64);
+    const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
+    if (plain) {
+        rc = ptd_make_tmap_2d_bf16(&p.tmB, x, Cin, p.P, (uint64_t)Cin * 2, 64, 64);
+        if (rc) return rc;
+        return dispatch_w<true>(p, nsub, stream);
+    }
+    fill_geom(p.g, (const bf16*)x, H, W, Cin, OH, OW, R, S, stride, pad, GM_FPROP);
+    return dispatch_w<false>(p, nsub, stream);
+}
+
+// Stem: x4 is NHWC with 4 channels (3 real + 1 zero), w4 is [64][8][8][4] (filter row 7 / tap 7 / channel 3 zero).
+extern "C" int ptd_stem_fprop(const void* x4, const void* w4, void* y, float* stat_sum, float* stat_sq, int N, int H,
+                              int W, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int OH = (H + 6 - 7) / 2 + 1, OW = (W + 6 - 7) / 2 + 1;
+    FParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = N * OH * OW; p.N = 64; p.num_kb = 4;
+    p.out = (bf16*)y; p.ldo = 64; p.stat_sum = stat_sum; p.stat_sq = stat_sq;
+    int rc = ptd_make_tmap_2d_bf16(&p.tmB, w4, 256, 64, 512, 64, 64);
+    if (rc) return rc;
+    fill_geom(p.g, (const bf16*)x4, H, W, 4, OH, OW, 7, 7, 2, 3, GM_STEM);
+    return dispatch_f<false, false, 0>(p, 64, stream);
+}
+
+extern "C" int ptd_stem_wgrad(const void* x4, const void* dy, float* dw4, int N, int H, int W, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int OH = (H + 6 - 7) / 2 + 1, OW = (W + 6 - 7) / 2 + 1;
+    WParams p;
+    memset(&p, 0, sizeof(p));
+    p.P = N * OH * OW; p.Cout = 64; p.Kw = 256; p.dw = dw4;
+    int rc = ptd_make_tmap_2d_bf16(&p.tmA, dy, 64, p.P, 128, 64, 64);
+    if (rc) return rc;
+    fill_geom(p.g, (const bf16*)x4, H, W, 4, OH, OW, 7, 7, 2, 3, GM_STEM);
+    return dispatch_w<false>(p, 4, stream);
+}
+
+// Classifier / generic dense layers.  a: [M][K] bf16, w: [N][K] bf16.
+//   forward : out_f32[M][N] = a * w^T + bias           (N need not be a multiple of the tile)
+extern "C" int ptd_linear_fwd(const void* a, const void* w, const float* bias, float* out, int M, int N, int K,
+                              void* stream_) {
+    PTD_REQUIRE(K % 8 == 0, "linear_fwd: K (%d) must be a multiple of 8 (16-byte TMA row pitch)", K);
+    FParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = M; p.N = N; p.num_kb = ceil_div_i(K, 64);
+    p.out_f32 = out; p.bias = bias; p.ldo = N;
+    const int bn = 128;
+    int rc = ptd_make_tmap_2d_bf16(&p.tmA, a, K, M, (uint64_t)K * 2, 64, BLOCK_M);
+    if (rc) return rc;
+    rc = ptd_make_tmap_2d_bf16(&p.tmB, w, K, N, (uint64_t)K * 2, 64, bn);
+    if (rc) return rc;
+    return dispatch_f<true, false, 1>(p, bn, (cudaStream_t)stream_);
+}
+
+//   data gradient : da_bf16[M][K] = dout_bf16[M][N] * w[N][K]        (K % 64 == 0)
+extern "C" int ptd_linear_dgrad(const void* dout, const void* w, void* da, int M, int N, int K, void* stream_) {
+    PTD_REQUIRE(K % 64 == 0 && N % 8 == 0, "linear_dgrad: K (%d) %% 64 and N (%d) %% 8 must be 0", K, N);
+    FParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = M; p.N = K; p.num_kb = ceil_div_i(N, 64);
+    p.out = (bf16*)da; p.ldo = K;
+    p.b_tap_cols = 0; p.b_cblocks = p.num_kb;
+    const int bn = pick_block_n(K);
+    int rc = ptd_make_tmap_2d_bf16(&p.tmA, dout, N, M, (uint64_t)N * 2, 64, BLOCK_M);
+    if (rc) return rc;
+    rc = ptd_make_tmap_2d_bf16(&p.tmB, w, K, N, (uint64_t)K * 2, 64, 64);
+    if (rc) return rc;
+    return dispatch_f<true, true, 0>(p, bn, (cudaStream_t)stream_);
+}
+
+//   weight gradient : dw_f32[N][K] += dout_bf16[M][N]^T * a_bf16[M][K]   (K % 64 == 0)
+extern "C" int ptd_linear_wgrad(const void* a, const void* dout, float* dw, int M, int N, int K, void* stream_) {
+    PTD_REQUIRE(K % 64 == 0 && N % 8 == 0, "linear_wgrad: K (%d) %% 64 and N (%d) %% 8 must be 0", K, N);
+    WParams p;
+    memset(&p, 0, sizeof(p));
+    p.P = M; p.Cout = N; p.Kw = K; p.dw = dw;
+    int rc = ptd_make_tmap_2d_bf16(&p.tmA, dout, N, M, (uint64_t)N * 2, 64, 64);
+    if (rc) return rc;
+    rc = ptd_make_tmap_2d_bf16(&p.tmB, a, K, M, (uint64_t)K * 2, 64, 64);
+    if (rc) return rc;
+    return dispatch_w<true>(p, pick_nsub(K / 64), (cudaStream_t)stream_);
+}

@@ -1,0 +1,83 @@
+// Host-side runtime shared by all kernels: error string, SM count cache, TMA tensor-map encoding
+// (driver entry point fetched at run time so the library links without libcuda and loads on a
+// CPU-only box for the plumbing tests).
+#include <stdarg.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "common.cuh"
+#include "tensormap.h"
+
+static thread_local char g_err[1024] = "";
+
+void ptd_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char* ptd_last_error() { return g_err; }
+
+extern "C" int ptd_version() { return 100; }
+
+int ptd_num_sms() {
+    static int cache[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cache[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cache[dev] = n;
+    }
+    return cache[dev];
+}
+
+extern "C" int ptd_device_sm_count() { return ptd_num_sms(); }
+
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+int ptd_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t rows, uint64_t row_pitch_bytes,
+                          uint32_t box_inner, uint32_t box_rows) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) {
+        ptd_set_error("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
+        return PTD_ERR_CUDA;
+    }
+    if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || (row_pitch_bytes & 15) != 0) {
+        ptd_set_error("TMA needs a 16-byte aligned base (%p) and row pitch (%llu)", base,
+                      (unsigned long long)row_pitch_bytes);
+        return PTD_ERR_ARG;
+    }
+    cuuint64_t dims[2] = {inner, rows};
+    cuuint64_t strides[1] = {row_pitch_bytes};
+    cuuint32_t box[2] = {box_inner, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        ptd_set_error("cuTensorMapEncodeTiled failed: %d (inner=%llu rows=%llu pitch=%llu box=%ux%u)", (int)r,
+                      (unsigned long long)inner, (unsigned long long)rows, (unsigned long long)row_pitch_bytes,
+                      box_inner, box_rows);
+        return PTD_ERR_CUDA;
+    }
+    return PTD_OK;
+}

@@ -1,0 +1,10 @@
+// Host helper: encode a 2-D bf16 TMA descriptor with 128-byte swizzle.
+#pragma once
+#include <cuda.h>
+#include <stdint.h>
+
+// `inner` is the contiguous extent in elements, `rows` the outer extent, `row_pitch_bytes` the
+// distance between rows.  The box is `box_inner` x `box_rows` elements (box_inner * 2 <= 128).
+// Out-of-bounds elements of a box read as zero.
+int ptd_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t rows, uint64_t row_pitch_bytes,
+                          uint32_t box_inner, uint32_t box_rows);

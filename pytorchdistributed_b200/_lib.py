@@ -1,0 +1,140 @@
+"""ctypes binding of ``libptdb200.so`` (declarations mirror ``include/ptdb200.h``).
+
+The library is plain C ABI: no torch C++ ABI coupling, compiles in seconds, and the same ``.so``
+serves Python, tests and foreign callers.  ``call(name, *args)`` accepts tensors (passed as device
+pointers), ``None`` (NULL), ints and floats; a non-zero return raises ``RuntimeError`` with the
+library's message.  On a box with a GPU a missing library is a hard error - there is no silent
+fallback to eager PyTorch for the CUDA ops.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int, c_longlong, c_void_p
+from pathlib import Path
+from typing import Any, Optional
+
+import torch
+
+P, I, L, F = c_void_p, c_int, c_longlong, c_float
+
+_SIGS: dict[str, list] = {
+    "ptd_version": [],
+    "ptd_device_sm_count": [],
+    "ptd_conv_fprop": [P, P, P, P, P, I, I, I, I, I, I, I, I, I, P],
+    "ptd_conv_dgrad": [P, P, P, P, I, I, I, I, I, I, I, I, I, P],
+    "ptd_conv_wgrad": [P, P, P, I, I, I, I, I, I, I, I, I, P],
+    "ptd_stem_fprop": [P, P, P, P, P, I, I, I, P],
+    "ptd_stem_wgrad": [P, P, P, I, I, I, P],
+    "ptd_linear_fwd": [P, P, P, P, I, I, I, P],
+    "ptd_linear_dgrad": [P, P, P, I, I, I, P],
+    "ptd_linear_wgrad": [P, P, P, I, I, I, P],
+    "ptd_bn_stats": [P, P, P, L, I, P],
+    "ptd_bn_apply": [P, P, P, P, P, P, P, P, P, P, P, L, I, F, F, I, P],
+    "ptd_affine_act": [P, P, P, P, P, L, I, I, P],
+    "ptd_bn_bwd_reduce": [P, P, P, P, P, P, P, L, I, I, P],
+    "ptd_bn_bwd_apply": [P, P, P, P, P, P, P, P, P, P, L, I, I, P],
+    "ptd_maxpool3x3s2_fwd": [P, P, P, I, I, I, I, P],
+    "ptd_maxpool3x3s2_bwd": [P, P, P, I, I, I, I, P],
+    "ptd_avgpool_fwd": [P, P, I, I, I, P],
+    "ptd_avgpool_bwd": [P, P, I, I, I, P],
+    "ptd_nchw3_f32_to_nhwc4_bf16": [P, P, I, I, I, P],
+    "ptd_nchw_f32_to_nhwc_bf16": [P, P, I, I, I, P],
+    "ptd_nhwc_bf16_to_nchw_f32": [P, P, I, I, I, P],
+    "ptd_cast_f32_to_bf16": [P, P, L, P],
+    "ptd_stem_pack_weight": [P, P, L, L, L, L, P],
+    "ptd_stem_unpack_wgrad": [P, P, L, L, L, L, I, P],
+    "ptd_softmax_ce": [P, P, P, P, P, I, I, I, I, F, P],
+    "ptd_multi_sgd": [P, P, I, F, F, F, F, I, P],
+    "ptd_multi_adam": [P, P, I, F, F, F, F, F, I, F, P],
+    "ptd_multi_cast_bf16": [P, P, I, P],
+    "ptd_multi_zero_grad": [P, P, I, P],
+    "ptd_opt_chunk_elems": [],
+    "ptd_small_linear_fwd": [P, P, P, P, I, I, I, I, P],
+    "ptd_small_linear_bwd": [P, P, P, P, P, P, I, I, I, P],
+    "ptd_mlp_fwd": [P, P, P, P, P, I, I, P],
+}
+
+_LIB: Optional[ctypes.CDLL] = None
+_LOAD_ERROR: Optional[str] = None
+LIB_PATH = Path(__file__).resolve().parent / "lib" / "libptdb200.so"
+
+
+def _load() -> Optional[ctypes.CDLL]:
+    global _LIB, _LOAD_ERROR
+    if _LIB is not None or _LOAD_ERROR is not None:
+        return _LIB
+    path = Path(os.environ.get("PTDB200_LIB", LIB_PATH))
+    if not path.exists():
+        try:
+            from ._build import build
+            build()
+        except Exception as e:  # noqa: BLE001 - surfaced through available()/require()
+            _LOAD_ERROR = f"{path} missing and in-tree build failed: {e}"
+            return None
+    try:
+        lib = ctypes.CDLL(str(path))
+    except OSError as e:
+        _LOAD_ERROR = f"cannot load {path}: {e}"
+        return None
+    lib.ptd_last_error.restype = c_char_p
+    lib.ptd_last_error.argtypes = []
+    for name, sig in _SIGS.items():
+        fn = getattr(lib, name, None)
+        if fn is None:
+            continue
+        fn.restype = c_int
+        fn.argtypes = sig
+    _LIB = lib
+    return _LIB
+
+
+def available() -> bool:
+    return _load() is not None
+
+
+def load_error() -> Optional[str]:
+    _load()
+    return _LOAD_ERROR
+
+
+def require() -> ctypes.CDLL:
+    lib = _load()
+    if lib is None:
+        raise RuntimeError(f"pytorchdistributed_b200 native library unavailable: {_LOAD_ERROR}")
+    return lib
+
+
+def register(name: str, sig: list) -> None:
+    """Declare an entry point added by another module (e.g. the peer-to-peer runtime)."""
+    _SIGS[name] = sig
+    if _LIB is not None and hasattr(_LIB, name):
+        fn = getattr(_LIB, name)
+        fn.restype = c_int
+        fn.argtypes = sig
+
+
+def _conv(a: Any):
+    if a is None:
+        return None
+    if isinstance(a, torch.Tensor):
+        return a.data_ptr()
+    return a
+
+
+def stream_ptr(device: Optional[torch.device] = None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def call(name: str, *args: Any) -> None:
+    lib = require()
+    rc = getattr(lib, name)(*[_conv(a) for a in args])
+    if rc != 0:
+        msg = lib.ptd_last_error()
+        raise RuntimeError(f"{name} failed ({rc}): {msg.decode() if msg else '?'}")
+
+
+def call_ret(name: str, *args: Any) -> int:
+    """Call an entry point whose return value is data (not an error code)."""
+    lib = require()
+    return getattr(lib, name)(*[_conv(a) for a in args])

@@ -1,0 +1,421 @@
+"""Autograd-level ops on top of the sm_100a kernel library.
+
+Activations are ``torch.bfloat16`` tensors with logical shape ``[N, C, H, W]`` in
+``torch.channels_last`` memory format, i.e. NHWC in memory - the layout the tensor-core kernels
+read with TMA / 128-byte row gathers.  Convolution weights are fp32 masters with logical shape
+``[Cout, Cin, R, S]`` in channels_last (physically ``[Cout][R][S][Cin]``) plus a bf16 shadow.
+
+Every op here launches our kernels; there is no eager-PyTorch fallback on a CUDA tensor.  The same
+math in plain PyTorch lives in ``ops/reference.py`` and is what the tests compare against (and what
+CPU tensors use, so the model classes stay importable/runnable for plumbing tests without a GPU).
+
+Reference call sites: every layer of torchvision ``ResNet(Bottleneck,[3,4,6,3])`` used by
+``R/03 模型并行/03_model_parallel.ipynb#cell4-5,12`` and the loss/optimizer calls of
+``R/02 DDP基本概念/ddp_gpus.py:37-42``.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from .. import _lib
+from . import reference as ref
+
+CL = torch.channels_last
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _empty_act(n: int, c: int, h: int, w: int, device, dtype=torch.bfloat16) -> torch.Tensor:
+    return torch.empty((n, c, h, w), device=device, dtype=dtype, memory_format=CL)
+
+
+def is_nhwc_bf16(x: torch.Tensor) -> bool:
+    return x.dtype == torch.bfloat16 and x.dim() == 4 and x.is_contiguous(memory_format=CL)
+
+
+def as_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
+    """Bring any 4-D activation to bf16 channels_last (no copy if already there)."""
+    if is_nhwc_bf16(x):
+        return x
+    if x.is_cuda and x.dtype == torch.float32 and x.is_contiguous():
+        n, c, h, w = x.shape
+        out = _empty_act(n, c, h, w, x.device)
+        _lib.call("ptd_nchw_f32_to_nhwc_bf16", x, out, n, c, h * w, _stream())
+        return out
+    return x.to(dtype=torch.bfloat16).contiguous(memory_format=CL)
+
+
+def out_hw(h: int, w: int, r: int, s: int, stride: int, pad: int) -> Tuple[int, int]:
+    return (h + 2 * pad - r) // stride + 1, (w + 2 * pad - s) // stride + 1
+
+
+# ------------------------------------------------------------------------------------------------
+# raw kernel wrappers (no autograd)
+# ------------------------------------------------------------------------------------------------
+def conv_fprop_raw(x: torch.Tensor, w_bf16: torch.Tensor, stride: int, pad: int, want_stats: bool):
+    n, cin, h, w = x.shape
+    cout, _, r, s = w_bf16.shape
+    oh, ow = out_hw(h, w, r, s, stride, pad)
+    y = _empty_act(n, cout, oh, ow, x.device)
+    stats = torch.zeros((2, cout), device=x.device, dtype=torch.float32) if want_stats else None
+    _lib.call("ptd_conv_fprop", x, w_bf16, y, stats[0] if want_stats else None, stats[1] if want_stats else None,
+              n, h, w, cin, cout, r, s, stride, pad, _stream())
+    return y, stats
+
+
+def conv_dgrad_raw(dy: torch.Tensor, w_bf16: torch.Tensor, x_shape, stride: int, pad: int,
+                   addend: Optional[torch.Tensor] = None) -> torch.Tensor:
+    n, cin, h, w = x_shape
+    cout, _, r, s = w_bf16.shape
+    dx = _empty_act(n, cin, h, w, dy.device)
+    _lib.call("ptd_conv_dgrad", dy, w_bf16, dx, addend, n, h, w, cin, cout, r, s, stride, pad, _stream())
+    return dx
+
+
+def conv_wgrad_raw(x: torch.Tensor, dy: torch.Tensor, w_shape, stride: int, pad: int,
+                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    n, cin, h, w = x.shape
+    cout, _, r, s = w_shape
+    if out is None:
+        out = torch.empty(w_shape, device=x.device, dtype=torch.float32, memory_format=CL).zero_()
+    _lib.call("ptd_conv_wgrad", x, dy, out, n, h, w, cin, cout, r, s, stride, pad, _stream())
+    return out
+
+
+def bn_apply_raw(y, stats, gamma, beta, running_mean, running_var, eps, momentum, relu, residual=None):
+    n, c, h, w = y.shape
+    z = torch.empty_like(y, memory_format=CL)
+    saved = torch.empty((2, c), device=y.device, dtype=torch.float32)
+    _lib.call("ptd_bn_apply", y, residual, z, stats[0], stats[1], gamma, beta, running_mean, running_var,
+              saved[0], saved[1], n * h * w, c, float(eps), float(momentum), int(relu), _stream())
+    return z, saved
+
+
+def bn_stats_raw(y: torch.Tensor) -> torch.Tensor:
+    n, c, h, w = y.shape
+    stats = torch.zeros((2, c), device=y.device, dtype=torch.float32)
+    _lib.call("ptd_bn_stats", y, stats[0], stats[1], n * h * w, c, _stream())
+    return stats
+
+
+def bn_backward_raw(dz, z, y, saved, gamma, relu: bool, want_gout: bool):
+    n, c, h, w = y.shape
+    m = n * h * w
+    sums = torch.zeros((2, c), device=y.device, dtype=torch.float32)   # [0] = dbeta, [1] = dgamma
+    _lib.call("ptd_bn_bwd_reduce", dz, z, y, saved[0], saved[1], sums[0], sums[1], m, c, int(relu), _stream())
+    dy = torch.empty_like(y, memory_format=CL)
+    gout = torch.empty_like(y, memory_format=CL) if want_gout else None
+    _lib.call("ptd_bn_bwd_apply", dz, z, y, saved[0], saved[1], gamma, sums[0], sums[1], dy, gout, m, c, int(relu),
+              _stream())
+    return dy, gout, sums[1], sums[0]
+
+
+# ------------------------------------------------------------------------------------------------
+# conv + batch-norm (+ residual) (+ ReLU), training mode - the workhorse
+# ------------------------------------------------------------------------------------------------
+class _ConvBnAct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, w_bf16, gamma, beta, running_mean, running_var, residual, stride, pad, eps,
+                momentum, relu, stem):
+        x = x if stem else as_nhwc_bf16(x)
+        if stem:
+            y, stats = stem_fprop_raw(x, w_bf16)
+        else:
+            y, stats = conv_fprop_raw(x, w_bf16, stride, pad, True)
+        z, saved = bn_apply_raw(y, stats, gamma, beta, running_mean, running_var, eps, momentum, relu, residual)
+        ctx.save_for_backward(x, w_bf16, y, z, saved, gamma)
+        ctx.cfg = (stride, pad, relu, stem, residual is not None, tuple(weight.shape))
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        x, w_bf16, y, z, saved, gamma = ctx.saved_tensors
+        stride, pad, relu, stem, has_res, w_shape = ctx.cfg
+        dz = as_nhwc_bf16(dz)
+        need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        dy, gout, dgamma, dbeta = bn_backward_raw(dz, z, y, saved, gamma, relu, has_res and ctx.needs_input_grad[7])
+        dx = dw = None
+        if stem:
+            if need_w:
+                dw = stem_wgrad_raw(x, dy, w_shape)
+        else:
+            if need_x:
+                dx = conv_dgrad_raw(dy, w_bf16, x.shape, stride, pad)
+            if need_w:
+                dw = conv_wgrad_raw(x, dy, w_shape, stride, pad)
+        return dx, dw, None, dgamma, dbeta, None, None, gout, None, None, None, None, None, None
+
+
+def conv_bn_act(x, weight, w_bf16, gamma, beta, running_mean, running_var, residual=None, stride=1, pad=0,
+                eps=1e-5, momentum=0.1, relu=True, stem=False):
+    if not x.is_cuda:
+        return ref.conv_bn_act(x, weight, gamma, beta, running_mean, running_var, residual, stride, pad, eps,
+                               momentum, relu)
+    return _ConvBnAct.apply(x, weight, w_bf16, gamma, beta, running_mean, running_var, residual, stride, pad, eps,
+                            momentum, relu, stem)
+
+
+# ---- conv only / bn only (standalone modules, e.g. inside a user-built nn.Sequential) -------------
+class _Conv(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, w_bf16, stride, pad):
+        x = as_nhwc_bf16(x)
+        y, _ = conv_fprop_raw(x, w_bf16, stride, pad, False)
+        ctx.save_for_backward(x, w_bf16)
+        ctx.cfg = (stride, pad, tuple(weight.shape))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w_bf16 = ctx.saved_tensors
+        stride, pad, w_shape = ctx.cfg
+        dy = as_nhwc_bf16(dy)
+        dx = conv_dgrad_raw(dy, w_bf16, x.shape, stride, pad) if ctx.needs_input_grad[0] else None
+        dw = conv_wgrad_raw(x, dy, w_shape, stride, pad) if ctx.needs_input_grad[1] else None
+        return dx, dw, None, None, None
+
+
+def conv2d(x, weight, w_bf16, stride=1, pad=0):
+    if not x.is_cuda:
+        return ref.conv2d(x, weight, stride, pad)
+    return _Conv.apply(x, weight, w_bf16, stride, pad)
+
+
+class _BnAct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, y, gamma, beta, running_mean, running_var, residual, eps, momentum, relu):
+        y = as_nhwc_bf16(y)
+        stats = bn_stats_raw(y)
+        z, saved = bn_apply_raw(y, stats, gamma, beta, running_mean, running_var, eps, momentum, relu, residual)
+        ctx.save_for_backward(y, z, saved, gamma)
+        ctx.cfg = (relu, residual is not None)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        y, z, saved, gamma = ctx.saved_tensors
+        relu, has_res = ctx.cfg
+        dz = as_nhwc_bf16(dz)
+        dy, gout, dgamma, dbeta = bn_backward_raw(dz, z, y, saved, gamma, relu, has_res and ctx.needs_input_grad[5])
+        return dy, dgamma, dbeta, None, None, gout, None, None, None
+
+
+def batch_norm_act(y, gamma, beta, running_mean, running_var, residual=None, eps=1e-5, momentum=0.1, relu=False):
+    if not y.is_cuda:
+        return ref.batch_norm_act(y, gamma, beta, running_mean, running_var, residual, eps, momentum, relu)
+    return _BnAct.apply(y, gamma, beta, running_mean, running_var, residual, eps, momentum, relu)
+
+
+def affine_act(y, scale, shift, residual=None, relu=False):
+    """Inference-mode BN (per-channel affine) + residual + ReLU; no autograd (eval only)."""
+    if not y.is_cuda:
+        return ref.affine_act(y, scale, shift, residual, relu)
+    y = as_nhwc_bf16(y)
+    n, c, h, w = y.shape
+    z = torch.empty_like(y, memory_format=CL)
+    _lib.call("ptd_affine_act", y, residual, z, scale, shift, n * h * w, c, int(relu), _stream())
+    return z
+
+
+# ------------------------------------------------------------------------------------------------
+# stem helpers
+# ------------------------------------------------------------------------------------------------
+def to_nhwc4(x: torch.Tensor) -> torch.Tensor:
+    """fp32 NCHW image batch [N,3,H,W] -> bf16 NHWC with a zero 4th channel (stem input)."""
+    n, c, h, w = x.shape
+    assert c == 3, "stem expects 3 input channels"
+    x = x.contiguous().float()
+    out = _empty_act(n, 4, h, w, x.device)
+    _lib.call("ptd_nchw3_f32_to_nhwc4_bf16", x, out, n, h, w, _stream())
+    return out
+
+
+def stem_pack(weight: torch.Tensor) -> torch.Tensor:
+    w4 = torch.empty((64, 256), device=weight.device, dtype=torch.bfloat16)
+    sk, sc, sr, ss = weight.stride()
+    _lib.call("ptd_stem_pack_weight", weight, w4, sk, sc, sr, ss, _stream())
+    return w4
+
+
+def stem_fprop_raw(x4: torch.Tensor, w4: torch.Tensor):
+    n, _, h, w = x4.shape
+    oh, ow = out_hw(h, w, 7, 7, 2, 3)
+    y = _empty_act(n, 64, oh, ow, x4.device)
+    stats = torch.zeros((2, 64), device=x4.device, dtype=torch.float32)
+    _lib.call("ptd_stem_fprop", x4, w4, y, stats[0], stats[1], n, h, w, _stream())
+    return y, stats
+
+
+def stem_wgrad_raw(x4: torch.Tensor, dy: torch.Tensor, w_shape) -> torch.Tensor:
+    n, _, h, w = x4.shape
+    dw4 = torch.zeros((64, 256), device=x4.device, dtype=torch.float32)
+    _lib.call("ptd_stem_wgrad", x4, dy, dw4, n, h, w, _stream())
+    dw = torch.empty(w_shape, device=x4.device, dtype=torch.float32, memory_format=CL)
+    sk, sc, sr, ss = dw.stride()
+    _lib.call("ptd_stem_unpack_wgrad", dw4, dw, sk, sc, sr, ss, 0, _stream())
+    return dw
+
+
+# ------------------------------------------------------------------------------------------------
+# pooling
+# ------------------------------------------------------------------------------------------------
+class _MaxPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = as_nhwc_bf16(x)
+        n, c, h, w = x.shape
+        oh, ow = out_hw(h, w, 3, 3, 2, 1)
+        y = _empty_act(n, c, oh, ow, x.device)
+        idx = _empty_act(n, c, oh, ow, x.device, dtype=torch.uint8)
+        _lib.call("ptd_maxpool3x3s2_fwd", x, y, idx, n, h, w, c, _stream())
+        ctx.save_for_backward(idx)
+        ctx.shape = (n, c, h, w)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        n, c, h, w = ctx.shape
+        dy = as_nhwc_bf16(dy)
+        dx = _empty_act(n, c, h, w, dy.device)
+        _lib.call("ptd_maxpool3x3s2_bwd", dy, idx, dx, n, h, w, c, _stream())
+        return dx
+
+
+def max_pool_3x3_s2(x):
+    if not x.is_cuda:
+        return ref.max_pool_3x3_s2(x)
+    return _MaxPool.apply(x)
+
+
+class _AvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = as_nhwc_bf16(x)
+        n, c, h, w = x.shape
+        y = torch.empty((n, c), device=x.device, dtype=torch.bfloat16)
+        _lib.call("ptd_avgpool_fwd", x, y, n, h * w, c, _stream())
+        ctx.shape = (n, c, h, w)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        n, c, h, w = ctx.shape
+        dy = dy.to(torch.bfloat16).contiguous()
+        dx = _empty_act(n, c, h, w, dy.device)
+        _lib.call("ptd_avgpool_bwd", dy, dx, n, h * w, c, _stream())
+        return dx
+
+
+def global_avg_pool(x):
+    """[N,C,H,W] -> [N,C] (bf16), i.e. AdaptiveAvgPool2d(1) + flatten."""
+    if not x.is_cuda:
+        return ref.global_avg_pool(x)
+    return _AvgPool.apply(x)
+
+
+# ------------------------------------------------------------------------------------------------
+# classifier, loss
+# ------------------------------------------------------------------------------------------------
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a, weight, w_bf16, bias):
+        a = a.to(torch.bfloat16).contiguous()
+        m, k = a.shape
+        n = weight.shape[0]
+        out = torch.empty((m, n), device=a.device, dtype=torch.float32)
+        _lib.call("ptd_linear_fwd", a, w_bf16, bias, out, m, n, k, _stream())
+        ctx.save_for_backward(a, w_bf16)
+        ctx.has_bias = bias is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        a, w_bf16 = ctx.saved_tensors
+        m, k = a.shape
+        n = w_bf16.shape[0]
+        d16 = dout.to(torch.bfloat16).contiguous()
+        da = dw = db = None
+        if ctx.needs_input_grad[0]:
+            da = torch.empty((m, k), device=a.device, dtype=torch.bfloat16)
+            _lib.call("ptd_linear_dgrad", d16, w_bf16, da, m, n, k, _stream())
+        if ctx.needs_input_grad[1]:
+            dw = torch.zeros((n, k), device=a.device, dtype=torch.float32)
+            _lib.call("ptd_linear_wgrad", a, d16, dw, m, n, k, _stream())
+        if ctx.has_bias and ctx.needs_input_grad[3]:
+            db = dout.float().sum(0)
+        return da, dw, None, db
+
+
+def linear(a, weight, w_bf16, bias):
+    if not a.is_cuda:
+        return ref.linear(a, weight, bias)
+    return _Linear.apply(a, weight, w_bf16, bias)
+
+
+class _SoftmaxCE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target):
+        logits = logits.float().contiguous()
+        rows, c = logits.shape
+        loss = torch.zeros((), device=logits.device, dtype=torch.float32)
+        dlogits = torch.empty_like(logits)
+        soft = target.is_floating_point()
+        tgt = target.float().contiguous() if soft else target.long().contiguous()
+        _lib.call("ptd_softmax_ce", logits, tgt if soft else None, None if soft else tgt, loss, dlogits, 0, rows, c,
+                  c, 1.0 / rows, _stream())
+        ctx.save_for_backward(dlogits)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (dlogits,) = ctx.saved_tensors
+        return dlogits * g, None
+
+
+def cross_entropy(logits, target):
+    """Mean softmax cross-entropy; ``target`` is class indices [B] or probabilities [B, C]."""
+    if not logits.is_cuda:
+        return ref.cross_entropy(logits, target)
+    return _SoftmaxCE.apply(logits, target)
+
+
+# ------------------------------------------------------------------------------------------------
+# tutorial-sized dense layers (fp32, CUDA cores)
+# ------------------------------------------------------------------------------------------------
+class _SmallLinear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b, relu):
+        x = x.float().contiguous()
+        bsz, k = x.shape
+        n = w.shape[0]
+        y = torch.empty((bsz, n), device=x.device, dtype=torch.float32)
+        _lib.call("ptd_small_linear_fwd", x, w.contiguous(), b, y, bsz, k, n, int(relu), _stream())
+        ctx.save_for_backward(x, w, y)
+        ctx.relu = relu
+        ctx.has_bias = b is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, y = ctx.saved_tensors
+        bsz, k = x.shape
+        n = w.shape[0]
+        dy = dy.float().contiguous()
+        if ctx.relu:
+            dy = dy * (y > 0)
+        dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        dw = torch.zeros_like(w, memory_format=torch.contiguous_format) if ctx.needs_input_grad[1] else None
+        db = torch.zeros(n, device=x.device, dtype=torch.float32) if (ctx.has_bias and dw is not None) else None
+        _lib.call("ptd_small_linear_bwd", x, w.contiguous(), dy, dx, dw, db, bsz, k, n, _stream())
+        return dx, dw, db, None
+
+
+def small_linear(x, w, b, relu=False):
+    if not x.is_cuda:
+        return ref.small_linear(x, w, b, relu)
+    return _SmallLinear.apply(x, w, b, relu)

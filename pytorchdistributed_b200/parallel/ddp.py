@@ -1,0 +1,357 @@
+"""``DistributedDataParallel`` - one process per GPU, bucketed gradient averaging overlapped with backward.
+
+Surface and semantics follow what the reference uses (``DDP(model, device_ids=[gpu_id])`` at
+``R/02 DDP基本概念/ddp_gpus.py:35`` / ``ddp_gpus_torchrun.py:33``; inner module under ``.module`` so
+``state_dict()`` keys carry the ``module.`` prefix):
+
+* construction: parameter shapes are checked across ranks, then rank 0's parameters and buffers win;
+* gradients live as views into flat per-bucket buffers (first bucket 1 MiB, then 25 MiB, reverse
+  registration order; rebuilt once in observed ready order) - flatten is free;
+* a post-accumulate-grad hook per parameter tells the native reducer (``csrc/reducer.cpp``) the
+  gradient is ready; a bucket whose last gradient arrived is averaged across ranks right away on a
+  communication stream, overlapping the rest of backward;
+* ``no_sync()`` skips the reduction (local accumulation); buffers (BatchNorm statistics) are
+  re-broadcast from rank 0 before every forward, as one flat message.
+
+What changes underneath: on CUDA with >1 rank the averaging is our own peer-to-peer kernel over
+NVLink (``comm/p2p.py``: one-shot / two-shot / multimem, fused with the 1/world scale and the
+optional bf16 wire format); no NCCL call on that path.  ``comm="nccl"``/``"gloo"`` selects the
+``torch.distributed`` collective instead (baseline, and the CPU plumbing path).
+"""
+from __future__ import annotations
+
+import contextlib
+import ctypes
+import os
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from .. import _lib
+
+_MiB = 1024 * 1024
+
+_lib.register("ptd_plan_buckets", [ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_longlong, ctypes.c_void_p])
+_lib.register("ptd_reducer_create", [ctypes.c_void_p, ctypes.c_int, ctypes.c_int])
+_lib.register("ptd_reducer_mark_ready", [ctypes.c_int, ctypes.c_int])
+_lib.register("ptd_reducer_all_done", [ctypes.c_int])
+_lib.register("ptd_reducer_ready_order", [ctypes.c_int, ctypes.c_void_p, ctypes.c_int])
+_lib.register("ptd_reducer_incomplete", [ctypes.c_int, ctypes.c_void_p, ctypes.c_int])
+_lib.register("ptd_reducer_reset", [ctypes.c_int])
+_lib.register("ptd_reducer_destroy", [ctypes.c_int])
+
+
+def plan_buckets(sizes_bytes: List[int], first_cap: int, cap: int) -> List[int]:
+    """Bucket index per tensor, tensors taken in the given order (native planner)."""
+    n = len(sizes_bytes)
+    if n == 0:
+        return []
+    sizes = (ctypes.c_longlong * n)(*sizes_bytes)
+    out = (ctypes.c_int * n)()
+    nb = _lib.call_ret("ptd_plan_buckets", ctypes.cast(sizes, ctypes.c_void_p), n, first_cap, cap,
+                       ctypes.cast(out, ctypes.c_void_p))
+    if nb < 0:
+        raise RuntimeError("ptd_plan_buckets failed")
+    return list(out)
+
+
+class _TorchCollectives:
+    """Gradient averaging / broadcast through torch.distributed (gloo on CPU, NCCL baseline on GPU)."""
+
+    name = "torch"
+
+    def __init__(self, group) -> None:
+        self.group = group
+        self.world = dist.get_world_size(group)
+
+    def alloc(self, numel: int, dtype, device) -> torch.Tensor:
+        return torch.zeros(numel, dtype=dtype, device=device)
+
+    def all_reduce_avg(self, flat: torch.Tensor) -> None:
+        if flat.is_cuda:
+            dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group)
+        else:
+            dist.all_reduce(flat, group=self.group)
+            flat.div_(self.world)
+
+    def broadcast(self, flat: torch.Tensor, src: int = 0) -> None:
+        dist.broadcast(flat, src=dist.get_global_rank(self.group, src) if self.group is not None else src,
+                       group=self.group)
+
+    def close(self) -> None:
+        pass
+
+
+class _Bucket:
+    __slots__ = ("flat", "params", "views", "offsets", "ready_event", "done_event", "launched")
+
+    def __init__(self) -> None:
+        self.params: List[nn.Parameter] = []
+        self.views: List[torch.Tensor] = []
+        self.offsets: List[int] = []
+        self.flat: Optional[torch.Tensor] = None
+        self.ready_event = None
+        self.done_event = None
+        self.launched = False
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(self, module: nn.Module, device_ids=None, output_device=None, dim: int = 0,
+                 broadcast_buffers: bool = True, process_group=None, bucket_cap_mb: float = 25,
+                 first_bucket_mb: float = 1, find_unused_parameters: bool = False,
+                 gradient_as_bucket_view: bool = True, comm: str = "auto", wire_dtype: Optional[torch.dtype] = None,
+                 rebuild_buckets: bool = True) -> None:
+        super().__init__()
+        if not dist.is_initialized():
+            raise RuntimeError("DistributedDataParallel needs an initialised process group (comm.ddp_setup)")
+        if find_unused_parameters:
+            raise NotImplementedError("find_unused_parameters=True is not supported")
+        self.module = module
+        self.process_group = process_group
+        self.world_size = dist.get_world_size(process_group)
+        self.rank = dist.get_rank(process_group)
+        self.broadcast_buffers = broadcast_buffers
+        self.require_backward_grad_sync = True
+        self.bucket_cap = int(bucket_cap_mb * _MiB)
+        self.first_cap = int(first_bucket_mb * _MiB)
+        self._want_rebuild = rebuild_buckets
+        self._rebuilt = False
+        self._params: List[nn.Parameter] = [p for p in module.parameters() if p.requires_grad]
+        if not self._params:
+            raise RuntimeError("DistributedDataParallel: module has no parameter that requires grad")
+        self.device = self._params[0].device
+        if device_ids is not None and self.device.type == "cuda":
+            want = torch.device("cuda", device_ids[0]) if isinstance(device_ids[0], int) else torch.device(device_ids[0])
+            if want.index is not None and want != self.device:
+                raise RuntimeError(f"module is on {self.device} but device_ids={device_ids}")
+        self.backend = self._make_backend(comm, wire_dtype)
+        self._comm_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
+        self._verify_shapes()
+        self._flatten_buffers()
+        self._sync_module_states()
+        self._index_of: Dict[int, int] = {id(p): i for i, p in enumerate(self._params)}
+        self._reducer_id = 0
+        self._buckets: List[_Bucket] = []
+        self._build_buckets(list(reversed(range(len(self._params)))))
+        self._callback_queued = False
+        self._hooks = [p.register_post_accumulate_grad_hook(self._grad_ready) for p in self._params]
+        self.stats = {"allreduce_launches": 0, "bytes_reduced": 0, "iterations": 0}
+
+    # ------------------------------------------------------------------ construction helpers
+    def _make_backend(self, comm: str, wire_dtype):
+        comm = os.environ.get("PTDB200_DDP_COMM", comm)
+        if comm == "auto":
+            comm = "p2p" if (self.device.type == "cuda" and self.world_size > 1) else "torch"
+        if comm == "p2p":
+            from ..comm import p2p
+            return p2p.P2PCollectives(self.process_group, self.device, wire_dtype=wire_dtype)
+        return _TorchCollectives(self.process_group)
+
+    def _verify_shapes(self) -> None:
+        mine = [tuple(p.shape) for p in self._params]
+        allv: List = [None] * self.world_size
+        dist.all_gather_object(allv, mine, group=self.process_group)
+        for r, other in enumerate(allv):
+            if other != mine:
+                raise RuntimeError(f"parameter shapes differ between rank {self.rank} and rank {r}")
+
+    def _flatten_buffers(self) -> None:
+        """Re-point every floating buffer at a slice of one flat tensor (same for integer buffers) so the
+        per-forward buffer broadcast is one message instead of one per BatchNorm tensor."""
+        self._buf_flats: List[torch.Tensor] = []
+        groups: Dict[torch.dtype, List] = {}
+        for mod in self.module.modules():
+            for name, buf in mod._buffers.items():
+                if buf is not None and name not in mod._non_persistent_buffers_set:
+                    groups.setdefault(buf.dtype, []).append((mod, name, buf))
+        for dtype, items in groups.items():
+            total = sum(b.numel() for _, _, b in items)
+            flat = self.backend.alloc(total, dtype, items[0][2].device)
+            off = 0
+            for mod, name, buf in items:
+                n = buf.numel()
+                view = flat[off:off + n].view(buf.shape)
+                view.copy_(buf)
+                mod._buffers[name] = view
+                off += n
+            self._buf_flats.append(flat)
+
+    def _sync_module_states(self) -> None:
+        """Rank 0's parameters and buffers win (torch DDP does the same at construction)."""
+        if self.world_size == 1:
+            return
+        with torch.no_grad():
+            chunks = [self._storage_view(p) for p in self.module.parameters()]
+            by_dtype: Dict[torch.dtype, List[torch.Tensor]] = {}
+            for c in chunks:
+                by_dtype.setdefault(c.dtype, []).append(c)
+            for _, group in by_dtype.items():
+                flat = torch.cat(group)
+                self.backend.broadcast(flat, 0)
+                off = 0
+                for c in group:
+                    c.copy_(flat[off:off + c.numel()])
+                    off += c.numel()
+            for bf in self._buf_flats:
+                self.backend.broadcast(bf, 0)
+
+    @staticmethod
+    def _storage_view(p: torch.Tensor) -> torch.Tensor:
+        """1-D view of a dense tensor in memory order (so channels_last parameters need no permute)."""
+        t = p.detach()
+        return torch.as_strided(t, (t.numel(),), (1,), t.storage_offset())
+
+    def _build_buckets(self, order: List[int]) -> None:
+        sizes = [self._params[i].numel() * self._params[i].element_size() for i in order]
+        assign = plan_buckets(sizes, self.first_cap, self.bucket_cap)
+        n_buckets = max(assign) + 1
+        old_grads = {id(p): p.grad for p in self._params}
+        buckets = [_Bucket() for _ in range(n_buckets)]
+        bucket_of = [0] * len(self._params)
+        for pos, pi in enumerate(order):
+            buckets[assign[pos]].params.append(self._params[pi])
+            bucket_of[pi] = assign[pos]
+        for b in buckets:
+            total, offs = 0, []
+            for p in b.params:
+                total = (total + 3) // 4 * 4          # 16-byte alignment of every fp32 view
+                offs.append(total)
+                total += p.numel()
+            total = (total + 31) // 32 * 32
+            dtype = b.params[0].dtype
+            b.flat = self.backend.alloc(total, dtype, self.device)
+            b.offsets = offs
+            for p, off in zip(b.params, offs):
+                view = torch.as_strided(b.flat, p.shape, p.stride(), off)
+                g = old_grads[id(p)]
+                if g is not None:
+                    view.copy_(g)
+                p.grad = view
+                b.views.append(view)
+            if self.device.type == "cuda":
+                b.ready_event = torch.cuda.Event()
+                b.done_event = torch.cuda.Event()
+        self._buckets = buckets
+        self._bucket_of = bucket_of
+        arr = (ctypes.c_int * len(bucket_of))(*bucket_of)
+        if self._reducer_id:
+            _lib.call_ret("ptd_reducer_destroy", self._reducer_id)
+        self._reducer_id = _lib.call_ret("ptd_reducer_create", ctypes.cast(arr, ctypes.c_void_p), len(bucket_of),
+                                         n_buckets)
+        if self._reducer_id <= 0:
+            raise RuntimeError("ptd_reducer_create failed")
+        self._view_of = {id(p): v for b in buckets for p, v in zip(b.params, b.views)}
+
+    # ------------------------------------------------------------------ public surface
+    @contextlib.contextmanager
+    def no_sync(self):
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+    def bucket_sizes_bytes(self) -> List[int]:
+        return [b.flat.numel() * b.flat.element_size() for b in self._buckets]
+
+    def forward(self, *inputs, **kwargs):
+        if self.training and torch.is_grad_enabled():
+            self._prepare_iteration()
+        return self.module(*inputs, **kwargs)
+
+    def _prepare_iteration(self) -> None:
+        if self._want_rebuild and not self._rebuilt and self.stats["iterations"] >= 1:
+            # one-time rebuild in the order gradients actually became ready (rank 0's order, like torch)
+            box = [self._last_ready_order]
+            if self.world_size > 1:
+                dist.broadcast_object_list(box, src=0, group=self.process_group)
+            order = box[0]
+            if order is not None and len(order) == len(self._params):
+                if self.device.type == "cuda":
+                    torch.cuda.current_stream(self.device).synchronize()
+                self._build_buckets(order)
+            self._rebuilt = True
+        # gradients dropped by optimizer.zero_grad(set_to_none=True): zero the flat buffers, re-attach views
+        if any(p.grad is None for p in self._params):
+            for b in self._buckets:
+                b.flat.zero_()
+                for p, v in zip(b.params, b.views):
+                    p.grad = v
+        if self.broadcast_buffers and self.world_size > 1 and self.require_backward_grad_sync:
+            with torch.no_grad():
+                for bf in self._buf_flats:
+                    self.backend.broadcast(bf, 0)
+
+    _last_ready_order: Optional[List[int]] = None
+
+    # ------------------------------------------------------------------ backward-time machinery
+    def _grad_ready(self, p: nn.Parameter) -> None:
+        if not self.require_backward_grad_sync:
+            return
+        view = self._view_of[id(p)]
+        g = p.grad
+        if g is not view and (g.data_ptr() != view.data_ptr() or g.stride() != view.stride()):
+            with torch.no_grad():
+                view.copy_(g)
+            p.grad = view
+        self.mark_ready(p)
+
+    def mark_ready(self, p: nn.Parameter) -> None:
+        """Tell the reducer that ``p``'s gradient (already in its bucket view) is final for this backward."""
+        if not self._callback_queued:
+            torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
+            self._callback_queued = True
+        b = _lib.call_ret("ptd_reducer_mark_ready", self._reducer_id, self._index_of[id(p)])
+        if b >= 0:
+            self._launch_bucket(self._buckets[b])
+        elif b < -2:
+            raise RuntimeError(f"reducer error {b}")
+
+    def _launch_bucket(self, b: _Bucket) -> None:
+        b.launched = True
+        self.stats["allreduce_launches"] += 1
+        self.stats["bytes_reduced"] += b.flat.numel() * b.flat.element_size()
+        if self.world_size == 1:
+            return
+        if self._comm_stream is not None:
+            b.ready_event.record(torch.cuda.current_stream(self.device))
+            self._comm_stream.wait_event(b.ready_event)
+            with torch.cuda.stream(self._comm_stream):
+                self.backend.all_reduce_avg(b.flat)
+                b.done_event.record(self._comm_stream)
+        else:
+            self.backend.all_reduce_avg(b.flat)
+
+    def _finalize_backward(self) -> None:
+        self._callback_queued = False
+        if _lib.call_ret("ptd_reducer_all_done", self._reducer_id) != 1:
+            n = len(self._buckets)
+            out = (ctypes.c_int * n)()
+            c = _lib.call_ret("ptd_reducer_incomplete", self._reducer_id, ctypes.cast(out, ctypes.c_void_p), n)
+            _lib.call_ret("ptd_reducer_reset", self._reducer_id)
+            raise RuntimeError(f"{c} gradient bucket(s) did not complete in this backward: some parameter did not "
+                               "receive a gradient (find_unused_parameters is not supported)")
+        if self._comm_stream is not None:
+            cur = torch.cuda.current_stream(self.device)
+            for b in self._buckets:
+                if b.launched and self.world_size > 1:
+                    cur.wait_event(b.done_event)
+        for b in self._buckets:
+            b.launched = False
+        if not self._rebuilt:
+            n = len(self._params)
+            out = (ctypes.c_int * n)()
+            got = _lib.call_ret("ptd_reducer_ready_order", self._reducer_id, ctypes.cast(out, ctypes.c_void_p), n)
+            self._last_ready_order = list(out)[:got] if got == n else None
+        _lib.call_ret("ptd_reducer_reset", self._reducer_id)
+        self.stats["iterations"] += 1
+
+    def __del__(self):
+        try:
+            if getattr(self, "_reducer_id", 0):
+                _lib.call_ret("ptd_reducer_destroy", self._reducer_id)
+        except Exception:  # noqa: BLE001 - interpreter shutdown
+            pass

@@ -1,0 +1,107 @@
+"""``Trainer`` - the training loop of the reference's DDP scripts, plus rank-0 checkpoints.
+
+Same constructor surface and per-epoch behaviour as ``R/02 DDP基本概念/ddp_gpus.py:25-55`` (spawn:
+``Trainer(model, train_dataloader, optimizer, gpu_id)``) and ``ddp_gpus_torchrun.py:21-54``
+(torchrun: ``gpu_id`` read from ``LOCAL_RANK``):
+
+* the model is moved to the device and wrapped in ``DistributedDataParallel``;
+* ``_run_epoch`` peeks one batch to print ``[GPU: r] Epoch: e | Batchsize: b | Steps: n`` (exact
+  format, golden-tested), calls ``sampler.set_epoch(epoch)``, then ``.to(device)`` + ``_run_batch``;
+* ``_run_batch`` = ``zero_grad -> forward -> cross_entropy -> backward -> step``.
+
+Additions (defaults keep the reference behaviour): ``save_every``/``snapshot_path`` write
+``model.module.state_dict()`` from rank 0 (keys without the ``module.`` prefix, so the file loads
+into the reference's own model definitions); ``resume`` reloads it; ``loss_fn`` swaps the loss
+(the reference's float-target cross-entropy on one logit is identically zero - SURVEY.md 2.6 quirk 1).
+"""
+from __future__ import annotations
+
+import os
+from typing import Callable, Optional
+
+import torch
+import torch.distributed as dist
+from torch.utils.data import DataLoader
+
+from ..ops import functional as K
+from ..parallel.ddp import DistributedDataParallel as DDP
+
+
+class Trainer:
+    def __init__(self, model: torch.nn.Module, train_dataloader: DataLoader, optimizer: torch.optim.Optimizer,
+                 gpu_id: Optional[int] = None, *, save_every: int = 0, snapshot_path: str = "snapshot.pt",
+                 loss_fn: Optional[Callable] = None, resume: bool = False, ddp_kwargs: Optional[dict] = None,
+                 quiet: bool = False) -> None:
+        self.gpu_id = int(os.environ.get("LOCAL_RANK", 0)) if gpu_id is None else gpu_id
+        self.device = torch.device("cuda", self.gpu_id) if torch.cuda.is_available() else torch.device("cpu")
+        self.model = model.to(self.device)
+        self.train_dataloader = train_dataloader
+        self.optimizer = optimizer
+        self.save_every = save_every
+        self.snapshot_path = snapshot_path
+        self.loss_fn = loss_fn or K.cross_entropy
+        self.quiet = quiet
+        self.epochs_run = 0
+        self.last_loss: Optional[torch.Tensor] = None
+        if resume and os.path.exists(snapshot_path):
+            self._load_snapshot(snapshot_path)
+        kw = dict(ddp_kwargs or {})
+        self.model = DDP(self.model, device_ids=[self.gpu_id] if self.device.type == "cuda" else None, **kw)
+        if hasattr(optimizer, "attach_model"):
+            optimizer.attach_model(self.model.module)
+
+    # -- one optimisation step ----------------------------------------------------------------
+    def _run_batch(self, xs, ys):
+        self.optimizer.zero_grad()
+        output = self.model(xs)
+        loss = self.loss_fn(output, ys)
+        loss.backward()
+        self.optimizer.step()
+        self.last_loss = loss.detach()
+        return self.last_loss
+
+    def _run_epoch(self, epoch: int):
+        batch_size = len(next(iter(self.train_dataloader))[0])
+        if not self.quiet:
+            print(f"[GPU: {self.gpu_id}] Epoch: {epoch} | Batchsize: {batch_size} | Steps: {len(self.train_dataloader)}",
+                  flush=True)
+        sampler = getattr(self.train_dataloader, "sampler", None)
+        if hasattr(sampler, "set_epoch"):
+            sampler.set_epoch(epoch)
+        for xs, ys in self.train_dataloader:
+            xs = xs.to(self.device, non_blocking=True)
+            ys = ys.to(self.device, non_blocking=True)
+            self._run_batch(xs, ys)
+
+    def train(self, max_epoch: int):
+        for epoch in range(self.epochs_run, max_epoch):
+            self._run_epoch(epoch)
+            if self.save_every and (epoch + 1) % self.save_every == 0:
+                self._save_snapshot(epoch)
+
+    # -- checkpoints ----------------------------------------------------------------------------
+    def _is_rank0(self) -> bool:
+        return (not dist.is_initialized()) or dist.get_rank() == 0
+
+    def _save_snapshot(self, epoch: int) -> None:
+        if self._is_rank0():
+            inner = self.model.module if hasattr(self.model, "module") else self.model
+            state = {k: v.detach().cpu().contiguous() for k, v in inner.state_dict().items()}
+            torch.save({"MODEL_STATE": state, "EPOCHS_RUN": epoch + 1}, self.snapshot_path)
+            if not self.quiet:
+                print(f"Epoch {epoch} | Training snapshot saved at {self.snapshot_path}", flush=True)
+        if dist.is_initialized():
+            dist.barrier()
+
+    def _load_snapshot(self, path: str) -> None:
+        snap = torch.load(path, map_location=self.device)
+        self.model.load_state_dict(snap["MODEL_STATE"])
+        self.epochs_run = int(snap.get("EPOCHS_RUN", 0))
+        if not self.quiet:
+            print(f"[GPU: {self.gpu_id}] Resuming training from snapshot at epoch {self.epochs_run}", flush=True)
+
+
+def save_model_state(model: torch.nn.Module, path: str) -> None:
+    """Plain ``state_dict`` file (no wrapper dict): ``torch.nn.Linear(20,1).load_state_dict(torch.load(path))``."""
+    inner = model.module if hasattr(model, "module") else model
+    torch.save({k: v.detach().cpu().contiguous() for k, v in inner.state_dict().items()}, path)

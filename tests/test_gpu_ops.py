@@ -1,0 +1,263 @@
+"""Numerics of every CUDA op against a plain PyTorch fp32 statement of the same op."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from pytorchdistributed_b200 import _lib
+from pytorchdistributed_b200.ops import functional as K
+
+pytestmark = pytest.mark.gpu
+CL = torch.channels_last
+DEV = "cuda"
+
+
+def _act(n, c, h, w, scale=1.0, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    x = torch.randn(n, c, h, w, generator=g) * scale
+    return x.to(DEV).to(torch.bfloat16).contiguous(memory_format=CL)
+
+
+def _wt(cout, cin, r, seed=1):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    w = torch.randn(cout, cin, r, r, generator=g) * (2.0 / (cin * r * r)) ** 0.5
+    return w.to(DEV).to(torch.bfloat16).contiguous(memory_format=CL)
+
+
+def _rel(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / (b.norm() + 1e-12)).item()
+
+
+def test_library_loaded():
+    assert _lib.available(), _lib.load_error()
+    assert _lib.call_ret("ptd_version") >= 100
+
+
+CONV_CASES = [
+    # n, cin, cout, h, r, stride, pad
+    (2, 64, 64, 16, 1, 1, 0),
+    (2, 64, 256, 16, 1, 1, 0),
+    (3, 256, 64, 14, 1, 1, 0),
+    (2, 64, 64, 16, 3, 1, 1),
+    (2, 128, 128, 16, 3, 2, 1),
+    (2, 256, 512, 14, 1, 2, 0),
+    (5, 512, 512, 7, 3, 1, 1),
+    (4, 1024, 2048, 7, 1, 1, 0),
+    (1, 2048, 512, 7, 1, 1, 0),
+    (2, 256, 256, 14, 3, 1, 1),
+]
+
+
+@pytest.mark.parametrize("n,cin,cout,h,r,stride,pad", CONV_CASES)
+def test_conv_fprop(n, cin, cout, h, r, stride, pad):
+    x, w = _act(n, cin, h, h), _wt(cout, cin, r)
+    y, stats = K.conv_fprop_raw(x, w, stride, pad, True)
+    ref = F.conv2d(x.float(), w.float(), None, stride, pad)
+    assert _rel(y, ref) < 1e-2
+    assert _rel(stats[0], ref.sum((0, 2, 3))) < 1e-2 or (stats[0] - ref.sum((0, 2, 3))).abs().max() < 0.5
+    assert _rel(stats[1], (ref * ref).sum((0, 2, 3))) < 1e-2
+
+
+@pytest.mark.parametrize("n,cin,cout,h,r,stride,pad", CONV_CASES)
+def test_conv_dgrad(n, cin, cout, h, r, stride, pad):
+    x, w = _act(n, cin, h, h), _wt(cout, cin, r)
+    oh = (h + 2 * pad - r) // stride + 1
+    dy = _act(n, cout, oh, oh, seed=3)
+    dx = K.conv_dgrad_raw(dy, w, x.shape, stride, pad)
+    ref = torch.nn.grad.conv2d_input(x.shape, w.float(), dy.float(), stride, pad)
+    assert _rel(dx, ref) < 1e-2
+    add = _act(n, cin, h, h, seed=5)
+    dx2 = K.conv_dgrad_raw(dy, w, x.shape, stride, pad, addend=add)
+    assert _rel(dx2, ref + add.float()) < 1e-2
+
+
+@pytest.mark.parametrize("n,cin,cout,h,r,stride,pad", CONV_CASES)
+def test_conv_wgrad(n, cin, cout, h, r, stride, pad):
+    x, w = _act(n, cin, h, h), _wt(cout, cin, r)
+    oh = (h + 2 * pad - r) // stride + 1
+    dy = _act(n, cout, oh, oh, seed=3)
+    dw = K.conv_wgrad_raw(x, dy, w.shape, stride, pad)
+    ref = torch.nn.grad.conv2d_weight(x.float(), w.shape, dy.float(), stride, pad)
+    assert _rel(dw, ref) < 1e-2
+
+
+def test_conv_large_m_multi_tile():
+    # more tiles than SMs, exercises the persistent loop / TMEM double buffering
+    x, w = _act(32, 64, 56, 56), _wt(128, 64, 1)
+    y, stats = K.conv_fprop_raw(x, w, 1, 0, True)
+    ref = F.conv2d(x.float(), w.float())
+    assert _rel(y, ref) < 1e-2
+    assert _rel(stats[1], (ref * ref).sum((0, 2, 3))) < 1e-2
+    x, w = _act(16, 64, 56, 56), _wt(64, 64, 3)
+    y, _ = K.conv_fprop_raw(x, w, 1, 1, True)
+    assert _rel(y, F.conv2d(x.float(), w.float(), None, 1, 1)) < 1e-2
+
+
+def test_stem():
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(4, 3, 64, 64, generator=g).to(DEV)
+    w = (torch.randn(64, 3, 7, 7, generator=g) * 0.1).to(DEV).contiguous(memory_format=CL)
+    x4 = K.to_nhwc4(x)
+    assert torch.equal(x4[:, :3].float(), x.to(torch.bfloat16).float())
+    w4 = K.stem_pack(w)
+    y, stats = K.stem_fprop_raw(x4, w4)
+    ref = F.conv2d(x.to(torch.bfloat16).float(), w.to(torch.bfloat16).float(), None, 2, 3)
+    assert _rel(y, ref) < 1e-2
+    assert _rel(stats[1], (ref * ref).sum((0, 2, 3))) < 1e-2
+    dy = _act(4, 64, 32, 32, seed=7)
+    dw = K.stem_wgrad_raw(x4, dy, w.shape)
+    refw = torch.nn.grad.conv2d_weight(x.to(torch.bfloat16).float(), w.shape, dy.float(), 2, 3)
+    assert _rel(dw, refw) < 1e-2
+
+
+@pytest.mark.parametrize("m,n,k", [(256, 1000, 2048), (120, 1000, 2048), (7, 16, 64), (300, 72, 128)])
+def test_linear(m, n, k):
+    g = torch.Generator().manual_seed(0)
+    a = torch.randn(m, k, generator=g).to(DEV).to(torch.bfloat16)
+    w = (torch.randn(n, k, generator=g) / k ** 0.5).to(DEV).to(torch.bfloat16)
+    b = torch.randn(n, generator=g).to(DEV)
+    out = torch.empty(m, n, device=DEV)
+    _lib.call("ptd_linear_fwd", a, w, b, out, m, n, k, K._stream())
+    assert _rel(out, a.float() @ w.float().t() + b) < 1e-2
+    d = torch.randn(m, n, generator=g).to(DEV).to(torch.bfloat16)
+    da = torch.empty(m, k, device=DEV, dtype=torch.bfloat16)
+    _lib.call("ptd_linear_dgrad", d, w, da, m, n, k, K._stream())
+    assert _rel(da, d.float() @ w.float()) < 1e-2
+    dw = torch.zeros(n, k, device=DEV)
+    _lib.call("ptd_linear_wgrad", a, d, dw, m, n, k, K._stream())
+    assert _rel(dw, d.float().t() @ a.float()) < 1e-2
+
+
+@pytest.mark.parametrize("c,relu,res", [(64, True, False), (256, True, True), (2048, False, False), (512, False, True)])
+def test_bn_forward_backward(c, relu, res):
+    n, h = 4, 9
+    y = _act(n, c, h, h, scale=2.0)
+    r = _act(n, c, h, h, seed=9) if res else None
+    gamma = (torch.rand(c, device=DEV) + 0.5).requires_grad_()
+    beta = (torch.randn(c, device=DEV) * 0.1).requires_grad_()
+    rm, rv = torch.zeros(c, device=DEV), torch.ones(c, device=DEV)
+    rm2, rv2 = rm.clone(), rv.clone()
+    y1 = y.clone().requires_grad_()
+    r1 = r.clone().requires_grad_() if res else None
+    z = K.batch_norm_act(y1, gamma, beta, rm, rv, r1, 1e-5, 0.1, relu)
+    yf = y.float().requires_grad_()
+    rf = r.float().requires_grad_() if res else None
+    g2, b2 = gamma.detach().clone().requires_grad_(), beta.detach().clone().requires_grad_()
+    zr = F.batch_norm(yf, rm2, rv2, g2, b2, True, 0.1, 1e-5)
+    if res:
+        zr = zr + rf
+    if relu:
+        zr = F.relu(zr)
+    assert _rel(z, zr) < 1e-2
+    assert _rel(rm, rm2) < 1e-3 and _rel(rv, rv2) < 1e-3
+    dz = _act(n, c, h, h, seed=11)
+    z.backward(dz)
+    zr.backward(dz.float())
+    assert _rel(y1.grad, yf.grad) < 2e-2
+    assert _rel(gamma.grad, g2.grad) < 2e-2 and _rel(beta.grad, b2.grad) < 2e-2
+    if res:
+        assert _rel(r1.grad, rf.grad) < 1e-2
+
+
+def test_conv_bn_act_fused_matches_unfused():
+    x, c = _act(4, 64, 16, 16), 128
+    w = _wt(c, 64, 3).float().contiguous(memory_format=CL).requires_grad_()
+    gamma, beta = torch.ones(c, device=DEV, requires_grad=True), torch.zeros(c, device=DEV, requires_grad=True)
+    rm, rv = torch.zeros(c, device=DEV), torch.ones(c, device=DEV)
+    x1 = x.clone().requires_grad_()
+    z = K.conv_bn_act(x1, w, w.detach().to(torch.bfloat16).contiguous(memory_format=CL), gamma, beta, rm, rv, None,
+                      1, 1, 1e-5, 0.1, True)
+    xf = x.float().requires_grad_()
+    wf = w.detach().to(torch.bfloat16).float().requires_grad_()
+    zr = F.relu(F.batch_norm(F.conv2d(xf, wf, None, 1, 1), None, None, torch.ones(c, device=DEV),
+                             torch.zeros(c, device=DEV), True))
+    assert _rel(z, zr) < 1e-2
+    dz = _act(4, c, 16, 16, seed=4)
+    z.backward(dz)
+    zr.backward(dz.float())
+    assert _rel(x1.grad, xf.grad) < 3e-2
+    assert _rel(w.grad, wf.grad) < 3e-2
+
+
+def test_pools():
+    x = _act(3, 64, 17, 17).requires_grad_()
+    y = K.max_pool_3x3_s2(x)
+    xf = x.detach().float().requires_grad_()
+    yr = F.max_pool2d(xf, 3, 2, 1)
+    assert torch.equal(y.float(), yr)
+    dy = _act(*y.shape, seed=2)
+    y.backward(dy)
+    yr.backward(dy.float())
+    assert _rel(x.grad, xf.grad) < 1e-2
+    # post-ReLU input (many exact ties at zero) must route gradients like torch (first max wins)
+    x0 = torch.relu(_act(2, 64, 12, 12, seed=5)).requires_grad_()
+    y0 = K.max_pool_3x3_s2(x0)
+    x0f = x0.detach().float().requires_grad_()
+    y0r = F.max_pool2d(x0f, 3, 2, 1)
+    d0 = _act(*y0.shape, seed=6)
+    y0.backward(d0)
+    y0r.backward(d0.float())
+    assert _rel(x0.grad, x0f.grad) < 1e-2
+    a = _act(5, 2048, 7, 7).requires_grad_()
+    p = K.global_avg_pool(a)
+    assert _rel(p, a.float().mean((2, 3))) < 1e-2
+    dp = torch.randn(5, 2048, device=DEV)
+    p.backward(dp.to(torch.bfloat16))
+    assert _rel(a.grad, (dp / 49)[:, :, None, None].expand(5, 2048, 7, 7)) < 1e-2
+
+
+def test_cross_entropy_index_and_soft():
+    g = torch.Generator().manual_seed(0)
+    logits = (torch.randn(37, 1000, generator=g) * 3).to(DEV).requires_grad_()
+    idx = torch.randint(0, 1000, (37,), generator=g).to(DEV)
+    loss = K.cross_entropy(logits, idx)
+    lf = logits.detach().clone().requires_grad_()
+    lr = F.cross_entropy(lf, idx)
+    assert abs(loss.item() - lr.item()) < 1e-4 * max(1, abs(lr.item()))
+    loss.backward(); lr.backward()
+    assert _rel(logits.grad, lf.grad) < 1e-4
+    soft = torch.softmax(torch.randn(37, 1000, generator=g), 1).to(DEV)
+    l2 = logits.detach().clone().requires_grad_()
+    l3 = logits.detach().clone().requires_grad_()
+    a, b = K.cross_entropy(l2, soft), F.cross_entropy(l3, soft)
+    assert abs(a.item() - b.item()) < 1e-4 * max(1, abs(b.item()))
+    a.backward(); b.backward()
+    assert _rel(l2.grad, l3.grad) < 1e-4
+    # the reference's degenerate toy loss: one class, float target -> exactly zero loss and gradient
+    out = torch.randn(32, 1, device=DEV, requires_grad=True)
+    z = K.cross_entropy(out, torch.rand(32, 1, device=DEV))
+    z.backward()
+    assert z.item() == 0.0 and out.grad.abs().max().item() == 0.0
+
+
+def test_small_linear_and_mlp():
+    from pytorchdistributed_b200.models import MLP, ToyLinear
+    torch.manual_seed(0)
+    m = ToyLinear().to(DEV)
+    x = torch.rand(32, 20, device=DEV, requires_grad=True)
+    y = m(x)
+    ref = F.linear(x.detach(), m.weight.detach(), m.bias.detach())
+    assert torch.allclose(y, ref, atol=1e-5)
+    (y ** 2).sum().backward()
+    xr = x.detach().clone().requires_grad_()
+    wr, br = m.weight.detach().clone().requires_grad_(), m.bias.detach().clone().requires_grad_()
+    (F.linear(xr, wr, br) ** 2).sum().backward()
+    assert torch.allclose(x.grad, xr.grad, atol=1e-4)
+    assert torch.allclose(m.weight.grad, wr.grad, atol=1e-3) and torch.allclose(m.bias.grad, br.grad, atol=1e-3)
+    mlp = MLP().to(DEV)
+    xi = torch.randn(32, 10, device=DEV)
+    with torch.no_grad():
+        fused = mlp(xi)
+    cpu = MLP()
+    cpu.load_state_dict(mlp.state_dict())
+    assert torch.allclose(fused.cpu(), cpu(xi.cpu()), atol=1e-5)
+    assert torch.allclose(mlp(xi).detach().cpu(), cpu(xi.cpu()).detach(), atol=1e-5)   # autograd path
+
+
+def test_layout_roundtrip():
+    x = torch.randn(3, 70, 9, 11, device=DEV)
+    y = K.as_nhwc_bf16(x)
+    assert y.is_contiguous(memory_format=CL) and torch.equal(y.float(), x.to(torch.bfloat16).float())
+    back = torch.empty_like(x)
+    _lib.call("ptd_nhwc_bf16_to_nchw_f32", y, back, 3, 70, 99, K._stream())
+    assert torch.equal(back, y.float())
