@@ -62,7 +62,7 @@ softmax_ce_kernel(const float* __restrict__ logits, const float* __restrict__ so
     long long ti = 0;
     if (SOFT) {
         sum_t = tot[1];
-        loss = lse * sum_t - tot[2];
+        loss = __fmul_rn(lse, sum_t) - tot[2];      // no FMA: x*t - t*x must cancel exactly (one-class toy loss)
     } else {
         ti = idx_t[row];
         sum_t = 1.f;

@@ -1,0 +1,357 @@
+// Peer-to-peer runtime and collective kernels over NVLink 5 / NVSwitch.
+//
+// Every rank owns a "symmetric" buffer (cudaMalloc, exported with CUDA IPC, mapped by every peer) and a
+// signal pad.  Collectives are single kernels that read and write peers' buffers with plain
+// ld/st.global on the mapped pointers and synchronise ranks with sequence-numbered flags
+// (st.release.sys / ld.acquire.sys) - there is no NCCL call anywhere in this file.
+//
+//   all-reduce (average), in place, "two-shot": rank r owns slice r of the buffer; for each 16-byte
+//   element of its slice it loads the element from all N buffers, adds in fp32, applies the 1/N (or any)
+//   scale and stores the result into all N buffers.  Per GPU that moves (N-1)/N of the buffer in each
+//   direction - the bandwidth-optimal volume - and needs two flag barriers (inputs ready / outputs
+//   complete).  The flatten step of DDP is free (gradients already live in the buffer), the averaging
+//   and the optional bf16 storage format are fused into the same pass.
+//   broadcast: non-root ranks pull the root's buffer.    reduce-to-root / peer copy: used by the
+//   single-process DataParallel wrapper (replicate, gather, gradient reduction).
+//
+// Replaces what the reference reaches through NCCL: DDP's bucket all-reduce and parameter/buffer
+// broadcast (R/02 DDP基本概念/ddp_gpus.py:35,41) and nn.DataParallel's
+// broadcast_coalesced / gather / reduce_add_coalesced (R/01 数据并行/...ipynb#cell5-6; K6-K9).
+#include "common.cuh"
+#include "ptdb200.h"
+
+namespace {
+
+constexpr int MAX_WORLD = 8;
+constexpr int MAX_BLOCKS = 128;
+constexpr int AR_THREADS = 512;
+
+struct PeerPtrs {
+    void* buf[MAX_WORLD];
+    uint32_t* pad[MAX_WORLD];
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// Block-level barrier across ranks: block b of every rank meets block b of every other rank.
+// Flags only grow (seq is a host-side counter shared by construction), so a late waiter still passes.
+__device__ __forceinline__ void rank_barrier(const PeerPtrs& pp, int rank, int world, uint32_t seq) {
+    __syncthreads();
+    if ((int)threadIdx.x < world) {
+        const int peer = threadIdx.x;
+        __threadfence_system();
+        st_release_sys(pp.pad[peer] + blockIdx.x * MAX_WORLD + rank, seq);
+        const uint32_t* mine = pp.pad[rank] + blockIdx.x * MAX_WORLD + peer;
+        const unsigned long long t0 = global_timer_ns();
+        while ((int32_t)(ld_acquire_sys(mine) - seq) < 0) {
+            if (global_timer_ns() - t0 > 20ull * 1000 * 1000 * 1000) {      // 20 s: a peer died; do not hang the GPU
+                printf("ptd: rank %d block %d timed out waiting for rank %d (seq %u)\n", rank, blockIdx.x, peer, seq);
+                __trap();
+            }
+        }
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float4 ld_f4(const float4* p) {
+    float4 v;
+    asm volatile("ld.global.relaxed.sys.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_f4(float4* p, const float4& v) {
+    asm volatile("st.global.relaxed.sys.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 ld_u4(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.global.relaxed.sys.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_u4(uint4* p, const uint4& v) {
+    asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// ---- two-shot all-reduce, fp32 storage ------------------------------------------------------------
+// n4 = number of float4 elements (buffer length is padded to a multiple of 4 floats by the caller).
+template <int WORLD>
+__global__ void __launch_bounds__(AR_THREADS) allreduce_f32_kernel(PeerPtrs pp, int rank, long long n4, float scale,
+                                                                   uint32_t seq) {
+    rank_barrier(pp, rank, WORLD, seq);
+    const long long per = (n4 + WORLD - 1) / WORLD;
+    const long long begin = min(n4, per * rank), end = min(n4, begin + per);
+    const long long stride = (long long)gridDim.x * AR_THREADS;
+    constexpr int UNROLL = 4;
+    long long i = begin + (long long)blockIdx.x * AR_THREADS + threadIdx.x;
+    for (; i + (UNROLL - 1) * stride < end; i += UNROLL * stride) {
+        float4 acc[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r) {
+            const int src = (rank + r) % WORLD;        // start at the local copy, spread peers over time
+            float4 v[UNROLL];
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) v[u] = ld_f4(reinterpret_cast<const float4*>(pp.buf[src]) + i + u * stride);
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) { acc[u].x += v[u].x; acc[u].y += v[u].y; acc[u].z += v[u].z; acc[u].w += v[u].w; }
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) { acc[u].x *= scale; acc[u].y *= scale; acc[u].z *= scale; acc[u].w *= scale; }
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r) {
+            const int dst = (rank + r) % WORLD;
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) st_f4(reinterpret_cast<float4*>(pp.buf[dst]) + i + u * stride, acc[u]);
+        }
+    }
+    for (; i < end; i += stride) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r) {
+            const float4 v = ld_f4(reinterpret_cast<const float4*>(pp.buf[(rank + r) % WORLD]) + i);
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+        acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r) st_f4(reinterpret_cast<float4*>(pp.buf[(rank + r) % WORLD]) + i, acc);
+    }
+    rank_barrier(pp, rank, WORLD, seq + 1);
+}
+
+// ---- two-shot all-reduce, bf16 storage (fp32 accumulate) -----------------------------------------------
+template <int WORLD>
+__global__ void __launch_bounds__(AR_THREADS) allreduce_bf16_kernel(PeerPtrs pp, int rank, long long n8, float scale,
+                                                                    uint32_t seq) {
+    rank_barrier(pp, rank, WORLD, seq);
+    const long long per = (n8 + WORLD - 1) / WORLD;
+    const long long begin = min(n8, per * rank), end = min(n8, begin + per);
+    const long long stride = (long long)gridDim.x * AR_THREADS;
+    for (long long i = begin + (long long)blockIdx.x * AR_THREADS + threadIdx.x; i < end; i += stride) {
+        float acc[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+        uint4 v[WORLD];
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r) v[r] = ld_u4(reinterpret_cast<const uint4*>(pp.buf[(rank + r) % WORLD]) + i);
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r) {
+            const uint32_t w[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float2 f = unpack_bf16x2(w[k]);
+                acc[2 * k] += f.x;
+                acc[2 * k + 1] += f.y;
+            }
+        }
+        uint4 o;
+        o.x = pack_bf16x2(acc[0] * scale, acc[1] * scale);
+        o.y = pack_bf16x2(acc[2] * scale, acc[3] * scale);
+        o.z = pack_bf16x2(acc[4] * scale, acc[5] * scale);
+        o.w = pack_bf16x2(acc[6] * scale, acc[7] * scale);
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r) st_u4(reinterpret_cast<uint4*>(pp.buf[(rank + r) % WORLD]) + i, o);
+    }
+    rank_barrier(pp, rank, WORLD, seq + 1);
+}
+
+// ---- broadcast: every non-root rank pulls the root's buffer ----------------------------------------------
+__global__ void __launch_bounds__(AR_THREADS) broadcast_pull_kernel(PeerPtrs pp, int rank, int world, int root,
+                                                                    long long n16, uint32_t seq) {
+    rank_barrier(pp, rank, world, seq);                 // root's data is final
+    if (rank != root) {
+        const uint4* src = reinterpret_cast<const uint4*>(pp.buf[root]);
+        uint4* dst = reinterpret_cast<uint4*>(pp.buf[rank]);
+        const long long stride = (long long)gridDim.x * AR_THREADS;
+        long long i = (long long)blockIdx.x * AR_THREADS + threadIdx.x;
+        for (; i + 3 * stride < n16; i += 4 * stride) {
+            uint4 v0 = ld_u4(src + i), v1 = ld_u4(src + i + stride), v2 = ld_u4(src + i + 2 * stride), v3 = ld_u4(src + i + 3 * stride);
+            dst[i] = v0; dst[i + stride] = v1; dst[i + 2 * stride] = v2; dst[i + 3 * stride] = v3;
+        }
+        for (; i < n16; i += stride) dst[i] = ld_u4(src + i);
+    }
+    rank_barrier(pp, rank, world, seq + 1);             // root may overwrite its buffer again
+}
+
+__global__ void __launch_bounds__(AR_THREADS) barrier_only_kernel(PeerPtrs pp, int rank, int world, uint32_t seq) {
+    rank_barrier(pp, rank, world, seq);
+}
+
+// ---- single-process helpers (DataParallel): device-issued copies / reductions over peer pointers ----------
+__global__ void __launch_bounds__(256) peer_copy_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src,
+                                                        long long n16, const uint8_t* src_tail, uint8_t* dst_tail,
+                                                        int tail) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < n16; i += 4 * stride) {
+        uint4 v0 = src[i], v1 = src[i + stride], v2 = src[i + 2 * stride], v3 = src[i + 3 * stride];
+        dst[i] = v0; dst[i + stride] = v1; dst[i + 2 * stride] = v2; dst[i + 3 * stride] = v3;
+    }
+    for (; i < n16; i += stride) dst[i] = src[i];
+    if (blockIdx.x == 0 && (int)threadIdx.x < tail) dst_tail[threadIdx.x] = src_tail[threadIdx.x];
+}
+
+struct SrcList {
+    const float* p[MAX_WORLD];
+};
+// dst[i] = scale * (beta*dst[i] + sum_k src_k[i])
+__global__ void __launch_bounds__(256) reduce_sum_kernel(float* __restrict__ dst, SrcList srcs, int n_src, long long n,
+                                                         float scale, int accumulate) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        float acc = accumulate ? dst[i] : 0.f;
+        for (int k = 0; k < n_src; ++k) acc += srcs.p[k][i];
+        dst[i] = acc * scale;
+    }
+}
+
+int pick_blocks(long long work_items, int requested) {
+    if (requested > 0) return requested > MAX_BLOCKS ? MAX_BLOCKS : requested;
+    long long b = (work_items + AR_THREADS * 4 - 1) / (AR_THREADS * 4);
+    if (b < 1) b = 1;
+    if (b > 64) b = 64;      // enough loads in flight to fill NVLink; leaves the other SMs to backward
+    return (int)b;
+}
+
+int fill_peers(PeerPtrs& pp, const void* const* bufs, const void* const* pads, int world) {
+    if (world < 1 || world > MAX_WORLD) {
+        ptd_set_error("p2p: world size %d outside [1,%d]", world, MAX_WORLD);
+        return PTD_ERR_ARG;
+    }
+    for (int r = 0; r < MAX_WORLD; ++r) {
+        pp.buf[r] = r < world ? const_cast<void*>(bufs[r]) : nullptr;
+        pp.pad[r] = r < world ? (uint32_t*)const_cast<void*>(pads[r]) : nullptr;
+    }
+    return PTD_OK;
+}
+
+}  // namespace
+
+// ---- memory / IPC -------------------------------------------------------------------------------------------
+extern "C" int ptd_p2p_malloc(long long bytes, void** out) {
+    PTD_CUDA_CHECK(cudaMalloc(out, (size_t)bytes));
+    PTD_CUDA_CHECK(cudaMemset(*out, 0, (size_t)bytes));
+    return PTD_OK;
+}
+extern "C" int ptd_p2p_free(void* p) {
+    PTD_CUDA_CHECK(cudaFree(p));
+    return PTD_OK;
+}
+extern "C" int ptd_p2p_ipc_handle_size() { return (int)sizeof(cudaIpcMemHandle_t); }
+extern "C" int ptd_p2p_ipc_get(void* p, void* handle_out) {
+    cudaIpcMemHandle_t h;
+    PTD_CUDA_CHECK(cudaIpcGetMemHandle(&h, p));
+    memcpy(handle_out, &h, sizeof(h));
+    return PTD_OK;
+}
+extern "C" int ptd_p2p_ipc_open(const void* handle, void** out) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, sizeof(h));
+    PTD_CUDA_CHECK(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+    return PTD_OK;
+}
+extern "C" int ptd_p2p_ipc_close(void* p) {
+    PTD_CUDA_CHECK(cudaIpcCloseMemHandle(p));
+    return PTD_OK;
+}
+// Single process, several devices: make `peer` memory addressable from kernels running on `dev`.
+extern "C" int ptd_p2p_enable_peer_access(int dev, int peer) {
+    int can = 0;
+    PTD_CUDA_CHECK(cudaDeviceCanAccessPeer(&can, dev, peer));
+    PTD_REQUIRE(can, "device %d cannot access device %d", dev, peer);
+    int cur = 0;
+    PTD_CUDA_CHECK(cudaGetDevice(&cur));
+    PTD_CUDA_CHECK(cudaSetDevice(dev));
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+    cudaSetDevice(cur);
+    PTD_CUDA_CHECK(e);
+    return PTD_OK;
+}
+extern "C" int ptd_p2p_pad_bytes() { return MAX_BLOCKS * MAX_WORLD * (int)sizeof(uint32_t); }
+extern "C" int ptd_p2p_max_blocks() { return MAX_BLOCKS; }
+
+// ---- collectives --------------------------------------------------------------------------------------------
+// bufs / pads: HOST arrays of `world` device pointers (this rank's mapping of every rank's buffer / signal pad).
+// `seq` must be the same on every rank and grow by 2 per call on a given signal pad.
+extern "C" int ptd_allreduce_inplace(const void* const* bufs, const void* const* pads, int rank, int world,
+                                     long long numel, int is_bf16, float scale, unsigned seq, int blocks, void* stream) {
+    PeerPtrs pp;
+    int rc = fill_peers(pp, bufs, pads, world);
+    if (rc) return rc;
+    const int per_vec = is_bf16 ? 8 : 4;
+    PTD_REQUIRE(numel % per_vec == 0, "allreduce: numel (%lld) must be a multiple of %d", numel, per_vec);
+    const long long nvec = numel / per_vec;
+    const int grid = pick_blocks((nvec + world - 1) / world, blocks);
+    cudaStream_t st = (cudaStream_t)stream;
+#define PTD_AR(W)                                                                                   \
+    case W:                                                                                         \
+        if (is_bf16) allreduce_bf16_kernel<W><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale, seq); \
+        else allreduce_f32_kernel<W><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale, seq);      \
+        break;
+    switch (world) {
+        PTD_AR(1) PTD_AR(2) PTD_AR(3) PTD_AR(4) PTD_AR(5) PTD_AR(6) PTD_AR(7) PTD_AR(8)
+    }
+#undef PTD_AR
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+extern "C" int ptd_broadcast_inplace(const void* const* bufs, const void* const* pads, int rank, int world, int root,
+                                     long long nbytes, unsigned seq, int blocks, void* stream) {
+    PeerPtrs pp;
+    int rc = fill_peers(pp, bufs, pads, world);
+    if (rc) return rc;
+    PTD_REQUIRE(nbytes % 16 == 0, "broadcast: nbytes (%lld) must be a multiple of 16", nbytes);
+    const int grid = pick_blocks(nbytes / 16, blocks);
+    broadcast_pull_kernel<<<grid, AR_THREADS, 0, (cudaStream_t)stream>>>(pp, rank, world, root, nbytes / 16, seq);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+extern "C" int ptd_p2p_barrier(const void* const* pads, int rank, int world, unsigned seq, void* stream) {
+    PeerPtrs pp;
+    const void* none[MAX_WORLD] = {nullptr};
+    int rc = fill_peers(pp, none, pads, world);
+    if (rc) return rc;
+    barrier_only_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pp, rank, world, seq);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+extern "C" int ptd_peer_copy(void* dst, const void* src, long long nbytes, void* stream) {
+    PTD_REQUIRE(((uintptr_t)dst & 15) == 0 && ((uintptr_t)src & 15) == 0, "peer_copy: pointers must be 16-byte aligned");
+    const long long n16 = nbytes / 16;
+    const int tail = (int)(nbytes - n16 * 16);
+    long long blocks = (n16 + 256 * 4 - 1) / (256 * 4);
+    if (blocks < 1) blocks = 1;
+    if (blocks > 4LL * ptd_num_sms()) blocks = 4LL * ptd_num_sms();
+    peer_copy_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((uint4*)dst, (const uint4*)src, n16,
+                                                                    (const uint8_t*)src + n16 * 16,
+                                                                    (uint8_t*)dst + n16 * 16, tail);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+extern "C" int ptd_reduce_sum_f32(float* dst, const void* const* srcs, int n_src, long long numel, float scale,
+                                  int accumulate, void* stream) {
+    PTD_REQUIRE(n_src >= 0 && n_src <= MAX_WORLD, "reduce_sum: %d sources (max %d)", n_src, MAX_WORLD);
+    SrcList sl;
+    for (int k = 0; k < MAX_WORLD; ++k) sl.p[k] = k < n_src ? (const float*)srcs[k] : nullptr;
+    long long blocks = (numel + 255) / 256;
+    if (blocks < 1) blocks = 1;
+    if (blocks > 4LL * ptd_num_sms()) blocks = 4LL * ptd_num_sms();
+    reduce_sum_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(dst, sl, n_src, numel, scale, accumulate);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}

@@ -126,8 +126,13 @@ def stream_ptr(device: Optional[torch.device] = None) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 
 
+LAUNCHES = 0   # entry-point calls that launch device work (bench.py reports it as gpu_launches)
+
+
 def call(name: str, *args: Any) -> None:
+    global LAUNCHES
     lib = require()
+    LAUNCHES += 1
     rc = getattr(lib, name)(*[_conv(a) for a in args])
     if rc != 0:
         msg = lib.ptd_last_error()

@@ -1,0 +1,3 @@
+from .clocks import ClockSampler
+
+__all__ = ["ClockSampler"]
