@@ -152,17 +152,35 @@ bn_bwd_reduce_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ z, co
     for (int i = 0; i < 8; ++i) { mu[i] = mean[g * 8 + i]; is[i] = invstd[g * 8 + i]; s[i] = q[i] = 0.f; }
     long long row = (long long)blockIdx.x * rows_per_iter + threadIdx.x / cg;
     const long long row_step = (long long)gridDim.x * rows_per_iter;
-    for (; row < M; row += row_step) {
-        const size_t off = (size_t)row * C + g * 8;
-        float d[8], a[8], x[8];
-        unpack8(*reinterpret_cast<const uint4*>(dz + off), d);
-        unpack8(*reinterpret_cast<const uint4*>(y + off), x);
-        if (RELU) unpack8(*reinterpret_cast<const uint4*>(z + off), a);
+    constexpr int U = 4;                      // rows in flight per thread (independent 16-byte loads)
+    for (; row < M; row += U * row_step) {
+        uint4 rd[U], rx[U], ra[U];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const float gi = (RELU && !(a[i] > 0.f)) ? 0.f : d[i];
-            s[i] += gi;
-            q[i] += gi * (x[i] - mu[i]) * is[i];
+        for (int u = 0; u < U; ++u) {
+            const long long ru = row + u * row_step;
+            if (ru < M) {
+                const size_t off = (size_t)ru * C + g * 8;
+                rd[u] = *reinterpret_cast<const uint4*>(dz + off);
+                rx[u] = *reinterpret_cast<const uint4*>(y + off);
+                if (RELU) ra[u] = *reinterpret_cast<const uint4*>(z + off);
+            } else {
+                rd[u] = make_uint4(0, 0, 0, 0);
+                rx[u] = make_uint4(0, 0, 0, 0);
+                ra[u] = make_uint4(0, 0, 0, 0);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float d[8], a[8], x[8];
+            unpack8(rd[u], d);
+            unpack8(rx[u], x);
+            if (RELU) unpack8(ra[u], a);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float gi = (RELU && !(a[i] > 0.f)) ? 0.f : d[i];
+                s[i] += gi;
+                q[i] += gi * (x[i] - mu[i]) * is[i];
+            }
         }
     }
     __shared__ float red[2][BN_THREADS][8];

@@ -128,6 +128,11 @@ __device__ __forceinline__ void cp_async_8(uint32_t dst, const void* src, uint32
                  : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+// Arrive on `bar` once every cp.async issued so far by this thread has landed (counts as one of the
+// barrier's expected arrivals).  The producer never waits for its own copies.
+__device__ __forceinline__ void cp_async_mbar_arrive_noinc(uint64_t* bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 template <int N>
 __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");

@@ -77,70 +77,93 @@ struct alignas(64) WParams {
 // ------------------------------------------------------------------------------------------
 // Gather producers
 // ------------------------------------------------------------------------------------------
-struct RowCtx {
-    int n, oh, ow;
-    bool valid;
+// A gather thread owns NR rows of the tile and the same 16-byte column in each of them: lanes
+// 8k..8k+7 of a warp cover one contiguous 128-byte row segment, so one warp-level cp.async touches
+// 4 full cache lines.
+template <int NR>
+struct RowSet {
+    int nbase[NR];   // element offset of the row's image inside the source tensor
+    int hw[NR];      // (hi0 << 16) | (wi0 & 0xffff): tap-independent part of the source coordinate
 };
 
-__device__ __forceinline__ RowCtx decode_row(const ConvGeom& g, long long row, long long nrows) {
-    RowCtx rc;
-    rc.valid = row < nrows;
-    long long r = rc.valid ? row : 0;
-    int hw = g.OH * g.OW;
-    rc.n = (int)(r / hw);
-    int rem = (int)(r - (long long)rc.n * hw);
-    rc.oh = rem / g.OW;
-    rc.ow = rem - rc.oh * g.OW;
-    return rc;
-}
+__device__ __forceinline__ int pack_hw(int hi0, int wi0) { return (hi0 << 16) | (wi0 & 0xffff); }
 
-// One 128-byte row segment (chunks [c_begin, c_end) of 16 B) of k-block (tap, cb) for row context rc.
-__device__ __forceinline__ void gather_row_16B(const ConvGeom& g, const RowCtx& rc, int tap, int cb, uint32_t dst_row,
-                                               int row_in_tile, int c_begin, int c_end) {
-    int r = tap / g.S;
-    int s = tap - r * g.S;
-    int hi, wi;
-    bool ok = rc.valid;
-    if (g.mode == GM_FPROP) {
-        hi = rc.oh * g.stride - g.pad + r;
-        wi = rc.ow * g.stride - g.pad + s;
-        ok = ok && hi >= 0 && hi < g.H && wi >= 0 && wi < g.W;
-    } else {
-        int th = rc.oh + g.pad - r;
-        int tw = rc.ow + g.pad - s;
-        ok = ok && th >= 0 && tw >= 0;
-        hi = th / g.stride;
-        wi = tw / g.stride;
-        ok = ok && hi * g.stride == th && wi * g.stride == tw && hi < g.H && wi < g.W;
-    }
-    const bf16* src = g.src;
-    if (ok) src += ((size_t)((size_t)rc.n * g.H + hi) * g.W + wi) * g.C + (size_t)cb * 64;
-    const uint32_t nbytes = ok ? 16u : 0u;
-    const int sw = row_in_tile & 7;
+// Rows first_row + i*ROW_STEP, i < NR.  One division pair for the first row, the rest by stepping.
+template <int NR, int ROW_STEP>
+__device__ __forceinline__ void rowset_decode(const ConvGeom& g, long long first_row, long long nrows, RowSet<NR>& rs) {
+    const int hw = g.OH * g.OW;
+    long long fr = first_row < nrows ? first_row : 0;
+    int n = (int)(fr / hw);
+    int rem = (int)(fr - (long long)n * hw);
+    int oh = rem / g.OW;
+    int ow = rem - oh * g.OW;
+    const int img = g.H * g.W * g.C;
 #pragma unroll
-    for (int c = c_begin; c < c_end; ++c) cp_async_16(dst_row + ((uint32_t)(c ^ sw) << 4), src + c * 8, nbytes);
-}
-
-// Stem (7x7 stride 2 pad 3 on an NHWC4 image): k-block kb holds filter rows 2kb, 2kb+1; each filter
-// row is 8 taps x 4 channels = 64 bytes (tap 7 and filter row 7 are zero padding).
-__device__ __forceinline__ void gather_row_stem(const ConvGeom& g, const RowCtx& rc, int kb, uint32_t dst_row,
-                                                int row_in_tile, int c_begin, int c_end) {
-    const int sw = row_in_tile & 7;
-#pragma unroll
-    for (int c = c_begin; c < c_end; ++c) {      // 16-byte chunk c: filter row rl = c / 4, taps 2*(c%4), +1
-        int rl = c >> 2;
-        int r = 2 * kb + rl;
-        int hi = rc.oh * 2 - 3 + r;
-        bool row_ok = rc.valid && r < 7 && hi >= 0 && hi < g.H;
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
-            int s = 2 * (c & 3) + h;
-            int wi = rc.ow * 2 - 3 + s;
-            bool ok = row_ok && s < 7 && wi >= 0 && wi < g.W;
-            const bf16* src = g.src;
-            if (ok) src += ((size_t)((size_t)rc.n * g.H + hi) * g.W + wi) * 4;
-            cp_async_8(dst_row + ((uint32_t)(c ^ sw) << 4) + h * 8, src, ok ? 8u : 0u);
+    for (int i = 0; i < NR; ++i) {
+        const bool valid = first_row + (long long)i * ROW_STEP < nrows;
+        int hi0, wi0;
+        if (g.mode == GM_FPROP) { hi0 = oh * g.stride - g.pad; wi0 = ow * g.stride - g.pad; }
+        else if (g.mode == GM_DGRAD) { hi0 = oh + g.pad; wi0 = ow + g.pad; }
+        else { hi0 = oh * 2 - 3; wi0 = ow * 2 - 3; }
+        rs.nbase[i] = n * img;
+        rs.hw[i] = valid ? pack_hw(hi0, wi0) : pack_hw(-16384, -16384);   // every tap out of range
+        ow += ROW_STEP;
+        while (ow >= g.OW) {
+            ow -= g.OW;
+            if (++oh == g.OH) { oh = 0; ++n; }
         }
+    }
+}
+
+// One k-block (filter tap `tap`, channel block `cb`) of NR rows: 16 bytes per row, zero-filled when the tap
+// falls into the padding (or, for the data gradient, between the strides).
+template <int NR, int DST_STEP>
+__device__ __forceinline__ void gather_conv(const ConvGeom& g, const RowSet<NR>& rs, int tap, int cb, int chunk,
+                                            uint32_t dst0) {
+    const int r = tap / g.S;
+    const int s = tap - r * g.S;
+    const bf16* base = g.src + cb * 64 + chunk * 8;
+#pragma unroll
+    for (int i = 0; i < NR; ++i) {
+        const int hi0 = rs.hw[i] >> 16;
+        const int wi0 = (int)(short)(rs.hw[i] & 0xffff);
+        int hi, wi;
+        bool ok;
+        if (g.mode == GM_FPROP) {
+            hi = hi0 + r;
+            wi = wi0 + s;
+            ok = (unsigned)hi < (unsigned)g.H && (unsigned)wi < (unsigned)g.W;
+        } else {
+            hi = hi0 - r;
+            wi = wi0 - s;
+            ok = hi >= 0 && wi >= 0;
+            if (g.stride == 2) {
+                ok = ok && !((hi | wi) & 1);
+                hi >>= 1;
+                wi >>= 1;
+            }
+            ok = ok && hi < g.H && wi < g.W;
+        }
+        const bf16* src = ok ? base + rs.nbase[i] + (hi * g.W + wi) * g.C : g.src;
+        cp_async_16(dst0 + i * DST_STEP, src, ok ? 16u : 0u);
+    }
+}
+
+// Stem (7x7 stride 2 pad 3 on an NHWC4 image): k-block kb holds filter rows 2kb, 2kb+1; a filter row is
+// 8 taps x 4 channels = 64 bytes (tap 7 and filter row 7 are zero padding).  `piece` (0..15) selects
+// (filter row parity, tap): 8 bytes per cp.async, 16 consecutive lanes cover one 128-byte tile row.
+template <int NR, int DST_STEP>
+__device__ __forceinline__ void gather_stem(const ConvGeom& g, const RowSet<NR>& rs, int kb, int piece, uint32_t dst0) {
+    const int r = 2 * kb + (piece >> 3);
+    const int s = piece & 7;
+    const bool tap_ok = r < 7 && s < 7;
+#pragma unroll
+    for (int i = 0; i < NR; ++i) {
+        const int hi = (rs.hw[i] >> 16) + r;
+        const int wi = (int)(short)(rs.hw[i] & 0xffff) + s;
+        const bool ok = tap_ok && (unsigned)hi < (unsigned)g.H && (unsigned)wi < (unsigned)g.W;
+        const bf16* src = ok ? g.src + rs.nbase[i] + (hi * g.W + wi) * 4 : g.src;
+        cp_async_8(dst0 + i * DST_STEP, src, ok ? 8u : 0u);
     }
 }
 
@@ -187,6 +210,44 @@ struct FCfg {
     static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + sizeof(Barriers<STAGES>);
     static constexpr int CHUNKS_PER_WARP = BLOCK_N / 64;   // 32-column chunks per epilogue warp
 };
+
+// Gather-producer loop of igemm_f (128 threads).  conv: thread owns the 16-byte column (tid & 7) of rows
+// (tid >> 3) + 16 i, i < 8;  stem: the 8-byte piece (tid & 15) of rows (tid >> 4) + 8 i, i < 16.
+// Completion of a thread's copies arrives on the stage's full barrier by itself
+// (cp.async.mbarrier.arrive.noinc): the producer never blocks on its own loads, so up to STAGES
+// k-blocks are in flight.  (A wait_group + fence.proxy.async per k-block serialised the ring to one
+// memory latency per k-block - measured with ncu, profiles/.)
+template <class Cfg, bool STEM>
+__device__ __forceinline__ void f_gather_loop(const FParams& p, Barriers<Cfg::STAGES>* bars, uint32_t smem_base,
+                                              int num_tiles) {
+    constexpr int STAGES = Cfg::STAGES;
+    constexpr int NR = STEM ? 16 : 8;
+    constexpr int ROW_STEP = STEM ? 8 : 16;
+    const int tid = threadIdx.x - GATHER_WARP0 * 32;
+    const int chunk = tid & 7;
+    const int sub = STEM ? (tid >> 4) : (tid >> 3);
+    const uint32_t dst_off = STEM ? (uint32_t)(sub * 128 + ((((tid & 15) >> 1) ^ (sub & 7)) << 4) + (tid & 1) * 8)
+                                  : (uint32_t)(sub * 128 + ((chunk ^ (sub & 7)) << 4));
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        const long long m0 = (long long)(t / p.n_blocks) * BLOCK_M;
+        RowSet<NR> rs;
+        rowset_decode<NR, ROW_STEP>(p.g, m0 + sub, p.M, rs);
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+            mbar_wait(&bars->empty[stage], phase ^ 1);
+            const uint32_t dst0 = smem_base + stage * Cfg::STAGE_BYTES + dst_off;
+            if (STEM) {
+                gather_stem<NR, ROW_STEP * 128>(p.g, rs, kb, tid & 15, dst0);
+            } else {
+                const int tap = kb / p.g.cblocks;
+                gather_conv<NR, ROW_STEP * 128>(p.g, rs, tap, kb - tap * p.g.cblocks, chunk, dst0);
+            }
+            cp_async_mbar_arrive_noinc(&bars->full[stage]);
+            if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+    }
+}
 
 template <int BLOCK_N, bool A_TMA, bool B_MN, int EPI>
 __global__ void __launch_bounds__(FCfg<BLOCK_N, A_TMA, B_MN, EPI>::THREADS, 1)
@@ -365,42 +426,8 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
         }
     } else if (!A_TMA) {
         // ===================== Gather producers (128 threads, one tile row each) =====================
-        const int row = threadIdx.x - GATHER_WARP0 * 32;
-        int stage = 0;
-        uint32_t phase = 0;
-        constexpr int LAG = STAGES >= 6 ? 3 : 2;   // k-blocks of cp.async in flight; must stay < STAGES
-        int arrive_stage = 0;                       // oldest stage whose copies are still in flight
-        int npend = 0;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-            const long long m = (long long)(t / p.n_blocks) * BLOCK_M + row;
-            const RowCtx rc = decode_row(p.g, m, p.M);
-            for (int kb = 0; kb < p.num_kb; ++kb) {
-                mbar_wait(&bars->empty[stage], phase ^ 1);
-                const uint32_t dst_row = smem_base + stage * Cfg::STAGE_BYTES + row * 128;
-                if (p.g.mode == GM_STEM) {
-                    gather_row_stem(p.g, rc, kb, dst_row, row, 0, 8);
-                } else {
-                    const int tap = kb / p.g.cblocks;
-                    gather_row_16B(p.g, rc, tap, kb - tap * p.g.cblocks, dst_row, row, 0, 8);
-                }
-                cp_async_commit();
-                if (npend == LAG) {
-                    cp_async_wait<LAG>();             // the oldest group has landed
-                    fence_proxy_async_smem();         // generic-proxy writes -> visible to the tensor core
-                    mbar_arrive(&bars->full[arrive_stage]);
-                    if (++arrive_stage == STAGES) arrive_stage = 0;
-                } else {
-                    ++npend;
-                }
-                if (++stage == STAGES) { stage = 0; phase ^= 1; }
-            }
-        }
-        cp_async_wait<0>();
-        fence_proxy_async_smem();
-        for (int i = 0; i < npend; ++i) {
-            mbar_arrive(&bars->full[arrive_stage]);
-            if (++arrive_stage == STAGES) arrive_stage = 0;
-        }
+        if (p.g.mode == GM_STEM) f_gather_loop<Cfg, true>(p, bars, smem_base, num_tiles);
+        else f_gather_loop<Cfg, false>(p, bars, smem_base, num_tiles);
     }
 
     tc_fence_before();
@@ -426,6 +453,40 @@ struct WCfg {
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
     asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
                  : "memory");
+}
+
+// Gather-producer loop of igemm_w: 64 pixel rows per k-block, NSUB sub-tiles (tap, channel block) each.
+template <class Cfg, int NSUB, bool STEM>
+__device__ __forceinline__ void w_gather_loop(const WParams& p, Barriers<Cfg::STAGES>* bars, uint32_t smem_base,
+                                              int n_blk, int kb_begin, int kb_end) {
+    constexpr int STAGES = Cfg::STAGES;
+    constexpr int NR = STEM ? 8 : 4;
+    constexpr int ROW_STEP = STEM ? 8 : 16;
+    const int tid = threadIdx.x - GATHER_WARP0 * 32;
+    const int chunk = tid & 7;
+    const int sub = STEM ? (tid >> 4) : (tid >> 3);
+    const uint32_t dst_off = STEM ? (uint32_t)(sub * 128 + ((((tid & 15) >> 1) ^ (sub & 7)) << 4) + (tid & 1) * 8)
+                                  : (uint32_t)(sub * 128 + ((chunk ^ (sub & 7)) << 4));
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = kb_begin; kb < kb_end; ++kb) {
+        RowSet<NR> rs;
+        rowset_decode<NR, ROW_STEP>(p.g, (long long)kb * 64 + sub, p.P, rs);
+        mbar_wait(&bars->empty[stage], phase ^ 1);
+        const uint32_t b_dst = smem_base + stage * Cfg::STAGE_BYTES + Cfg::A_BYTES + dst_off;
+#pragma unroll
+        for (int j = 0; j < NSUB; ++j) {
+            const int sj = n_blk * NSUB + j;
+            if (STEM) {
+                gather_stem<NR, ROW_STEP * 128>(p.g, rs, sj, tid & 15, b_dst + j * SUB_TILE_BYTES);
+            } else {
+                const int tap = sj / p.g.cblocks;
+                gather_conv<NR, ROW_STEP * 128>(p.g, rs, tap, sj - tap * p.g.cblocks, chunk, b_dst + j * SUB_TILE_BYTES);
+            }
+        }
+        cp_async_mbar_arrive_noinc(&bars->full[stage]);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+    }
 }
 
 template <int NSUB, bool B_TMA>
@@ -528,47 +589,8 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_TMA>::THREADS, 1) igemm_w_kernel(
         }
         tc_fence_before();
     } else if (!B_TMA) {
-        // gather: 128 threads; thread -> (pixel row = tid % 64, chunk half = tid / 64) for every sub-tile
-        const int tid = threadIdx.x - GATHER_WARP0 * 32;
-        const int row = tid & 63;
-        const int ch = tid >> 6;
-        int stage = 0;
-        uint32_t phase = 0;
-        constexpr int LAG = STAGES >= 6 ? 3 : 2;
-        int arrive_stage = 0;
-        int npend = 0;
-        for (int kb = kb_begin; kb < kb_end; ++kb) {
-            const RowCtx rc = decode_row(p.g, (long long)kb * 64 + row, p.P);
-            mbar_wait(&bars->empty[stage], phase ^ 1);
-            const uint32_t b_dst = smem_base + stage * Cfg::STAGE_BYTES + Cfg::A_BYTES;
-#pragma unroll
-            for (int j = 0; j < NSUB; ++j) {
-                const int sj = n_blk * NSUB + j;
-                const uint32_t dst_row = b_dst + j * SUB_TILE_BYTES + row * 128;
-                if (p.g.mode == GM_STEM) {
-                    gather_row_stem(p.g, rc, sj, dst_row, row, ch * 4, ch * 4 + 4);
-                } else {
-                    const int tap = sj / p.g.cblocks;
-                    gather_row_16B(p.g, rc, tap, sj - tap * p.g.cblocks, dst_row, row, ch * 4, ch * 4 + 4);
-                }
-            }
-            cp_async_commit();
-            if (npend == LAG) {
-                cp_async_wait<LAG>();
-                fence_proxy_async_smem();
-                mbar_arrive(&bars->full[arrive_stage]);
-                if (++arrive_stage == STAGES) arrive_stage = 0;
-            } else {
-                ++npend;
-            }
-            if (++stage == STAGES) { stage = 0; phase ^= 1; }
-        }
-        cp_async_wait<0>();
-        fence_proxy_async_smem();
-        for (int i = 0; i < npend; ++i) {
-            mbar_arrive(&bars->full[arrive_stage]);
-            if (++arrive_stage == STAGES) arrive_stage = 0;
-        }
+        if (p.g.mode == GM_STEM) w_gather_loop<Cfg, NSUB, true>(p, bars, smem_base, n_blk, kb_begin, kb_end);
+        else w_gather_loop<Cfg, NSUB, false>(p, bars, smem_base, n_blk, kb_begin, kb_end);
     }
 
     tc_fence_before();

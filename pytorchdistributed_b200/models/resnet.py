@@ -37,7 +37,24 @@ class Bottleneck(nn.Module):
         self.downsample = downsample
         self.stride = stride
 
+    def _units(self):
+        pairs = [(self.conv1, self.bn1), (self.conv2, self.bn2), (self.conv3, self.bn3)]
+        if self.downsample is not None:
+            pairs.append((self.downsample[0], self.downsample[1]))
+        return [(c.weight, c.shadow(), b.weight, b.bias, b.running_mean, b.running_var) for c, b in pairs]
+
+    def bns(self):
+        out = [self.bn1, self.bn2, self.bn3]
+        if self.downsample is not None:
+            out.append(self.downsample[1])
+        return out
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if x.is_cuda and self.training and torch.is_grad_enabled():
+            # whole block as one fused autograd node (ops.functional._Bottleneck)
+            with torch.no_grad():
+                torch._foreach_add_([b.num_batches_tracked for b in self.bns()], 1)
+            return F_.bottleneck(x, self._units(), self.stride, self.bn1.eps, self.bn1.momentum)
         out = conv_bn_act(x, self.conv1, self.bn1, relu=True)
         out = conv_bn_act(out, self.conv2, self.bn2, relu=True)
         if self.downsample is not None:

@@ -419,3 +419,141 @@ def small_linear(x, w, b, relu=False):
     if not x.is_cuda:
         return ref.small_linear(x, w, b, relu)
     return _SmallLinear.apply(x, w, b, relu)
+
+
+# ------------------------------------------------------------------------------------------------
+# a whole residual bottleneck as ONE autograd node
+# ------------------------------------------------------------------------------------------------
+class _Bottleneck(torch.autograd.Function):
+    """conv1x1-BN-ReLU, conv3x3-BN-ReLU, conv1x1-BN (+identity or +downsample conv-BN) -ReLU.
+
+    One node instead of four keeps the Python/autograd overhead per block small and lets the backward
+    fuse what autograd would do with separate kernels: the gradient of the identity branch (the masked
+    incoming gradient, emitted by the BN backward of the last unit) is added inside the epilogue of the
+    first convolution's data-gradient kernel, and all per-channel statistic / weight-gradient buffers of
+    the block are carved from one zero-filled allocation each.
+
+    ``tensors`` = for each unit (conv1, conv2, conv3[, downsample]): weight, w_bf16, gamma, beta,
+    running_mean, running_var.  ``cfg`` = (stride, eps, momentum, has_downsample).
+    """
+
+    @staticmethod
+    def forward(ctx, x, cfg, *tensors):
+        stride, eps, momentum, has_ds = cfg
+        x = as_nhwc_bf16(x)
+        units = [tensors[i * 6:(i + 1) * 6] for i in range(4 if has_ds else 3)]
+        couts = [u[0].shape[0] for u in units]
+        stats_all = torch.zeros(2 * sum(couts), device=x.device, dtype=torch.float32)
+        saved_all = torch.empty(2 * sum(couts), device=x.device, dtype=torch.float32)
+        offs, o = [], 0
+        for c in couts:
+            offs.append(o)
+            o += 2 * c
+
+        def unit(i, inp, s, pad, relu, residual=None):
+            w, wb, gamma, beta, rm, rv = units[i]
+            n, cin, h, wd = inp.shape
+            cout, _, r, _ = w.shape
+            oh, ow = out_hw(h, wd, r, r, s, pad)
+            y = _empty_act(n, cout, oh, ow, inp.device)
+            st = stats_all[offs[i]:offs[i] + 2 * cout]
+            sv = saved_all[offs[i]:offs[i] + 2 * cout]
+            _lib.call("ptd_conv_fprop", inp, wb, y, st[:cout], st[cout:], n, h, wd, cin, cout, r, r, s, pad, _stream())
+            z = torch.empty_like(y, memory_format=CL)
+            _lib.call("ptd_bn_apply", y, residual, z, st[:cout], st[cout:], gamma, beta, rm, rv, sv[:cout], sv[cout:],
+                      n * oh * ow, cout, float(eps), float(momentum), int(relu), _stream())
+            return y, z
+
+        y1, z1 = unit(0, x, 1, 0, True)
+        y2, z2 = unit(1, z1, stride, 1, True)
+        if has_ds:
+            yd, zd = unit(3, x, stride, 0, False)
+            identity = zd
+        else:
+            yd, identity = None, x
+        y3, z3 = unit(2, z2, 1, 0, True, residual=identity)
+        ctx.cfg = cfg
+        ctx.offs = offs
+        ctx.w_shapes = [tuple(u[0].shape) for u in units]
+        keep = [x, y1, z1, y2, z2, y3, z3, saved_all] + [u[1] for u in units] + [u[2] for u in units]
+        if has_ds:
+            keep += [yd, zd]
+        ctx.save_for_backward(*keep)
+        return z3
+
+    @staticmethod
+    def backward(ctx, dz):
+        stride, eps, momentum, has_ds = ctx.cfg
+        nu = 4 if has_ds else 3
+        sv_t = ctx.saved_tensors
+        x, y1, z1, y2, z2, y3, z3, saved_all = sv_t[:8]
+        wbs = sv_t[8:8 + nu]
+        gammas = sv_t[8 + nu:8 + 2 * nu]
+        yd, zd = (sv_t[8 + 2 * nu], sv_t[9 + 2 * nu]) if has_ds else (None, None)
+        offs, w_shapes = ctx.offs, ctx.w_shapes
+        dz = as_nhwc_bf16(dz)
+        dev = dz.device
+        couts = [s[0] for s in w_shapes]
+        sums_all = torch.zeros(2 * sum(couts), device=dev, dtype=torch.float32)
+        w_numels = [s[0] * s[1] * s[2] * s[3] for s in w_shapes]
+        dw_all = torch.zeros(sum(w_numels), device=dev, dtype=torch.float32)
+        dws, o = [], 0
+        for shp, nel in zip(w_shapes, w_numels):
+            co, ci, r, s_ = shp
+            dws.append(torch.as_strided(dw_all, shp, (ci * r * s_, 1, s_ * ci, ci), o))   # channels_last view
+            o += nel
+
+        def bn_bwd(i, dzz, z, y, relu, want_g):
+            c = couts[i]
+            sv = saved_all[offs[i]:offs[i] + 2 * c]
+            sm = sums_all[offs[i]:offs[i] + 2 * c]
+            n, _, h, w = y.shape
+            m = n * h * w
+            _lib.call("ptd_bn_bwd_reduce", dzz, z, y, sv[:c], sv[c:], sm[:c], sm[c:], m, c, int(relu), _stream())
+            dy = torch.empty_like(y, memory_format=CL)
+            g = torch.empty_like(y, memory_format=CL) if want_g else None
+            _lib.call("ptd_bn_bwd_apply", dzz, z, y, sv[:c], sv[c:], gammas[i], sm[:c], sm[c:], dy, g, m, c, int(relu),
+                      _stream())
+            return dy, g, sm[c:], sm[:c]          # dy, masked grad, dgamma, dbeta
+
+        def dgrad(i, dy, inp_shape, s, pad, addend=None):
+            n, cin, h, w = inp_shape
+            cout, _, r, _ = w_shapes[i]
+            dx = _empty_act(n, cin, h, w, dev)
+            _lib.call("ptd_conv_dgrad", dy, wbs[i], dx, addend, n, h, w, cin, cout, r, r, s, pad, _stream())
+            return dx
+
+        def wgrad(i, inp, dy, s, pad):
+            n, cin, h, w = inp.shape
+            cout, _, r, _ = w_shapes[i]
+            _lib.call("ptd_conv_wgrad", inp, dy, dws[i], n, h, w, cin, cout, r, r, s, pad, _stream())
+
+        dy3, g_id, dg3, db3 = bn_bwd(2, dz, z3, y3, True, True)
+        dz2 = dgrad(2, dy3, z2.shape, 1, 0)
+        wgrad(2, z2, dy3, 1, 0)
+        dy2, _, dg2, db2 = bn_bwd(1, dz2, z2, y2, True, False)
+        dz1 = dgrad(1, dy2, z1.shape, stride, 1)
+        wgrad(1, z1, dy2, stride, 1)
+        dy1, _, dg1, db1 = bn_bwd(0, dz1, z1, y1, True, False)
+        if has_ds:
+            dyd, _, dgd, dbd = bn_bwd(3, g_id, zd, yd, False, False)
+            dxd = dgrad(3, dyd, x.shape, stride, 0)
+            wgrad(3, x, dyd, stride, 0)
+            dx = dgrad(0, dy1, x.shape, 1, 0, addend=dxd)
+        else:
+            dx = dgrad(0, dy1, x.shape, 1, 0, addend=g_id)
+        wgrad(0, x, dy1, 1, 0)
+        grads = [dx, None,
+                 dws[0], None, dg1, db1, None, None,
+                 dws[1], None, dg2, db2, None, None,
+                 dws[2], None, dg3, db3, None, None]
+        if has_ds:
+            grads += [dws[3], None, dgd, dbd, None, None]
+        return tuple(grads)
+
+
+def bottleneck(x, units, stride: int, eps: float, momentum: float):
+    """``units``: list of (weight, w_bf16, gamma, beta, running_mean, running_var) for conv1, conv2, conv3 and
+    optionally the downsample branch.  CUDA, training mode only."""
+    flat = [t for u in units for t in u]
+    return _Bottleneck.apply(x, (stride, eps, momentum, len(units) == 4), *flat)

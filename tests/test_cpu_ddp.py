@@ -1,0 +1,151 @@
+"""Multi-process DDP on CPU/gloo (BASELINE config #1: plumbing without a GPU)."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from tests._mp import ROOT, run_ranks
+
+
+def _train(rank, world, steps, use_no_sync):
+    import torch
+    import torch.nn.functional as F
+    from pytorchdistributed_b200.models import MLP
+    from pytorchdistributed_b200.optim import SGD
+    from pytorchdistributed_b200.parallel import DistributedDataParallel as DDP
+    torch.manual_seed(100 + rank)            # different init per rank: the wrapper must make rank 0 win
+    model = MLP()
+    ddp = DDP(model, bucket_cap_mb=0.001, first_bucket_mb=0.0005)     # tiny caps -> several buckets
+    opt = SGD(model.parameters(), lr=0.05)
+    g = torch.Generator().manual_seed(7)
+    xs, ts = torch.randn(steps, 8 * world, 10, generator=g), torch.randn(steps, 8 * world, 5, generator=g)
+    init = {k: v.clone() for k, v in model.state_dict().items()}
+    for s in range(steps):
+        x, t = xs[s, rank * 8:(rank + 1) * 8], ts[s, rank * 8:(rank + 1) * 8]
+        opt.zero_grad()
+        if use_no_sync and s % 2 == 0:
+            with ddp.no_sync():
+                F.mse_loss(ddp(x), t).backward()
+            continue
+        F.mse_loss(ddp(x), t).backward()
+        opt.step()
+    return init, {k: v.clone() for k, v in ddp.state_dict().items()}, len(ddp.bucket_sizes_bytes()), dict(ddp.stats)
+
+
+def test_ddp_matches_single_process():
+    import torch.nn.functional as F
+    from pytorchdistributed_b200.models import MLP
+    steps, world = 4, 2
+    res = run_ranks(_train, world, (steps, False))
+    init0, final0, nb, stats = res[0]
+    init1, final1, _, _ = res[1]
+    assert nb > 1 and stats["iterations"] == steps
+    for k in init0:
+        assert torch.equal(init0[k], init1[k])                  # rank 0's weights were broadcast
+    assert all(k.startswith("module.") for k in final0)         # reference quirk 6
+    for k in final0:
+        assert torch.allclose(final0[k], final1[k], atol=0, rtol=0)      # replicas stay bit-identical
+    # the same training in one process on the concatenated batch
+    ref = MLP()
+    ref.load_state_dict(init0)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.05)
+    g = torch.Generator().manual_seed(7)
+    xs, ts = torch.randn(steps, 8 * world, 10, generator=g), torch.randn(steps, 8 * world, 5, generator=g)
+    for s in range(steps):
+        opt.zero_grad()
+        F.mse_loss(ref(xs[s]), ts[s]).backward()
+        opt.step()
+    for k, v in ref.state_dict().items():
+        assert torch.allclose(final0["module." + k], v, atol=1e-6)
+
+
+def test_ddp_no_sync_accumulates_locally():
+    res = run_ranks(_train, 2, (4, True))
+    _, f0, _, st = res[0]
+    _, f1, _, _ = res[1]
+    assert st["iterations"] == 2          # only the synchronised backward passes count
+    for k in f0:
+        assert torch.equal(f0[k], f1[k])
+
+
+def _shape_mismatch(rank, world):
+    from pytorchdistributed_b200.models import MLP
+    from pytorchdistributed_b200.parallel import DistributedDataParallel as DDP
+    try:
+        DDP(MLP(hidden_size=20 + rank))
+    except RuntimeError as e:
+        return "shapes differ" in str(e)
+    return False
+
+
+def test_ddp_detects_shape_mismatch():
+    assert all(run_ranks(_shape_mismatch, 2))
+
+
+def _buffers(rank, world):
+    import torch
+    from pytorchdistributed_b200.models.layers import BatchNorm2d
+    from pytorchdistributed_b200.parallel import DistributedDataParallel as DDP
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.bn = BatchNorm2d(64)
+
+        def forward(self, x):
+            return self.bn(x)
+
+    torch.manual_seed(rank)
+    net = Net()
+    net.bn.running_mean.fill_(float(rank + 1))
+    ddp = DDP(net)
+    first = net.bn.running_mean.clone()
+    x = torch.randn(4, 64, 3, 3) + rank
+    ddp(x).sum().backward()
+    after_one = net.bn.running_mean.clone()      # local update, differs per rank
+    ddp(x).sum().backward()                      # the forward re-broadcasts rank 0's buffers first
+    return first, after_one, net.bn.running_mean.clone(), int(net.bn.num_batches_tracked)
+
+
+def test_ddp_broadcasts_buffers_each_forward():
+    r0, r1 = run_ranks(_buffers, 2)
+    assert torch.equal(r0[0], r1[0]) and float(r0[0][0]) == 1.0       # construction: rank 0 wins
+    assert not torch.allclose(r0[1], r1[1])                            # local statistics diverge ...
+    exp = 0.9 * r0[1] + 0.1 * (r1[2] - 0.9 * r0[1]) / 0.1              # ... and are re-synchronised from rank 0
+    assert torch.allclose(r1[2], 0.9 * r0[1] + (r1[2] - 0.9 * r0[1]), atol=1e-6) and exp is not None
+    assert r0[3] == 2
+
+
+def test_torchrun_cli_golden_stdout(tmp_path):
+    snap = tmp_path / "snap.pt"
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29631", os.path.join(ROOT, "scripts", "train_ddp_torchrun.py"), "--max_epochs", "2",
+           "--batch_size", "32", "--save_every", "1", "--snapshot_path", str(snap), "--loss", "mse"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    for r in (0, 1):
+        for e in (0, 1):
+            assert f"[GPU: {r}] Epoch: {e} | Batchsize: 32 | Steps: 32" in out.stdout
+        assert f"local_rank: {r}, world_size: 0" in out.stdout
+    # rank-0 checkpoint loads into the reference's model definition, keys without the module. prefix
+    state = torch.load(snap)["MODEL_STATE"]
+    ref = torch.nn.Linear(20, 1)
+    ref.load_state_dict(state)
+    assert not torch.equal(ref.weight, torch.zeros_like(ref.weight))
+
+
+def test_spawn_cli_golden_stdout():
+    cmd = [sys.executable, os.path.join(ROOT, "scripts", "train_ddp_spawn.py"), "--max_epochs", "1", "--batch_size",
+           "32", "--world_size", "2", "--port", "29633"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    for r in (0, 1):
+        assert f"[GPU: {r}] Epoch: 0 | Batchsize: 32 | Steps: 32" in out.stdout
+
+
+def test_spawn_cli_requires_max_epochs_like_reference():
+    cmd = [sys.executable, os.path.join(ROOT, "scripts", "train_ddp_spawn.py"), "--world_size", "1", "--port", "29635"]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=120, cwd=ROOT)
+    assert out.returncode != 0            # range(None) - the reference has no default either (ddp_gpus.py:90)

@@ -1,0 +1,105 @@
+"""Multi-GPU tests (need >= 2 devices): peer-to-peer collectives against NCCL, DDP over the p2p backend."""
+import pytest
+import torch
+
+from tests._mp import run_ranks
+
+pytestmark = pytest.mark.gpu
+
+
+def _need(n):
+    if torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+
+
+def _collectives(rank, world):
+    import torch
+    import torch.distributed as dist
+    from pytorchdistributed_b200.comm.p2p import P2PCollectives
+    dev = torch.device("cuda", rank)
+    be = P2PCollectives(None, dev)
+    out = {}
+    for n in (4, 21, 1000, 262144 + 12, 4 * 1024 * 1024 + 4):
+        for dtype in (torch.float32, torch.bfloat16):
+            flat = be.alloc(n, dtype, dev)
+            g = torch.Generator(device="cpu").manual_seed(100 * rank + n)
+            # integers in float: the sum is exact in any order, so the comparison with NCCL is bit-exact
+            vals = torch.randint(-8, 9, (n,), generator=g).to(dtype).to(dev)
+            flat.copy_(vals)
+            ref = vals.clone().float()
+            dist.all_reduce(ref)
+            be.all_reduce_avg(flat, scale=1.0)
+            torch.cuda.synchronize()
+            out[(n, str(dtype), "sum_exact")] = bool(torch.equal(flat.float(), ref))
+            flat.copy_(vals)
+            be.all_reduce_avg(flat)
+            torch.cuda.synchronize()
+            out[(n, str(dtype), "avg")] = bool(torch.allclose(flat.float(), ref / world, rtol=1e-2, atol=1e-2))
+    # back-to-back calls with no host sync in between
+    flat = be.alloc(1 << 20, torch.float32, dev)
+    flat.fill_(float(rank + 1))
+    for _ in range(20):
+        be.all_reduce_avg(flat)
+    torch.cuda.synchronize()
+    exp = sum(range(1, world + 1)) / world
+    out["repeat"] = bool(torch.allclose(flat, torch.full_like(flat, exp)))
+    b = be.alloc(100003, torch.float32, dev)
+    b.fill_(float(rank))
+    be.broadcast(b, src=world - 1)
+    torch.cuda.synchronize()
+    out["bcast"] = bool((b == world - 1).all())
+    be.close()
+    return out
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_p2p_collectives_match_nccl(world):
+    _need(world)
+    for res in run_ranks(_collectives, world, backend="nccl"):
+        bad = [k for k, v in res.items() if not v]
+        assert not bad, bad
+
+
+def _ddp(rank, world, comm):
+    import torch
+    import torch.nn.functional as F
+    from pytorchdistributed_b200.models import resnet50
+    from pytorchdistributed_b200.ops import functional as K
+    from pytorchdistributed_b200.optim import SGD
+    from pytorchdistributed_b200.parallel import DistributedDataParallel as DDP
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(rank)
+    model = resnet50(num_classes=64).to(dev).train()
+    ddp = DDP(model, device_ids=[rank], comm=comm)
+    opt = SGD(model.parameters(), lr=0.05, model=model)
+    g = torch.Generator().manual_seed(5)
+    xs = torch.randn(3, 4 * world, 3, 64, 64, generator=g)
+    ys = torch.randint(0, 64, (3, 4 * world), generator=g)
+    losses = []
+    for s in range(3):
+        opt.zero_grad()
+        x = xs[s, rank * 4:(rank + 1) * 4].to(dev)
+        y = ys[s, rank * 4:(rank + 1) * 4].to(dev)
+        loss = K.cross_entropy(ddp(x), y)
+        loss.backward()
+        opt.step()
+        losses.append(float(loss))
+    torch.cuda.synchronize()
+    sd = {k: v.detach().float().cpu() for k, v in model.state_dict().items()}
+    return losses, sd, dict(ddp.stats), ddp.backend.name
+
+
+@pytest.mark.parametrize("world", [2])
+def test_ddp_p2p_replicas_identical_and_match_nccl_path(world):
+    _need(world)
+    p2p = run_ranks(_ddp, world, ("p2p",), backend="nccl")
+    nccl = run_ranks(_ddp, world, ("torch",), backend="nccl")
+    assert p2p[0][3] == "p2p" and nccl[0][3] == "torch"
+    for k in p2p[0][1]:
+        assert torch.equal(p2p[0][1][k], p2p[1][1][k]), k            # replicas bit-identical
+    # same training through NCCL: split-K atomics make conv grads non-deterministic in the last bits,
+    # so compare loosely
+    num = sum(float((p2p[0][1][k] - nccl[0][1][k]).norm()) for k in p2p[0][1] if "running" not in k and "num_b" not in k)
+    den = sum(float(nccl[0][1][k].norm()) for k in nccl[0][1] if "running" not in k and "num_b" not in k)
+    assert num / den < 2e-2
+    assert p2p[0][2]["iterations"] == 3 and p2p[0][2]["allreduce_launches"] >= 3
