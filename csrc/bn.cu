@@ -236,7 +236,9 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ z, con
 
 int bn_grid(long long M, int C) {
     const int rows_per_iter = BN_THREADS / (C >> 3);
-    long long blocks = (M + rows_per_iter - 1) / rows_per_iter;
+    // >= 8 row groups per block: small tensors get few blocks, so the per-block tail (shared-memory
+    // reduction + one atomic per channel) and the launch itself stay cheap
+    long long blocks = ((M + rows_per_iter - 1) / rows_per_iter + 7) / 8;
     const long long cap = (long long)ptd_num_sms() * 8;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;

@@ -149,6 +149,18 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* m, 
         : "memory");
 }
 
+// im2col-mode load: (c, w, h, n) is the input-space position of the first pixel's top-left tap, (off_w, off_h) the
+// filter tap; the box is [pixels][64 channels].
+__device__ __forceinline__ void tma_load_im2col(uint32_t dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h,
+                                                int n, uint32_t off_w, uint32_t off_h) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n),
+          "h"((uint16_t)off_w), "h"((uint16_t)off_h)
+        : "memory");
+}
+
 // ---- TMEM / tcgen05 ---------------------------------------------------------------------------
 template <uint32_t COLS>
 __device__ __forceinline__ void tmem_alloc(uint32_t* slot_in_smem) {

@@ -19,6 +19,8 @@
 // warp 9 TMEM allocator + single-thread MMA issuer, warps 10-13 gather producers.
 // The reference reaches these ops through cuDNN/cuBLAS (call sites
 // R/03 模型并行/03_model_parallel.ipynb#cell4-7,12).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "ptdb200.h"
 #include "tensormap.h"
@@ -63,6 +65,7 @@ struct alignas(64) FParams {
     float* out_f32;
     const float* bias;
     int ldo;
+    int dbg;             // experiment switches (PTD_IGEMM_DBG), 0 in production
 };
 
 struct alignas(64) WParams {
@@ -200,14 +203,17 @@ __device__ __forceinline__ float transpose_reduce32(float (&v)[32], uint32_t lan
 // ------------------------------------------------------------------------------------------
 // igemm_f
 // ------------------------------------------------------------------------------------------
-template <int BLOCK_N, bool A_TMA, bool B_MN, int EPI /*0 = bf16 (+stats/+addend), 1 = fp32 + bias*/>
+enum { AM_GATHER = 0, AM_TILED = 1, AM_IM2COL = 2 };   // how the pixel-row operand reaches shared memory
+
+template <int BLOCK_N, int A_MODE, bool B_MN, int EPI /*0 = bf16 (+stats/+addend), 1 = fp32 + bias*/>
 struct FCfg {
     static constexpr int B_TILE_BYTES = BLOCK_N * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
     static constexpr int STAGES = (BLOCK_N == 256) ? 4 : (BLOCK_N == 128 ? 6 : 8);
-    static constexpr int THREADS = A_TMA ? (MMA_WARP + 1) * 32 : (GATHER_WARP0 + 4) * 32;
+    static constexpr int THREADS = A_MODE != AM_GATHER ? (MMA_WARP + 1) * 32 : (GATHER_WARP0 + 4) * 32;
     static constexpr int TMEM_COLS = 2 * BLOCK_N;
-    static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + sizeof(Barriers<STAGES>);
+    static constexpr int STAGING_OFF = STAGES * STAGE_BYTES + 1024;        // barriers live in the 1 KiB before it
+    static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGING_OFF + NUM_EPI_WARPS * 2048;
     static constexpr int CHUNKS_PER_WARP = BLOCK_N / 64;   // 32-column chunks per epilogue warp
 };
 
@@ -237,22 +243,30 @@ __device__ __forceinline__ void f_gather_loop(const FParams& p, Barriers<Cfg::ST
         for (int kb = 0; kb < p.num_kb; ++kb) {
             mbar_wait(&bars->empty[stage], phase ^ 1);
             const uint32_t dst0 = smem_base + stage * Cfg::STAGE_BYTES + dst_off;
-            if (STEM) {
-                gather_stem<NR, ROW_STEP * 128>(p.g, rs, kb, tid & 15, dst0);
-            } else {
-                const int tap = kb / p.g.cblocks;
-                gather_conv<NR, ROW_STEP * 128>(p.g, rs, tap, kb - tap * p.g.cblocks, chunk, dst0);
+            if (!(p.dbg & 1)) {
+                if (STEM) {
+                    gather_stem<NR, ROW_STEP * 128>(p.g, rs, kb, tid & 15, dst0);
+                } else {
+                    const int tap = (p.dbg & 2) ? 0 : kb / p.g.cblocks;
+                    gather_conv<NR, ROW_STEP * 128>(p.g, rs, tap, (p.dbg & 2) ? 0 : kb - tap * p.g.cblocks, chunk, dst0);
+                }
             }
-            cp_async_mbar_arrive_noinc(&bars->full[stage]);
+            if (p.dbg & 4) {
+                __syncwarp();
+                if ((tid & 31) == 0) cp_async_mbar_arrive_noinc(&bars->full[stage]);
+            } else {
+                cp_async_mbar_arrive_noinc(&bars->full[stage]);
+            }
             if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
     }
 }
 
-template <int BLOCK_N, bool A_TMA, bool B_MN, int EPI>
-__global__ void __launch_bounds__(FCfg<BLOCK_N, A_TMA, B_MN, EPI>::THREADS, 1)
+template <int BLOCK_N, int A_MODE, bool B_MN, int EPI>
+__global__ void __launch_bounds__(FCfg<BLOCK_N, A_MODE, B_MN, EPI>::THREADS, 1)
 igemm_f_kernel(const __grid_constant__ FParams p) {
-    using Cfg = FCfg<BLOCK_N, A_TMA, B_MN, EPI>;
+    using Cfg = FCfg<BLOCK_N, A_MODE, B_MN, EPI>;
+    constexpr bool A_TMA = A_MODE != AM_GATHER;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -269,7 +283,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
         if (A_TMA) tma_prefetch_desc(&p.tmA);
         tma_prefetch_desc(&p.tmB);
         for (int s = 0; s < STAGES; ++s) {
-            mbar_init(&bars->full[s], A_TMA ? 1 : 1 + NUM_GATHER_THREADS);
+            mbar_init(&bars->full[s], A_TMA ? 1 : 1 + ((p.dbg & 4) ? 4 : NUM_GATHER_THREADS));
             mbar_init(&bars->empty[s], 1);
         }
         for (int a = 0; a < 2; ++a) {
@@ -291,12 +305,29 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
                 const int m0 = (t / p.n_blocks) * BLOCK_M;
+                int iw0 = 0, ih0 = 0, in0 = 0;          // im2col: input-space position of the tile's first row
+                if (A_MODE == AM_IM2COL) {
+                    const int hw = p.g.OH * p.g.OW;
+                    in0 = m0 / hw;
+                    const int rem = m0 - in0 * hw;
+                    const int oh = rem / p.g.OW, ow = rem - oh * p.g.OW;
+                    if (p.g.mode == GM_FPROP) { iw0 = ow * p.g.stride - p.g.pad; ih0 = oh * p.g.stride - p.g.pad; }
+                    else { iw0 = ow + p.g.pad - (p.g.S - 1); ih0 = oh + p.g.pad - (p.g.R - 1); }
+                }
                 for (int kb = 0; kb < p.num_kb; ++kb) {
                     mbar_wait(&bars->empty[stage], phase ^ 1);
                     const uint32_t a_dst = smem_base + stage * Cfg::STAGE_BYTES;
                     const uint32_t b_dst = a_dst + A_TILE_BYTES;
                     mbar_arrive_expect_tx(&bars->full[stage], Cfg::B_TILE_BYTES + (A_TMA ? A_TILE_BYTES : 0));
-                    if (A_TMA) tma_load_2d(a_dst, &p.tmA, &bars->full[stage], kb * BLOCK_K, m0);
+                    if (A_MODE == AM_TILED) tma_load_2d(a_dst, &p.tmA, &bars->full[stage], kb * BLOCK_K, m0);
+                    if (A_MODE == AM_IM2COL) {
+                        const int tap = kb / p.g.cblocks;
+                        const int cb = kb - tap * p.g.cblocks;
+                        const int r = tap / p.g.S, s = tap - r * p.g.S;
+                        const bool fp = p.g.mode == GM_FPROP;
+                        tma_load_im2col(a_dst, &p.tmA, &bars->full[stage], cb * 64, iw0, ih0, in0,
+                                        fp ? s : p.g.S - 1 - s, fp ? r : p.g.R - 1 - r);
+                    }
                     if (!B_MN) {
                         tma_load_2d(b_dst, &p.tmB, &bars->full[stage], kb * BLOCK_K, n0);
                     } else {
@@ -355,7 +386,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
             const int acc = it & 1;
             const uint32_t acc_phase = (it >> 1) & 1;
             const long long m = (long long)(t / p.n_blocks) * BLOCK_M + q * 32 + lane;
-            const bool row_ok = m < p.M;
+            const bool row_ok = m < p.M;      // fp32 epilogue: one row per lane
             mbar_wait(&bars->tmem_full[acc], acc_phase);
             tc_fence_after();
 #pragma unroll
@@ -368,32 +399,46 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
 #pragma unroll
                 for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(raw[i]);
                 if (EPI == 0) {
-                    bf16* dst = p.out + (size_t)m * p.ldo + n0 + col;
-                    if (p.addend != nullptr && row_ok) {
-                        const uint4* ad = reinterpret_cast<const uint4*>(p.addend + (size_t)m * p.ldo + n0 + col);
+                    // Stage the warp's 32 rows x 64 B through shared memory so that global stores are
+                    // contiguous: 4 lanes cover one row's 64 B (two full sectors) instead of every lane
+                    // writing 16 B of a different row.  XOR on the 16-byte slot keeps both phases conflict-free.
+                    const uint32_t stg = smem_base + Cfg::STAGING_OFF + warp * 2048;
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            uint4 a4 = ad[j];
-                            const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+                    for (int j = 0; j < 4; ++j) {
+                        const uint32_t a = stg + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4);
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a),
+                                     "r"(pack_bf16x2(v[j * 8 + 0], v[j * 8 + 1])), "r"(pack_bf16x2(v[j * 8 + 2], v[j * 8 + 3])),
+                                     "r"(pack_bf16x2(v[j * 8 + 4], v[j * 8 + 5])), "r"(pack_bf16x2(v[j * 8 + 6], v[j * 8 + 7]))
+                                     : "memory");
+                    }
+                    __syncwarp();
+                    const long long m_base = (long long)(t / p.n_blocks) * BLOCK_M + q * 32;
 #pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                float2 f = unpack_bf16x2(aw[e]);
-                                v[j * 8 + e * 2] += f.x;
-                                v[j * 8 + e * 2 + 1] += f.y;
+                    for (int i = 0; i < 4; ++i) {
+                        const int piece = (int)lane + 32 * i;
+                        const int row = piece >> 2, pc = piece & 3;
+                        uint4 o;
+                        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                                     : "=r"(o.x), "=r"(o.y), "=r"(o.z), "=r"(o.w)
+                                     : "r"(stg + row * 64 + ((pc ^ ((row >> 1) & 3)) << 4)));
+                        const long long mr = m_base + row;
+                        if (mr < p.M) {
+                            const size_t off = (size_t)mr * p.ldo + n0 + col + pc * 8;
+                            if (p.addend != nullptr) {
+                                const uint4 a4 = *reinterpret_cast<const uint4*>(p.addend + off);
+                                const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+                                uint32_t ow[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+                                for (int e = 0; e < 4; ++e) {
+                                    const float2 f = unpack_bf16x2(aw[e]), g = unpack_bf16x2(ow[e]);
+                                    ow[e] = pack_bf16x2(f.x + g.x, f.y + g.y);
+                                }
+                                o = make_uint4(ow[0], ow[1], ow[2], ow[3]);
                             }
+                            *reinterpret_cast<uint4*>(p.out + off) = o;
                         }
                     }
-                    if (row_ok) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            uint4 o;
-                            o.x = pack_bf16x2(v[j * 8 + 0], v[j * 8 + 1]);
-                            o.y = pack_bf16x2(v[j * 8 + 2], v[j * 8 + 3]);
-                            o.z = pack_bf16x2(v[j * 8 + 4], v[j * 8 + 5]);
-                            o.w = pack_bf16x2(v[j * 8 + 6], v[j * 8 + 7]);
-                            reinterpret_cast<uint4*>(dst)[j] = o;
-                        }
-                    }
+                    __syncwarp();
                     if (do_stats) {
                         // Rows past M were zero-filled by the producers, so they add nothing.
                         float sq[32];
@@ -438,14 +483,14 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
 // ------------------------------------------------------------------------------------------
 // igemm_w
 // ------------------------------------------------------------------------------------------
-template <int NSUB, bool B_TMA>
+template <int NSUB, int B_MODE>
 struct WCfg {
     static constexpr int BLOCK_N = 64 * NSUB;
     static constexpr int A_BYTES = 2 * SUB_TILE_BYTES;                 // [64 pixels][128 cout]
     static constexpr int B_BYTES = NSUB * SUB_TILE_BYTES;              // [64 pixels][64*NSUB]
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int STAGES = NSUB >= 3 ? 4 : 6;
-    static constexpr int THREADS = B_TMA ? (MMA_WARP + 1) * 32 : (GATHER_WARP0 + 4) * 32;
+    static constexpr int THREADS = B_MODE != AM_GATHER ? (MMA_WARP + 1) * 32 : (GATHER_WARP0 + 4) * 32;
     static constexpr int TMEM_COLS = NSUB == 1 ? 64 : (NSUB == 2 ? 128 : 256);
     static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + sizeof(Barriers<STAGES>);
 };
@@ -489,9 +534,10 @@ __device__ __forceinline__ void w_gather_loop(const WParams& p, Barriers<Cfg::ST
     }
 }
 
-template <int NSUB, bool B_TMA>
-__global__ void __launch_bounds__(WCfg<NSUB, B_TMA>::THREADS, 1) igemm_w_kernel(const __grid_constant__ WParams p) {
-    using Cfg = WCfg<NSUB, B_TMA>;
+template <int NSUB, int B_MODE>
+__global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel(const __grid_constant__ WParams p) {
+    using Cfg = WCfg<NSUB, B_MODE>;
+    constexpr bool B_TMA = B_MODE != AM_GATHER;
     constexpr int STAGES = Cfg::STAGES;
     constexpr int BLOCK_N = Cfg::BLOCK_N;
     extern __shared__ uint8_t smem_raw[];
@@ -537,11 +583,28 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_TMA>::THREADS, 1) igemm_w_kernel(
                 mbar_arrive_expect_tx(&bars->full[stage], Cfg::A_BYTES + (B_TMA ? Cfg::B_BYTES : 0));
                 tma_load_2d(a_dst, &p.tmA, &bars->full[stage], m_blk * 128, kb * 64);
                 tma_load_2d(a_dst + SUB_TILE_BYTES, &p.tmA, &bars->full[stage], m_blk * 128 + 64, kb * 64);
-                if (B_TMA) {
+                if (B_MODE == AM_TILED) {
 #pragma unroll
                     for (int j = 0; j < NSUB; ++j)
                         tma_load_2d(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage],
                                     (n_blk * NSUB + j) * 64, kb * 64);
+                }
+                if (B_MODE == AM_IM2COL) {
+                    // 64 output pixels starting at kb*64: one im2col load per (tap, channel block) sub-tile
+                    const int hw = p.g.OH * p.g.OW;
+                    const int p0 = kb * 64;
+                    const int n0 = p0 / hw;
+                    const int rem = p0 - n0 * hw;
+                    const int oh = rem / p.g.OW, ow = rem - oh * p.g.OW;
+                    const int iw0 = ow * p.g.stride - p.g.pad, ih0 = oh * p.g.stride - p.g.pad;
+#pragma unroll
+                    for (int j = 0; j < NSUB; ++j) {
+                        const int sj = n_blk * NSUB + j;
+                        const int tap = sj / p.g.cblocks;
+                        const int cb = sj - tap * p.g.cblocks;
+                        const int r = tap / p.g.S, s_ = tap - r * p.g.S;
+                        tma_load_im2col(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage], cb * 64, iw0, ih0, n0, s_, r);
+                    }
                 }
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
@@ -601,10 +664,10 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_TMA>::THREADS, 1) igemm_w_kernel(
 // ------------------------------------------------------------------------------------------
 // Host launchers
 // ------------------------------------------------------------------------------------------
-template <int BLOCK_N, bool A_TMA, bool B_MN, int EPI>
+template <int BLOCK_N, int A_MODE, bool B_MN, int EPI>
 int launch_f(FParams& p, cudaStream_t stream) {
-    using Cfg = FCfg<BLOCK_N, A_TMA, B_MN, EPI>;
-    auto kern = igemm_f_kernel<BLOCK_N, A_TMA, B_MN, EPI>;
+    using Cfg = FCfg<BLOCK_N, A_MODE, B_MN, EPI>;
+    auto kern = igemm_f_kernel<BLOCK_N, A_MODE, B_MN, EPI>;
     static bool configured[64] = {false};
     int dev = 0;
     PTD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -614,6 +677,7 @@ int launch_f(FParams& p, cudaStream_t stream) {
     }
     p.m_blocks = ceil_div_i(p.M, BLOCK_M);
     p.n_blocks = ceil_div_i(p.N, BLOCK_N);
+    { const char* e = getenv("PTD_IGEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
     const int tiles = p.m_blocks * p.n_blocks;
     int grid = ptd_num_sms();
     grid = (grid / p.n_blocks) * p.n_blocks;      // fixed n block per CTA (register-resident BN partial sums)
@@ -624,12 +688,12 @@ int launch_f(FParams& p, cudaStream_t stream) {
     return PTD_OK;
 }
 
-template <bool A_TMA, bool B_MN, int EPI>
+template <int A_MODE, bool B_MN, int EPI>
 int dispatch_f(FParams& p, int block_n, cudaStream_t stream) {
     switch (block_n) {
-        case 64: return launch_f<64, A_TMA, B_MN, EPI>(p, stream);
-        case 128: return launch_f<128, A_TMA, B_MN, EPI>(p, stream);
-        case 256: return launch_f<256, A_TMA, B_MN, EPI>(p, stream);
+        case 64: return launch_f<64, A_MODE, B_MN, EPI>(p, stream);
+        case 128: return launch_f<128, A_MODE, B_MN, EPI>(p, stream);
+        case 256: return launch_f<256, A_MODE, B_MN, EPI>(p, stream);
     }
     ptd_set_error("igemm_f: unsupported BLOCK_N %d", block_n);
     return PTD_ERR_ARG;
@@ -641,10 +705,10 @@ int pick_block_n(int n) {
     return 64;
 }
 
-template <int NSUB, bool B_TMA>
+template <int NSUB, int B_MODE>
 int launch_w(WParams& p, cudaStream_t stream) {
-    using Cfg = WCfg<NSUB, B_TMA>;
-    auto kern = igemm_w_kernel<NSUB, B_TMA>;
+    using Cfg = WCfg<NSUB, B_MODE>;
+    auto kern = igemm_w_kernel<NSUB, B_MODE>;
     static bool configured[64] = {false};
     int dev = 0;
     PTD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -666,13 +730,13 @@ int launch_w(WParams& p, cudaStream_t stream) {
     return PTD_OK;
 }
 
-template <bool B_TMA>
+template <int B_MODE>
 int dispatch_w(WParams& p, int nsub, cudaStream_t stream) {
     switch (nsub) {
-        case 1: return launch_w<1, B_TMA>(p, stream);
-        case 2: return launch_w<2, B_TMA>(p, stream);
-        case 3: return launch_w<3, B_TMA>(p, stream);
-        case 4: return launch_w<4, B_TMA>(p, stream);
+        case 1: return launch_w<1, B_MODE>(p, stream);
+        case 2: return launch_w<2, B_MODE>(p, stream);
+        case 3: return launch_w<3, B_MODE>(p, stream);
+        case 4: return launch_w<4, B_MODE>(p, stream);
     }
     ptd_set_error("igemm_w: unsupported sub-tile count %d", nsub);
     return PTD_ERR_ARG;
@@ -683,6 +747,12 @@ int pick_nsub(int ksub) {   // ksub = Kw / 64
     if (ksub % 3 == 0) return 3;
     if (ksub % 2 == 0) return 2;
     return 1;
+}
+
+bool force_gather() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("PTD_IGEMM_FORCE_GATHER"); v = (e && atoi(e)) ? 1 : 0; }
+    return v == 1;
 }
 
 void fill_geom(ConvGeom& g, const bf16* src, int H, int W, int C, int OH, int OW, int R, int S, int stride, int pad,
@@ -712,10 +782,16 @@ extern "C" int ptd_conv_fprop(const void* x, const void* w, void* y, float* stat
     if (plain) {
         rc = ptd_make_tmap_2d_bf16(&p.tmA, x, Cin, p.M, (uint64_t)Cin * 2, 64, BLOCK_M);
         if (rc) return rc;
-        return dispatch_f<true, false, 0>(p, bn, stream);
+        return dispatch_f<AM_TILED, false, 0>(p, bn, stream);
     }
     fill_geom(p.g, (const bf16*)x, H, W, Cin, OH, OW, R, S, stride, pad, GM_FPROP);
-    return dispatch_f<false, false, 0>(p, bn, stream);
+    if (!force_gather()) {
+        // walk output pixels over the padded input with TMA im2col: corners as in CUTLASS' fprop
+        rc = ptd_make_tmap_im2col_bf16(&p.tmA, x, Cin, W, H, N, -pad, -pad, pad - (S - 1), pad - (R - 1), BLOCK_M, stride);
+        if (rc) return rc;
+        return dispatch_f<AM_IM2COL, false, 0>(p, bn, stream);
+    }
+    return dispatch_f<AM_GATHER, false, 0>(p, bn, stream);
 }
 
 extern "C" int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const void* addend, int N, int H, int W,
@@ -737,10 +813,17 @@ extern "C" int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const voi
     if (plain) {
         rc = ptd_make_tmap_2d_bf16(&p.tmA, dy, Cout, p.M, (uint64_t)Cout * 2, 64, BLOCK_M);
         if (rc) return rc;
-        return dispatch_f<true, true, 0>(p, bn, stream);
+        return dispatch_f<AM_TILED, true, 0>(p, bn, stream);
     }
     fill_geom(p.g, (const bf16*)dy, OH, OW, Cout, H, W, R, S, stride, pad, GM_DGRAD);
-    return dispatch_f<false, true, 0>(p, bn, stream);
+    if (stride == 1 && !force_gather()) {
+        // dx pixel (h, w) reads dy at (h + pad - r, w + pad - s): im2col over dy with the tap order mirrored
+        rc = ptd_make_tmap_im2col_bf16(&p.tmA, dy, Cout, OW, OH, N, pad - (S - 1), pad - (R - 1),
+                                       pad - (S - 1) + (W - OW), pad - (R - 1) + (H - OH), BLOCK_M, 1);
+        if (rc) return rc;
+        return dispatch_f<AM_IM2COL, true, 0>(p, bn, stream);
+    }
+    return dispatch_f<AM_GATHER, true, 0>(p, bn, stream);
 }
 
 extern "C" int ptd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int R,
@@ -758,10 +841,15 @@ extern "C" int ptd_conv_wgrad(const void* x, const void* dy, float* dw, int N, i
     if (plain) {
         rc = ptd_make_tmap_2d_bf16(&p.tmB, x, Cin, p.P, (uint64_t)Cin * 2, 64, 64);
         if (rc) return rc;
-        return dispatch_w<true>(p, nsub, stream);
+        return dispatch_w<AM_TILED>(p, nsub, stream);
     }
     fill_geom(p.g, (const bf16*)x, H, W, Cin, OH, OW, R, S, stride, pad, GM_FPROP);
-    return dispatch_w<false>(p, nsub, stream);
+    if (!force_gather()) {
+        rc = ptd_make_tmap_im2col_bf16(&p.tmB, x, Cin, W, H, N, -pad, -pad, pad - (S - 1), pad - (R - 1), 64, stride);
+        if (rc) return rc;
+        return dispatch_w<AM_IM2COL>(p, nsub, stream);
+    }
+    return dispatch_w<AM_GATHER>(p, nsub, stream);
 }
 
 // Stem: x4 is NHWC with 4 channels (3 real + 1 zero), w4 is [64][8][8][4] (filter row 7 / tap 7 / channel 3 zero).
@@ -776,7 +864,7 @@ extern "C" int ptd_stem_fprop(const void* x4, const void* w4, void* y, float* st
     int rc = ptd_make_tmap_2d_bf16(&p.tmB, w4, 256, 64, 512, 64, 64);
     if (rc) return rc;
     fill_geom(p.g, (const bf16*)x4, H, W, 4, OH, OW, 7, 7, 2, 3, GM_STEM);
-    return dispatch_f<false, false, 0>(p, 64, stream);
+    return dispatch_f<AM_GATHER, false, 0>(p, 64, stream);
 }
 
 extern "C" int ptd_stem_wgrad(const void* x4, const void* dy, float* dw4, int N, int H, int W, void* stream_) {
@@ -788,7 +876,7 @@ extern "C" int ptd_stem_wgrad(const void* x4, const void* dy, float* dw4, int N,
     int rc = ptd_make_tmap_2d_bf16(&p.tmA, dy, 64, p.P, 128, 64, 64);
     if (rc) return rc;
     fill_geom(p.g, (const bf16*)x4, H, W, 4, OH, OW, 7, 7, 2, 3, GM_STEM);
-    return dispatch_w<false>(p, 4, stream);
+    return dispatch_w<AM_GATHER>(p, 4, stream);
 }
 
 // Classifier / generic dense layers.  a: [M][K] bf16, w: [N][K] bf16.
@@ -805,7 +893,7 @@ extern "C" int ptd_linear_fwd(const void* a, const void* w, const float* bias, f
     if (rc) return rc;
     rc = ptd_make_tmap_2d_bf16(&p.tmB, w, K, N, (uint64_t)K * 2, 64, bn);
     if (rc) return rc;
-    return dispatch_f<true, false, 1>(p, bn, (cudaStream_t)stream_);
+    return dispatch_f<AM_TILED, false, 1>(p, bn, (cudaStream_t)stream_);
 }
 
 //   data gradient : da_bf16[M][K] = dout_bf16[M][N] * w[N][K]        (K % 64 == 0)
@@ -821,7 +909,7 @@ extern "C" int ptd_linear_dgrad(const void* dout, const void* w, void* da, int M
     if (rc) return rc;
     rc = ptd_make_tmap_2d_bf16(&p.tmB, w, K, N, (uint64_t)K * 2, 64, 64);
     if (rc) return rc;
-    return dispatch_f<true, true, 0>(p, bn, (cudaStream_t)stream_);
+    return dispatch_f<AM_TILED, true, 0>(p, bn, (cudaStream_t)stream_);
 }
 
 //   weight gradient : dw_f32[N][K] += dout_bf16[M][N]^T * a_bf16[M][K]   (K % 64 == 0)
@@ -834,5 +922,5 @@ extern "C" int ptd_linear_wgrad(const void* a, const void* dout, float* dw, int 
     if (rc) return rc;
     rc = ptd_make_tmap_2d_bf16(&p.tmB, a, K, M, (uint64_t)K * 2, 64, 64);
     if (rc) return rc;
-    return dispatch_w<true>(p, pick_nsub(K / 64), (cudaStream_t)stream_);
+    return dispatch_w<AM_TILED>(p, pick_nsub(K / 64), (cudaStream_t)stream_);
 }

@@ -45,8 +45,23 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
     return t;
 }
 
+// Sequence numbers live in device memory next to the signal pad (one counter per block index, local to
+// the rank): a kernel reads its block's counter, uses counter+1 / counter+2 for its two barriers and
+// stores counter+2 back.  Every rank runs the same collectives with the same grids on a given pad, so
+// the counters advance in lock step without any host involvement - which also makes the collectives
+// replayable from a CUDA graph (a host-side sequence argument would be frozen at capture time).
+__device__ __forceinline__ uint32_t seq_begin(const PeerPtrs& pp, int rank) {
+    __shared__ uint32_t s_seq;
+    if (threadIdx.x == 0) s_seq = pp.pad[rank][MAX_BLOCKS * MAX_WORLD + blockIdx.x];
+    __syncthreads();
+    return s_seq + 1;
+}
+__device__ __forceinline__ void seq_end(const PeerPtrs& pp, int rank, uint32_t last_used) {
+    if (threadIdx.x == 0) pp.pad[rank][MAX_BLOCKS * MAX_WORLD + blockIdx.x] = last_used;
+}
+
 // Block-level barrier across ranks: block b of every rank meets block b of every other rank.
-// Flags only grow (seq is a host-side counter shared by construction), so a late waiter still passes.
+// Flags only grow, so a late waiter still passes.
 __device__ __forceinline__ void rank_barrier(const PeerPtrs& pp, int rank, int world, uint32_t seq) {
     __syncthreads();
     if ((int)threadIdx.x < world) {
@@ -85,8 +100,8 @@ __device__ __forceinline__ void st_u4(uint4* p, const uint4& v) {
 // ---- two-shot all-reduce, fp32 storage ------------------------------------------------------------
 // n4 = number of float4 elements (buffer length is padded to a multiple of 4 floats by the caller).
 template <int WORLD>
-__global__ void __launch_bounds__(AR_THREADS) allreduce_f32_kernel(PeerPtrs pp, int rank, long long n4, float scale,
-                                                                   uint32_t seq) {
+__global__ void __launch_bounds__(AR_THREADS) allreduce_f32_kernel(PeerPtrs pp, int rank, long long n4, float scale) {
+    const uint32_t seq = seq_begin(pp, rank);
     rank_barrier(pp, rank, WORLD, seq);
     const long long per = (n4 + WORLD - 1) / WORLD;
     const long long begin = min(n4, per * rank), end = min(n4, begin + per);
@@ -127,12 +142,13 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_f32_kernel(PeerPtrs pp, 
         for (int r = 0; r < WORLD; ++r) st_f4(reinterpret_cast<float4*>(pp.buf[(rank + r) % WORLD]) + i, acc);
     }
     rank_barrier(pp, rank, WORLD, seq + 1);
+    seq_end(pp, rank, seq + 1);
 }
 
 // ---- two-shot all-reduce, bf16 storage (fp32 accumulate) -----------------------------------------------
 template <int WORLD>
-__global__ void __launch_bounds__(AR_THREADS) allreduce_bf16_kernel(PeerPtrs pp, int rank, long long n8, float scale,
-                                                                    uint32_t seq) {
+__global__ void __launch_bounds__(AR_THREADS) allreduce_bf16_kernel(PeerPtrs pp, int rank, long long n8, float scale) {
+    const uint32_t seq = seq_begin(pp, rank);
     rank_barrier(pp, rank, WORLD, seq);
     const long long per = (n8 + WORLD - 1) / WORLD;
     const long long begin = min(n8, per * rank), end = min(n8, begin + per);
@@ -163,11 +179,13 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_bf16_kernel(PeerPtrs pp,
         for (int r = 0; r < WORLD; ++r) st_u4(reinterpret_cast<uint4*>(pp.buf[(rank + r) % WORLD]) + i, o);
     }
     rank_barrier(pp, rank, WORLD, seq + 1);
+    seq_end(pp, rank, seq + 1);
 }
 
 // ---- broadcast: every non-root rank pulls the root's buffer ----------------------------------------------
 __global__ void __launch_bounds__(AR_THREADS) broadcast_pull_kernel(PeerPtrs pp, int rank, int world, int root,
-                                                                    long long n16, uint32_t seq) {
+                                                                    long long n16) {
+    const uint32_t seq = seq_begin(pp, rank);
     rank_barrier(pp, rank, world, seq);                 // root's data is final
     if (rank != root) {
         const uint4* src = reinterpret_cast<const uint4*>(pp.buf[root]);
@@ -181,10 +199,13 @@ __global__ void __launch_bounds__(AR_THREADS) broadcast_pull_kernel(PeerPtrs pp,
         for (; i < n16; i += stride) dst[i] = ld_u4(src + i);
     }
     rank_barrier(pp, rank, world, seq + 1);             // root may overwrite its buffer again
+    seq_end(pp, rank, seq + 1);
 }
 
-__global__ void __launch_bounds__(AR_THREADS) barrier_only_kernel(PeerPtrs pp, int rank, int world, uint32_t seq) {
+__global__ void __launch_bounds__(AR_THREADS) barrier_only_kernel(PeerPtrs pp, int rank, int world) {
+    const uint32_t seq = seq_begin(pp, rank);
     rank_barrier(pp, rank, world, seq);
+    seq_end(pp, rank, seq);
 }
 
 // ---- single-process helpers (DataParallel): device-issued copies / reductions over peer pointers ----------
@@ -278,14 +299,14 @@ extern "C" int ptd_p2p_enable_peer_access(int dev, int peer) {
     PTD_CUDA_CHECK(e);
     return PTD_OK;
 }
-extern "C" int ptd_p2p_pad_bytes() { return MAX_BLOCKS * MAX_WORLD * (int)sizeof(uint32_t); }
+extern "C" int ptd_p2p_pad_bytes() { return (MAX_BLOCKS * MAX_WORLD + MAX_BLOCKS) * (int)sizeof(uint32_t); }
 extern "C" int ptd_p2p_max_blocks() { return MAX_BLOCKS; }
 
 // ---- collectives --------------------------------------------------------------------------------------------
 // bufs / pads: HOST arrays of `world` device pointers (this rank's mapping of every rank's buffer / signal pad).
-// `seq` must be the same on every rank and grow by 2 per call on a given signal pad.
+// Kernels sharing a signal pad must be stream-ordered with respect to each other.
 extern "C" int ptd_allreduce_inplace(const void* const* bufs, const void* const* pads, int rank, int world,
-                                     long long numel, int is_bf16, float scale, unsigned seq, int blocks, void* stream) {
+                                     long long numel, int is_bf16, float scale, int blocks, void* stream) {
     PeerPtrs pp;
     int rc = fill_peers(pp, bufs, pads, world);
     if (rc) return rc;
@@ -296,8 +317,8 @@ extern "C" int ptd_allreduce_inplace(const void* const* bufs, const void* const*
     cudaStream_t st = (cudaStream_t)stream;
 #define PTD_AR(W)                                                                                   \
     case W:                                                                                         \
-        if (is_bf16) allreduce_bf16_kernel<W><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale, seq); \
-        else allreduce_f32_kernel<W><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale, seq);      \
+        if (is_bf16) allreduce_bf16_kernel<W><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale); \
+        else allreduce_f32_kernel<W><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale);      \
         break;
     switch (world) {
         PTD_AR(1) PTD_AR(2) PTD_AR(3) PTD_AR(4) PTD_AR(5) PTD_AR(6) PTD_AR(7) PTD_AR(8)
@@ -308,23 +329,23 @@ extern "C" int ptd_allreduce_inplace(const void* const* bufs, const void* const*
 }
 
 extern "C" int ptd_broadcast_inplace(const void* const* bufs, const void* const* pads, int rank, int world, int root,
-                                     long long nbytes, unsigned seq, int blocks, void* stream) {
+                                     long long nbytes, int blocks, void* stream) {
     PeerPtrs pp;
     int rc = fill_peers(pp, bufs, pads, world);
     if (rc) return rc;
     PTD_REQUIRE(nbytes % 16 == 0, "broadcast: nbytes (%lld) must be a multiple of 16", nbytes);
     const int grid = pick_blocks(nbytes / 16, blocks);
-    broadcast_pull_kernel<<<grid, AR_THREADS, 0, (cudaStream_t)stream>>>(pp, rank, world, root, nbytes / 16, seq);
+    broadcast_pull_kernel<<<grid, AR_THREADS, 0, (cudaStream_t)stream>>>(pp, rank, world, root, nbytes / 16);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }
 
-extern "C" int ptd_p2p_barrier(const void* const* pads, int rank, int world, unsigned seq, void* stream) {
+extern "C" int ptd_p2p_barrier(const void* const* pads, int rank, int world, void* stream) {
     PeerPtrs pp;
     const void* none[MAX_WORLD] = {nullptr};
     int rc = fill_peers(pp, none, pads, world);
     if (rc) return rc;
-    barrier_only_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pp, rank, world, seq);
+    barrier_only_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pp, rank, world);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }

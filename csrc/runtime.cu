@@ -54,6 +54,62 @@ static EncodeTiledFn get_encode() {
     return fn;
 }
 
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*,
+                                   CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                   CUtensorMapFloatOOBfill);
+
+static EncodeIm2colFn get_encode_im2col() {
+    static EncodeIm2colFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeIm2colFn>(p);
+    });
+    return fn;
+}
+
+// NHWC bf16 activation [N][H][W][C] as an im2col TMA descriptor.  A load names the input-space position of
+// the first pixel's top-left filter tap (c, w, h, n) plus an unsigned tap offset; the unit then walks
+// `pixels` base positions (stride `stride` in w and h, wrapping inside the bounding box
+// [lower, extent - 1 + upper]) and fetches `64` channels per pixel, zero-filling whatever falls outside the
+// image.  128-byte swizzle, i.e. the same shared-memory image as a tiled [pixels][64] load.
+int ptd_make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int W, int H, int N, int lower_w, int lower_h,
+                              int upper_w, int upper_h, int pixels, int stride) {
+    EncodeIm2colFn enc = get_encode_im2col();
+    if (!enc) {
+        ptd_set_error("cuTensorMapEncodeIm2col entry point not available (no CUDA driver?)");
+        return PTD_ERR_CUDA;
+    }
+    if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || C % 8 != 0) {
+        ptd_set_error("im2col TMA needs a 16-byte aligned base (%p) and C %% 8 == 0 (C=%d)", base, C);
+        return PTD_ERR_ARG;
+    }
+    cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+    int lower[2] = {lower_w, lower_h};
+    int upper[2] = {upper_w, upper_h};
+    cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lower, upper, 64,
+                     (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        ptd_set_error("cuTensorMapEncodeIm2col failed: %d (C=%d W=%d H=%d N=%d lower=%d,%d upper=%d,%d pixels=%d stride=%d)",
+                      (int)r, C, W, H, N, lower_w, lower_h, upper_w, upper_h, pixels, stride);
+        return PTD_ERR_CUDA;
+    }
+    // Same driver workaround CUTLASS applies (copy_traits_sm90_im2col.hpp): for tensors under 128 KiB drivers up to
+    // 13.1 set a descriptor bit that makes the load misbehave; clear it.
+    int drv = 0;
+    if (cudaDriverGetVersion(&drv) == cudaSuccess && drv <= 13010 &&
+        (unsigned long long)N * H * W * C * 2ull < 131072ull)
+        reinterpret_cast<uint64_t*>(out)[1] &= ~(1ull << 21);
+    return PTD_OK;
+}
+
 int ptd_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t rows, uint64_t row_pitch_bytes,
                           uint32_t box_inner, uint32_t box_rows) {
     EncodeTiledFn enc = get_encode();

@@ -8,3 +8,7 @@
 // Out-of-bounds elements of a box read as zero.
 int ptd_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t rows, uint64_t row_pitch_bytes,
                           uint32_t box_inner, uint32_t box_rows);
+
+// im2col-mode descriptor over an NHWC bf16 activation (see runtime.cu for the walk it describes).
+int ptd_make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int W, int H, int N, int lower_w, int lower_h,
+                              int upper_w, int upper_h, int pixels, int stride);

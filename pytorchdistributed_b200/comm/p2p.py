@@ -32,9 +32,9 @@ _lib.register("ptd_p2p_ipc_close", [P])
 _lib.register("ptd_p2p_enable_peer_access", [I, I])
 _lib.register("ptd_p2p_pad_bytes", [])
 _lib.register("ptd_p2p_max_blocks", [])
-_lib.register("ptd_allreduce_inplace", [P, P, I, I, L, I, F, U, I, P])
-_lib.register("ptd_broadcast_inplace", [P, P, I, I, I, L, U, I, P])
-_lib.register("ptd_p2p_barrier", [P, I, I, U, P])
+_lib.register("ptd_allreduce_inplace", [P, P, I, I, L, I, F, I, P])
+_lib.register("ptd_broadcast_inplace", [P, P, I, I, I, L, I, P])
+_lib.register("ptd_p2p_barrier", [P, I, I, P])
 _lib.register("ptd_peer_copy", [P, P, L, P])
 _lib.register("ptd_reduce_sum_f32", [P, P, I, L, F, I, P])
 
@@ -128,10 +128,10 @@ class P2PCollectives:
         self.world = dist.get_world_size(group)
         if self.world > 8:
             raise RuntimeError("p2p backend covers one NVSwitch domain (<= 8 ranks)")
-        # Flags on one signal pad only grow, so kernels sharing a pad must be stream-ordered.  Two channels:
+        # Flags on one signal pad only grow (sequence counters live on the device next to the pad), so kernels
+        # sharing a pad must be stream-ordered.  Two channels:
         # 0 = gradient all-reduce (DDP's communication stream), 1 = broadcasts (the compute stream).
         self.pads = [SymmetricBuffer(_lib.call_ret("ptd_p2p_pad_bytes"), device, group) for _ in range(2)]
-        self.seqs = [2, 2]
         self.blocks = int(os.environ.get("PTDB200_AR_BLOCKS", "0"))
         self._bufs: List[SymmetricBuffer] = []
         self._by_ptr = {}
@@ -151,11 +151,6 @@ class P2PCollectives:
             raise RuntimeError("p2p collective on a tensor that was not allocated by P2PCollectives.alloc()")
         return sb
 
-    def _next_seq(self, channel: int) -> int:
-        s = self.seqs[channel]
-        self.seqs[channel] = (s + 2) & 0xFFFFFFFF       # each kernel uses seq and seq + 1
-        return s
-
     def all_reduce_avg(self, flat: torch.Tensor, scale: Optional[float] = None) -> None:
         sb = self._sym(flat)
         n = flat.numel()
@@ -166,7 +161,7 @@ class P2PCollectives:
         n_pad = (n + per - 1) // per * per               # buffers are padded to 256 B, the tail is ours
         _lib.call("ptd_allreduce_inplace", ctypes.cast(sb.ptr_array, P), ctypes.cast(self.pads[0].ptr_array, P),
                   self.rank, self.world, n_pad, int(is_bf16), float(1.0 / self.world if scale is None else scale),
-                  self._next_seq(0), self.blocks, torch.cuda.current_stream(self.device).cuda_stream)
+                  self.blocks, torch.cuda.current_stream(self.device).cuda_stream)
 
     def broadcast(self, flat: torch.Tensor, src: int = 0) -> None:
         sb = self._by_ptr.get(flat.data_ptr())
@@ -179,11 +174,11 @@ class P2PCollectives:
             return
         nbytes = (flat.numel() * flat.element_size() + 15) // 16 * 16
         _lib.call("ptd_broadcast_inplace", ctypes.cast(sb.ptr_array, P), ctypes.cast(self.pads[1].ptr_array, P),
-                  self.rank, self.world, src, nbytes, self._next_seq(1), self.blocks,
+                  self.rank, self.world, src, nbytes, self.blocks,
                   torch.cuda.current_stream(self.device).cuda_stream)
 
     def barrier(self) -> None:
-        _lib.call("ptd_p2p_barrier", ctypes.cast(self.pads[1].ptr_array, P), self.rank, self.world, self._next_seq(1),
+        _lib.call("ptd_p2p_barrier", ctypes.cast(self.pads[1].ptr_array, P), self.rank, self.world,
                   torch.cuda.current_stream(self.device).cuda_stream)
 
     def close(self) -> None:

@@ -1,0 +1,139 @@
+"""Model-parallel and micro-batch pipeline-parallel ResNet-50 over two GPUs of one process.
+
+* ``ModelParallelResNet50``    - the reference's layer split (``R/03 模型并行/03_model_parallel.ipynb#cell5``):
+  ``seq1`` = conv1..layer2 on the first device, ``seq2`` = layer3..avgpool and ``fc`` on the second;
+  ``forward`` = ``seq1(x) -> transfer -> seq2 -> fc``.
+* ``PipelineParallelResNet50(split_size=20)`` (``#cell12``): the batch is cut into ``split_size`` micro-batches
+  and the two stages overlap - stage 2 works on micro-batch i while stage 1 computes i+1.  Uneven last
+  split allowed (``torch.split`` semantics).  Backward is plain autograd over the whole graph (all forward,
+  then all backward, GPipe-like without recompute), as in the reference.
+
+What changes underneath: activations and activation gradients cross the stage boundary as bf16 NHWC with an
+NCCL send/recv pair on per-device side streams (``comm/nccl_p2p.py``), ordered against the compute streams
+with events, so the copy of micro-batch i overlaps the compute of i+1 on both devices; the stages run on
+the sm_100a kernels.  ``transfer="p2p"`` swaps NCCL for our device-issued peer copy kernel.
+Unlike the reference class this one does not double-register sub-modules (quirk 5 in SURVEY.md 2.6):
+``state_dict()`` has torchvision's 320 keys; ``reference_state_dict()`` adds the ``seq1.*``/``seq2.*`` aliases.
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+from torch import nn
+
+from .. import _lib
+from ..comm import p2p as _p2p  # noqa: F401
+from ..models.resnet import Bottleneck, ResNet
+
+_GROUPS = {}
+
+
+def _group(d0: int, d1: int):
+    from ..comm.nccl_p2p import LocalNcclGroup
+    key = (d0, d1)
+    if key not in _GROUPS:
+        _GROUPS[key] = LocalNcclGroup([d0, d1])
+    return _GROUPS[key]
+
+
+class _Transfer(torch.autograd.Function):
+    """Move a tensor to another device on side streams; the gradient travels back the same way."""
+
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, dst_index: int, mode: str):
+        ctx.src_index, ctx.dst_index, ctx.mode = x.device.index, dst_index, mode
+        return _Transfer._move(x, dst_index, mode)
+
+    @staticmethod
+    def backward(ctx, g: torch.Tensor):
+        return _Transfer._move(g, ctx.src_index, ctx.mode), None, None
+
+    @staticmethod
+    def _move(t: torch.Tensor, dst_index: int, mode: str) -> torch.Tensor:
+        src_dev, dst_dev = t.device, torch.device("cuda", dst_index)
+        cl = t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last) and not t.is_contiguous()
+        src = t if (t.is_contiguous() or cl) else t.contiguous()
+        with torch.cuda.device(dst_dev):
+            out = torch.empty_like(src, device=dst_dev)         # same strides (keeps NHWC)
+        if mode == "nccl":
+            done = _group(min(src_dev.index, dst_index), max(src_dev.index, dst_index)).send_recv(
+                _flat(src), _flat(out))
+            torch.cuda.current_stream(dst_dev).wait_event(done)
+        else:
+            ready = torch.cuda.Event()
+            ready.record(torch.cuda.current_stream(src_dev))
+            with torch.cuda.device(dst_dev):
+                st = torch.cuda.current_stream(dst_dev)
+                st.wait_event(ready)
+                nb = src.numel() * src.element_size()
+                if nb % 16 == 0:
+                    _lib.call("ptd_peer_copy", out, src, nb, st.cuda_stream)   # the consumer pulls over NVLink
+                else:
+                    out.copy_(src, non_blocking=True)
+            src.record_stream(torch.cuda.current_stream(dst_dev))
+        return out
+
+
+def _flat(t: torch.Tensor) -> torch.Tensor:
+    return torch.as_strided(t, (t.numel(),), (1,), t.storage_offset())
+
+
+class ModelParallelResNet50(ResNet):
+    def __init__(self, num_classes: int = 1000, devices=("cuda:0", "cuda:1"), transfer: str = "nccl") -> None:
+        super().__init__(block=Bottleneck, layers=[3, 4, 6, 3], num_classes=num_classes)
+        self.devices = [torch.device(d) for d in devices]
+        self.transfer = transfer
+        self._on_gpu = torch.cuda.is_available() and all(d.type == "cuda" for d in self.devices)
+        seq1, seq2, fc = self.stage_modules()
+        # plain attributes (not registered a second time): state_dict keeps torchvision's keys
+        object.__setattr__(self, "seq1", seq1)
+        object.__setattr__(self, "seq2", seq2)
+        if self._on_gpu:
+            seq1.to(self.devices[0])
+            seq2.to(self.devices[1])
+            fc.to(self.devices[1])
+
+    def _boundary(self, x: torch.Tensor) -> torch.Tensor:
+        if not self._on_gpu:
+            return x
+        return _Transfer.apply(x, self.devices[1].index, self.transfer)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        x = self._boundary(self.seq1(x))
+        x = self.seq2(x)
+        return self.fc(x.view(x.size(0), -1))
+
+    def reference_state_dict(self):
+        """state_dict with the alias keys the reference class produces by registering modules twice."""
+        sd = dict(self.state_dict())
+        for k, v in list(sd.items()):
+            head = k.split(".")[0]
+            m1 = {"conv1": "seq1.0", "bn1": "seq1.1", "layer1": "seq1.4", "layer2": "seq1.5"}
+            m2 = {"layer3": "seq2.0", "layer4": "seq2.1"}
+            if head in m1:
+                sd[m1[head] + k[len(head):]] = v
+            elif head in m2:
+                sd[m2[head] + k[len(head):]] = v
+        return sd
+
+
+class PipelineParallelResNet50(ModelParallelResNet50):
+    def __init__(self, split_size: int = 20, *args, **kwargs) -> None:
+        super().__init__(*args, **kwargs)
+        self.split_size = split_size
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        splits = iter(x.split(self.split_size, dim=0))
+        s_next = next(splits)
+        s_prev = self._boundary(self.seq1(s_next))
+        ret: List[torch.Tensor] = []
+        for s_next in splits:
+            # A. s_prev runs on the second device
+            s_prev = self.seq2(s_prev)
+            ret.append(self.fc(s_prev.view(s_prev.size(0), -1)))
+            # B. s_next runs on the first device, concurrently with A; its transfer rides the side streams
+            s_prev = self._boundary(self.seq1(s_next))
+        s_prev = self.seq2(s_prev)
+        ret.append(self.fc(s_prev.view(s_prev.size(0), -1)))
+        return torch.cat(ret)

@@ -31,7 +31,7 @@ class Trainer:
     def __init__(self, model: torch.nn.Module, train_dataloader: DataLoader, optimizer: torch.optim.Optimizer,
                  gpu_id: Optional[int] = None, *, save_every: int = 0, snapshot_path: str = "snapshot.pt",
                  loss_fn: Optional[Callable] = None, resume: bool = False, ddp_kwargs: Optional[dict] = None,
-                 quiet: bool = False) -> None:
+                 quiet: bool = False, cuda_graph: bool = False, graph_warmup: int = 3) -> None:
         self.gpu_id = int(os.environ.get("LOCAL_RANK", 0)) if gpu_id is None else gpu_id
         self.device = torch.device("cuda", self.gpu_id) if torch.cuda.is_available() else torch.device("cpu")
         self.model = model.to(self.device)
@@ -49,16 +49,56 @@ class Trainer:
         self.model = DDP(self.model, device_ids=[self.gpu_id] if self.device.type == "cuda" else None, **kw)
         if hasattr(optimizer, "attach_model"):
             optimizer.attach_model(self.model.module)
+        # CUDA-graph replay of the whole step (zero_grad .. optimizer.step) once shapes have settled
+        self.cuda_graph = bool(cuda_graph) and self.device.type == "cuda"
+        self._graph_warmup = max(int(graph_warmup), 2)
+        self._eager_steps = 0
+        self._graph = None
+        self._graph_failed = False
 
     # -- one optimisation step ----------------------------------------------------------------
-    def _run_batch(self, xs, ys):
+    def _step_eager(self, xs, ys):
         self.optimizer.zero_grad()
         output = self.model(xs)
         loss = self.loss_fn(output, ys)
         loss.backward()
         self.optimizer.step()
-        self.last_loss = loss.detach()
+        return loss.detach()
+
+    def _run_batch(self, xs, ys):
+        if self.cuda_graph and not self._graph_failed:
+            g = self._graph
+            if g is not None and g["x"].shape == xs.shape and g["y"].shape == ys.shape and g["x"].dtype == xs.dtype:
+                g["x"].copy_(xs, non_blocking=True)
+                g["y"].copy_(ys, non_blocking=True)
+                g["graph"].replay()
+                self.last_loss = g["loss"]
+                return self.last_loss
+            if g is None and self._eager_steps >= self._graph_warmup:
+                self._capture(xs, ys)
+                if self._graph is not None:
+                    return self._run_batch(xs, ys)
+        self.last_loss = self._step_eager(xs, ys)
+        self._eager_steps += 1
         return self.last_loss
+
+    def _capture(self, xs, ys) -> None:
+        """Record one full training step (forward, loss, backward with the overlapped gradient all-reduce,
+        optimizer) into a CUDA graph on static input buffers; later steps are a copy + one graph launch."""
+        try:
+            sx, sy = xs.clone(), ys.clone()
+            torch.cuda.synchronize(self.device)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                loss = self._step_eager(sx, sy)
+            torch.cuda.synchronize(self.device)
+            self._graph = {"graph": graph, "x": sx, "y": sy, "loss": loss}
+        except Exception as e:  # noqa: BLE001 - fall back to eager, keep training
+            self._graph_failed = True
+            self._graph = None
+            torch.cuda.synchronize(self.device)
+            if not self.quiet:
+                print(f"[GPU: {self.gpu_id}] CUDA-graph capture failed, staying eager: {e}", flush=True)
 
     def _run_epoch(self, epoch: int):
         batch_size = len(next(iter(self.train_dataloader))[0])
