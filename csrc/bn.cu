@@ -29,6 +29,42 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
     return u;
 }
 
+
+// Block-level reduction of per-thread channel partials (8 channels per thread, threads with equal
+// `g = tid % cg` own the same channels): shuffle across the lanes of a warp that share g, then one
+// shared-memory atomic per (warp, channel), then one global atomic per (block, channel).
+__device__ __forceinline__ void block_channel_reduce(float (&s)[8], float (&q)[8], int cg, int g, float* __restrict__ out_s,
+                                                     float* __restrict__ out_q, float* sh /* [2][cg*8] */) {
+    const int C = cg * 8;
+    for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) sh[i] = 0.f;
+    __syncthreads();
+    if (cg < 32) {
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            if (o >= cg) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    s[i] += __shfl_xor_sync(0xffffffffu, s[i], o);
+                    q[i] += __shfl_xor_sync(0xffffffffu, q[i], o);
+                }
+            }
+        }
+    }
+    const int lane = threadIdx.x & 31;
+    if (cg >= 32 || lane < cg) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            atomicAdd(&sh[g * 8 + i], s[i]);
+            atomicAdd(&sh[C + g * 8 + i], q[i]);
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < C; i += blockDim.x) {
+        atomicAdd(out_s + i, sh[i]);
+        atomicAdd(out_q + i, sh[C + i]);
+    }
+}
+
 // Per-channel sums of a [M][C] bf16 matrix (used when the producer did not fuse them, e.g. tests).
 __global__ void __launch_bounds__(BN_THREADS) bn_stats_kernel(const bf16* __restrict__ y, float* __restrict__ sum,
                                                               float* __restrict__ sq, long long M, int C) {
@@ -46,17 +82,8 @@ __global__ void __launch_bounds__(BN_THREADS) bn_stats_kernel(const bf16* __rest
 #pragma unroll
         for (int i = 0; i < 8; ++i) { s[i] += f[i]; q[i] += f[i] * f[i]; }
     }
-    __shared__ float red[2][BN_THREADS][8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { red[0][threadIdx.x][i] = s[i]; red[1][threadIdx.x][i] = q[i]; }
-    __syncthreads();
-    if (threadIdx.x < cg) {
-        for (int r = 1; r < rows_per_iter; ++r)
-#pragma unroll
-            for (int i = 0; i < 8; ++i) { s[i] += red[0][threadIdx.x + r * cg][i]; q[i] += red[1][threadIdx.x + r * cg][i]; }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) { atomicAdd(sum + g * 8 + i, s[i]); atomicAdd(sq + g * 8 + i, q[i]); }
-    }
+    extern __shared__ float sh_red[];
+    block_channel_reduce(s, q, cg, g, sum, sq, sh_red);
 }
 
 // z = act( (y - mean) * invstd * gamma + beta  [+ residual] ), plus running-stat update by block 0.
@@ -183,17 +210,8 @@ bn_bwd_reduce_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ z, co
             }
         }
     }
-    __shared__ float red[2][BN_THREADS][8];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) { red[0][threadIdx.x][i] = s[i]; red[1][threadIdx.x][i] = q[i]; }
-    __syncthreads();
-    if (threadIdx.x < cg) {
-        for (int r = 1; r < rows_per_iter; ++r)
-#pragma unroll
-            for (int i = 0; i < 8; ++i) { s[i] += red[0][threadIdx.x + r * cg][i]; q[i] += red[1][threadIdx.x + r * cg][i]; }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) { atomicAdd(sum_g + g * 8 + i, s[i]); atomicAdd(sum_gx + g * 8 + i, q[i]); }
-    }
+    extern __shared__ float sh_red[];
+    block_channel_reduce(s, q, cg, g, sum_g, sum_gx, sh_red);
 }
 
 // Backward pass 2: dy = gamma*invstd * (g - sum_g/M - xhat*sum_gx/M); optionally g_out = g.
@@ -251,7 +269,7 @@ bool bn_shape_ok(int C) { return C >= 64 && C <= 2048 && (C & (C - 1)) == 0; }
 
 extern "C" int ptd_bn_stats(const void* y, float* sum, float* sq, long long M, int C, void* stream) {
     PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
-    bn_stats_kernel<<<bn_grid(M, C), BN_THREADS, 0, (cudaStream_t)stream>>>((const bf16*)y, sum, sq, M, C);
+    bn_stats_kernel<<<bn_grid(M, C), BN_THREADS, 2 * C * sizeof(float), (cudaStream_t)stream>>>((const bf16*)y, sum, sq, M, C);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }
@@ -295,13 +313,13 @@ extern "C" int ptd_affine_act(const void* y, const void* residual, void* z, cons
 extern "C" int ptd_bn_bwd_reduce(const void* dz, const void* z, const void* y, const float* mean, const float* invstd,
                                  float* sum_g, float* sum_gx, long long M, int C, int relu, void* stream) {
     PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
-    const int grid = bn_grid(M, C);
+    const int grid = min(bn_grid(M, C), ptd_num_sms() * 4);
     cudaStream_t st = (cudaStream_t)stream;
     if (relu)
-        bn_bwd_reduce_kernel<true><<<grid, BN_THREADS, 0, st>>>((const bf16*)dz, (const bf16*)z, (const bf16*)y, mean,
+        bn_bwd_reduce_kernel<true><<<grid, BN_THREADS, 2 * C * sizeof(float), st>>>((const bf16*)dz, (const bf16*)z, (const bf16*)y, mean,
                                                                 invstd, sum_g, sum_gx, M, C);
     else
-        bn_bwd_reduce_kernel<false><<<grid, BN_THREADS, 0, st>>>((const bf16*)dz, (const bf16*)z, (const bf16*)y, mean,
+        bn_bwd_reduce_kernel<false><<<grid, BN_THREADS, 2 * C * sizeof(float), st>>>((const bf16*)dz, (const bf16*)z, (const bf16*)y, mean,
                                                                  invstd, sum_g, sum_gx, M, C);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;

@@ -66,6 +66,13 @@ struct alignas(64) FParams {
     const float* bias;
     int ldo;
     int dbg;             // experiment switches (PTD_IGEMM_DBG), 0 in production
+    // im2col tap table: k-block kb belongs to table entry kb / cblocks; `wtap` is the filter tap (r*S+s) whose
+    // weights it multiplies, (off_w, off_h) the unsigned offsets handed to the im2col load.
+    int ntaps;
+    signed char tap_wtap[9], tap_offw[9], tap_offh[9];
+    // Output row map (strided data gradient): GEMM row (n, a, b) of a [sub_oh x sub_ow] grid lands on
+    // pixel (n, a*mul + ph, b*mul + pw) of an [oH x oW] tensor.  mul == 0: identity.
+    int map_mul, map_ph, map_pw, map_sub_ow, map_sub_ohw, map_oH, map_oW;
 };
 
 struct alignas(64) WParams {
@@ -311,8 +318,9 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                     in0 = m0 / hw;
                     const int rem = m0 - in0 * hw;
                     const int oh = rem / p.g.OW, ow = rem - oh * p.g.OW;
-                    if (p.g.mode == GM_FPROP) { iw0 = ow * p.g.stride - p.g.pad; ih0 = oh * p.g.stride - p.g.pad; }
-                    else { iw0 = ow + p.g.pad - (p.g.S - 1); ih0 = oh + p.g.pad - (p.g.R - 1); }
+                    // input-space position of the first row's tap-table origin (g.pad holds the origin shift)
+                    iw0 = ow * p.g.stride - p.g.pad;
+                    ih0 = oh * p.g.stride - p.g.pad;
                 }
                 for (int kb = 0; kb < p.num_kb; ++kb) {
                     mbar_wait(&bars->empty[stage], phase ^ 1);
@@ -321,18 +329,17 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                     mbar_arrive_expect_tx(&bars->full[stage], Cfg::B_TILE_BYTES + (A_TMA ? A_TILE_BYTES : 0));
                     if (A_MODE == AM_TILED) tma_load_2d(a_dst, &p.tmA, &bars->full[stage], kb * BLOCK_K, m0);
                     if (A_MODE == AM_IM2COL) {
-                        const int tap = kb / p.g.cblocks;
-                        const int cb = kb - tap * p.g.cblocks;
-                        const int r = tap / p.g.S, s = tap - r * p.g.S;
-                        const bool fp = p.g.mode == GM_FPROP;
+                        const int te = kb / p.g.cblocks;
+                        const int cb = kb - te * p.g.cblocks;
                         tma_load_im2col(a_dst, &p.tmA, &bars->full[stage], cb * 64, iw0, ih0, in0,
-                                        fp ? s : p.g.S - 1 - s, fp ? r : p.g.R - 1 - r);
+                                        (uint32_t)p.tap_offw[te], (uint32_t)p.tap_offh[te]);
                     }
                     if (!B_MN) {
                         tma_load_2d(b_dst, &p.tmB, &bars->full[stage], kb * BLOCK_K, n0);
                     } else {
-                        const int tap = kb / p.b_cblocks;
-                        const int cb = kb - tap * p.b_cblocks;
+                        const int te = kb / p.b_cblocks;
+                        const int cb = kb - te * p.b_cblocks;
+                        const int tap = (A_MODE == AM_IM2COL) ? (int)p.tap_wtap[te] : te;
 #pragma unroll
                         for (int j = 0; j < BLOCK_N / 64; ++j)
                             tma_load_2d(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage],
@@ -423,7 +430,14 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                                      : "r"(stg + row * 64 + ((pc ^ ((row >> 1) & 3)) << 4)));
                         const long long mr = m_base + row;
                         if (mr < p.M) {
-                            const size_t off = (size_t)mr * p.ldo + n0 + col + pc * 8;
+                            long long orow = mr;
+                            if (p.map_mul != 0) {
+                                const int n_ = (int)(mr / p.map_sub_ohw);
+                                const int rem_ = (int)(mr - (long long)n_ * p.map_sub_ohw);
+                                const int a_ = rem_ / p.map_sub_ow, b_ = rem_ - a_ * p.map_sub_ow;
+                                orow = ((long long)n_ * p.map_oH + a_ * p.map_mul + p.map_ph) * p.map_oW + b_ * p.map_mul + p.map_pw;
+                            }
+                            const size_t off = (size_t)orow * p.ldo + n0 + col + pc * 8;
                             if (p.addend != nullptr) {
                                 const uint4 a4 = *reinterpret_cast<const uint4*>(p.addend + off);
                                 const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
@@ -755,6 +769,19 @@ bool force_gather() {
     return v == 1;
 }
 
+// Natural tap order (r, s); offsets = the tap itself (fprop / wgrad) or mirrored (stride-1 data gradient).
+void fill_taps(FParams& p, int R, int S, bool mirrored) {
+    if (R * S > 9) { R = 1; S = 1; }      // callers check; keeps the table in bounds
+    p.ntaps = R * S;
+    for (int r = 0; r < R; ++r)
+        for (int s = 0; s < S; ++s) {
+            const int t = r * S + s;
+            p.tap_wtap[t] = (signed char)t;
+            p.tap_offw[t] = (signed char)(mirrored ? S - 1 - s : s);
+            p.tap_offh[t] = (signed char)(mirrored ? R - 1 - r : r);
+        }
+}
+
 void fill_geom(ConvGeom& g, const bf16* src, int H, int W, int C, int OH, int OW, int R, int S, int stride, int pad,
                int mode) {
     g.src = src; g.H = H; g.W = W; g.C = C; g.OH = OH; g.OW = OW; g.R = R; g.S = S;
@@ -785,10 +812,11 @@ extern "C" int ptd_conv_fprop(const void* x, const void* w, void* y, float* stat
         return dispatch_f<AM_TILED, false, 0>(p, bn, stream);
     }
     fill_geom(p.g, (const bf16*)x, H, W, Cin, OH, OW, R, S, stride, pad, GM_FPROP);
-    if (!force_gather()) {
+    if (!force_gather() && R * S <= 9) {
         // walk output pixels over the padded input with TMA im2col: corners as in CUTLASS' fprop
         rc = ptd_make_tmap_im2col_bf16(&p.tmA, x, Cin, W, H, N, -pad, -pad, pad - (S - 1), pad - (R - 1), BLOCK_M, stride);
         if (rc) return rc;
+        fill_taps(p, R, S, false);
         return dispatch_f<AM_IM2COL, false, 0>(p, bn, stream);
     }
     return dispatch_f<AM_GATHER, false, 0>(p, bn, stream);
@@ -816,14 +844,72 @@ extern "C" int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const voi
         return dispatch_f<AM_TILED, true, 0>(p, bn, stream);
     }
     fill_geom(p.g, (const bf16*)dy, OH, OW, Cout, H, W, R, S, stride, pad, GM_DGRAD);
-    if (stride == 1 && !force_gather()) {
+    if (force_gather() || R != S || R * S > 9) return dispatch_f<AM_GATHER, true, 0>(p, bn, stream);
+    if (stride == 1) {
         // dx pixel (h, w) reads dy at (h + pad - r, w + pad - s): im2col over dy with the tap order mirrored
         rc = ptd_make_tmap_im2col_bf16(&p.tmA, dy, Cout, OW, OH, N, pad - (S - 1), pad - (R - 1),
                                        pad - (S - 1) + (W - OW), pad - (R - 1) + (H - OH), BLOCK_M, 1);
         if (rc) return rc;
+        fill_taps(p, R, S, true);
+        p.g.pad = (S - 1) - pad;          // tile origin = (w - ((S-1) - pad), h - ...)
         return dispatch_f<AM_IM2COL, true, 0>(p, bn, stream);
     }
+    if (stride == 2 && (H % 2 == 0) && (W % 2 == 0) && OH == H / 2 && OW == W / 2) {
+        // Strided data gradient without wasted taps: split dx pixels by parity (ph, pw).  Pixel (2a+ph, 2b+pw)
+        // only sees taps with (ph + pad - r) even, reading dy at (a + (ph+pad-r)/2, b + ...): each parity class
+        // is a dense stride-1 walk over dy (im2col, zero-filled past the edge) whose rows land on a strided
+        // subset of dx.  The four classes together use every tap exactly once.
+        if (R == 1) {
+            // 1x1: only class (0,0) receives anything; the rest of dx is the addend (or zero)
+            if (addend != nullptr && addend != dx)
+                PTD_CUDA_CHECK(cudaMemcpyAsync(dx, addend, (size_t)N * H * W * Cin * 2, cudaMemcpyDeviceToDevice, stream));
+            else if (addend == nullptr)
+                PTD_CUDA_CHECK(cudaMemsetAsync(dx, 0, (size_t)N * H * W * Cin * 2, stream));
+            p.M = N * OH * OW;
+            p.addend = (const bf16*)dx;       // in place: every mapped element is read and written by one thread
+            p.map_mul = 2; p.map_ph = 0; p.map_pw = 0; p.map_sub_ow = OW; p.map_sub_ohw = OH * OW; p.map_oH = H; p.map_oW = W;
+            rc = ptd_make_tmap_2d_bf16(&p.tmA, dy, Cout, p.M, (uint64_t)Cout * 2, 64, BLOCK_M);
+            if (rc) return rc;
+            return dispatch_f<AM_TILED, true, 0>(p, bn, stream);
+        }
+        rc = ptd_make_tmap_im2col_bf16(&p.tmA, dy, Cout, OW, OH, N, 0, 0, 0, 0, BLOCK_M, 1);
+        if (rc) return rc;
+        bool ok = true;
+        for (int ph = 0; ph < 2 && ok; ++ph)
+            for (int pw = 0; pw < 2 && ok; ++pw) {
+                FParams q = p;
+                q.ntaps = 0;
+                for (int r = 0; r < R; ++r) {
+                    const int th = ph + pad - r;
+                    if (th < 0 || (th & 1)) continue;
+                    for (int s2 = 0; s2 < S; ++s2) {
+                        const int tw = pw + pad - s2;
+                        if (tw < 0 || (tw & 1)) continue;
+                        q.tap_wtap[q.ntaps] = (signed char)(r * S + s2);
+                        q.tap_offh[q.ntaps] = (signed char)(th / 2);
+                        q.tap_offw[q.ntaps] = (signed char)(tw / 2);
+                        ++q.ntaps;
+                    }
+                }
+                q.M = N * (H / 2) * (W / 2);
+                q.g.OH = H / 2; q.g.OW = W / 2; q.g.stride = 1; q.g.pad = 0;
+                q.map_mul = 2; q.map_ph = ph; q.map_pw = pw; q.map_sub_ow = W / 2; q.map_sub_ohw = (H / 2) * (W / 2);
+                q.map_oH = H; q.map_oW = W;
+                if (q.ntaps == 0) { ok = false; break; }      // a class without taps would need a zero fill
+                q.num_kb = q.ntaps * (Cout / 64);
+                rc = dispatch_f<AM_IM2COL, true, 0>(q, bn, stream);
+                if (rc) return rc;
+            }
+        if (ok) return PTD_OK;
+    }
     return dispatch_f<AM_GATHER, true, 0>(p, bn, stream);
+}
+
+// dx += conv_transpose(dy, w)  (in place).  For the 1x1 stride-2 shortcut convolution this touches only the
+// strided quarter of dx - the reason the fused bottleneck backward calls it after the main branch wrote dx.
+extern "C" int ptd_conv_dgrad_accum(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout,
+                                    int R, int S, int stride, int pad, void* stream_) {
+    return ptd_conv_dgrad(dy, w, dx, dx, N, H, W, Cin, Cout, R, S, stride, pad, stream_);
 }
 
 extern "C" int ptd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int R,

@@ -29,6 +29,9 @@ int ptd_conv_fprop(const void* x, const void* w, void* y, float* stat_sum, float
 /* dx[N,H,W,Cin] = conv_transpose(dy[N,OH,OW,Cout], w) (+ addend[N,H,W,Cin] if not NULL). */
 int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const void* addend, int N, int H, int W, int Cin,
                    int Cout, int R, int S, int stride, int pad, void* stream);
+/* dx += conv_transpose(dy, w), in place (the 1x1 stride-2 shortcut only touches the strided quarter of dx). */
+int ptd_conv_dgrad_accum(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int R, int S,
+                         int stride, int pad, void* stream);
 /* dw[Cout,R,S,Cin] (fp32) += dy^T * im2col(x).  The caller zeroes dw (or keeps an accumulated value). */
 int ptd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int R, int S,
                    int stride, int pad, void* stream);

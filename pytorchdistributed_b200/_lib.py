@@ -23,6 +23,7 @@ _SIGS: dict[str, list] = {
     "ptd_device_sm_count": [],
     "ptd_conv_fprop": [P, P, P, P, P, I, I, I, I, I, I, I, I, I, P],
     "ptd_conv_dgrad": [P, P, P, P, I, I, I, I, I, I, I, I, I, P],
+    "ptd_conv_dgrad_accum": [P, P, P, I, I, I, I, I, I, I, I, I, P],
     "ptd_conv_wgrad": [P, P, P, I, I, I, I, I, I, I, I, I, P],
     "ptd_stem_fprop": [P, P, P, P, P, I, I, I, P],
     "ptd_stem_wgrad": [P, P, P, I, I, I, P],

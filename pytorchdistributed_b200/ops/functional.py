@@ -537,9 +537,11 @@ class _Bottleneck(torch.autograd.Function):
         dy1, _, dg1, db1 = bn_bwd(0, dz1, z1, y1, True, False)
         if has_ds:
             dyd, _, dgd, dbd = bn_bwd(3, g_id, zd, yd, False, False)
-            dxd = dgrad(3, dyd, x.shape, stride, 0)
             wgrad(3, x, dyd, stride, 0)
-            dx = dgrad(0, dy1, x.shape, 1, 0, addend=dxd)
+            dx = dgrad(0, dy1, x.shape, 1, 0)
+            # shortcut branch accumulates straight into dx (stride 2: only the strided quarter is touched)
+            n, cin, h, w = x.shape
+            _lib.call("ptd_conv_dgrad_accum", dyd, wbs[3], dx, n, h, w, cin, w_shapes[3][0], 1, 1, stride, 0, _stream())
         else:
             dx = dgrad(0, dy1, x.shape, 1, 0, addend=g_id)
         wgrad(0, x, dy1, 1, 0)
