@@ -96,7 +96,9 @@ def test_ddp_p2p_replicas_identical_and_match_nccl_path(world):
     nccl = run_ranks(_ddp, world, ("torch",), backend="nccl")
     assert p2p[0][3] == "p2p" and nccl[0][3] == "torch"
     for k in p2p[0][1]:
-        assert torch.equal(p2p[0][1][k], p2p[1][1][k]), k            # replicas bit-identical
+        if "running_" in k or "num_batches" in k:
+            continue              # BN statistics are per-rank until the next forward re-broadcasts rank 0's
+        assert torch.equal(p2p[0][1][k], p2p[1][1][k]), k            # parameter replicas stay bit-identical
     # same training through NCCL: split-K atomics make conv grads non-deterministic in the last bits,
     # so compare loosely
     num = sum(float((p2p[0][1][k] - nccl[0][1][k]).norm()) for k in p2p[0][1] if "running" not in k and "num_b" not in k)

@@ -297,23 +297,35 @@ def test_fused_bottleneck_matches_torchvision(inplanes, planes, stride, ds):
         assert _rel(b.float(), c.float()) < 1e-2, n
 
 
-def test_resnet50_step_matches_torchvision_loosely():
+def test_resnet50_step_tracks_fp32_as_well_as_torch_bf16_does():
+    """Whole-model check.  A randomly initialised ResNet-50 amplifies bf16 rounding chaotically (ReLU masks flip), so
+    deep gradients of ANY bf16 run differ from fp32 by O(1) - torch's own autocast included (benchmarks/grad_trace.py).
+    The meaningful statement: our run stays as close to the fp32 run as torch's bf16 autocast run does."""
     torchvision = pytest.importorskip("torchvision")
     from pytorchdistributed_b200.models import resnet50
     torch.manual_seed(0)
     m = resnet50().to(DEV).train()
+    with torch.no_grad():
+        for p in m.parameters():
+            p.copy_(p.to(torch.bfloat16).float())
     tv = torchvision.models.resnet50().to(DEV).train()
     tv.load_state_dict(m.state_dict())
-    x = torch.randn(8, 3, 64, 64, device=DEV)
-    y = torch.randint(0, 1000, (8,), device=DEV)
-    loss = K.cross_entropy(m(x), y)
-    lr = F.cross_entropy(tv(x), y)
-    assert abs(loss.item() - lr.item()) < 0.15
-    loss.backward(); lr.backward()
-    # fc gradient is the best conditioned one; deep conv grads differ more under bf16 activations
-    assert _rel(m.fc.weight.grad, tv.fc.weight.grad) < 0.5     # batch-8 BN statistics amplify bf16 rounding; sanity only
+    ac = torchvision.models.resnet50().to(DEV).train()
+    ac.load_state_dict(m.state_dict())
+    x = torch.randn(32, 3, 128, 128, device=DEV).to(torch.bfloat16).float()
+    y = torch.randint(0, 1000, (32,), device=DEV)
+    out, outr = m(x), tv(x)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        outa = ac(x).float()
+    loss, lr, la = K.cross_entropy(out, y), F.cross_entropy(outr, y), F.cross_entropy(outa, y)
+    assert abs(loss.item() - lr.item()) < max(0.05, 2 * abs(la.item() - lr.item()))
+    assert _rel(out, outr) < 1.5 * _rel(outa, outr) + 0.02
+    loss.backward(); lr.backward(); la.backward()
+    assert _rel(m.fc.weight.grad, tv.fc.weight.grad) < 1.5 * _rel(ac.fc.weight.grad, tv.fc.weight.grad) + 0.02
+    ours = sorted(_rel(p.grad, q.grad) for p, q in zip(m.parameters(), tv.parameters()))
+    ctrl = sorted(_rel(p.grad, q.grad) for p, q in zip(ac.parameters(), tv.parameters()))
+    assert ours[len(ours) // 2] < 1.2 * ctrl[len(ctrl) // 2] + 0.05
     assert m.conv1.weight.grad.shape == tv.conv1.weight.grad.shape
-    assert _rel(m.layer4[2].conv3.weight.grad, tv.layer4[2].conv3.weight.grad) < 0.6
 
 
 @pytest.mark.parametrize("opt_name", ["sgd", "sgd_momentum", "adam"])
