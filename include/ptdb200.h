@@ -45,6 +45,94 @@ int ptd_linear_fwd(const void* a, const void* w, const float* bias, float* out, 
 int ptd_linear_dgrad(const void* dout, const void* w, void* da, int M, int N, int K, void* stream);
 int ptd_linear_wgrad(const void* a, const void* dout, float* dw, int M, int N, int K, void* stream);
 
+/* ---- BatchNorm (training) fused with ReLU / residual add, NHWC bf16, fp32 statistics
+ *      (nn.BatchNorm2d of torchvision Bottleneck, R/03 模型并行/03_model_parallel.ipynb#cell5; cuDNN/ATen there) ---- */
+/* per-channel sum / sum of squares of y[M][C] (when the producing convolution did not fuse them) */
+int ptd_bn_stats(const void* y, float* sum, float* sq, long long M, int C, void* stream);
+/* z = act(bn(y) [+ residual]); updates running stats (may be NULL), writes mean / invstd for the backward */
+int ptd_bn_apply(const void* y, const void* residual, void* z, const float* sum, const float* sq, const float* gamma,
+                 const float* beta, float* running_mean, float* running_var, float* save_mean, float* save_invstd,
+                 long long M, int C, float eps, float momentum, int relu, void* stream);
+/* z = act(y * scale[c] + shift[c] [+ residual])  (inference-mode BN) */
+int ptd_affine_act(const void* y, const void* residual, void* z, const float* scale, const float* shift, long long M,
+                   int C, int relu, void* stream);
+/* backward pass 1: sum_g[c] += g, sum_gx[c] += g * xhat (caller-zeroed fp32[C] each), g = dz * (z > 0 if relu) */
+int ptd_bn_bwd_reduce(const void* dz, const void* z, const void* y, const float* mean, const float* invstd,
+                      float* sum_g, float* sum_gx, long long M, int C, int relu, void* stream);
+/* backward pass 2: dy from the sums; g_out (optional) = masked incoming gradient (identity-branch gradient) */
+int ptd_bn_bwd_apply(const void* dz, const void* z, const void* y, const float* mean, const float* invstd,
+                     const float* gamma, const float* sum_g, const float* sum_gx, void* dy, void* g_out, long long M,
+                     int C, int relu, void* stream);
+
+/* ---- pooling / layout (nn.MaxPool2d(3,2,1), nn.AdaptiveAvgPool2d(1), `.to(device)` input staging) ---- */
+int ptd_maxpool3x3s2_fwd(const void* x, void* y, void* argmax_u8, int N, int H, int W, int C, void* stream);
+int ptd_maxpool3x3s2_bwd(const void* dy, const void* argmax_u8, void* dx, int N, int H, int W, int C, void* stream);
+int ptd_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
+int ptd_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
+int ptd_nchw3_f32_to_nhwc4_bf16(const float* x, void* y, int N, int H, int W, void* stream);
+int ptd_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int HW, void* stream);
+int ptd_nhwc_bf16_to_nchw_f32(const void* x, float* y, int N, int C, int HW, void* stream);
+int ptd_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream);
+int ptd_stem_pack_weight(const float* w, void* w4, long long sk, long long sc, long long sr, long long ss, void* stream);
+int ptd_stem_unpack_wgrad(const float* dw4, float* dw, long long sk, long long sc, long long sr, long long ss,
+                          int accumulate, void* stream);
+
+/* ---- loss and optimizers (F.cross_entropy with float targets, R/02 DDP基本概念/ddp_gpus.py:40;
+ *      torch.optim.SGD(lr=1e-3) ddp_gpus.py:78; torch.optim.Adam(lr=1e-3) notebook 03 cell 7) ---- */
+/* loss_sum += scale * sum_rows CE(logits, target); dlogits = scale * dCE/dlogits.  Exactly one target kind. */
+int ptd_softmax_ce(const float* logits, const float* soft_targets, const long long* index_targets, float* loss_sum,
+                   void* dlogits, int dlogits_is_bf16, int rows, int C, int ldd, float scale, void* stream);
+/* table: device array of {param, grad, state1, state2, bf16 shadow, numel} records; blockmap: (tensor, chunk) per block */
+int ptd_multi_sgd(const void* table, const void* blockmap, int n_blocks, float lr, float momentum, float weight_decay,
+                  float grad_scale, int first_step, void* stream);
+int ptd_multi_adam(const void* table, const void* blockmap, int n_blocks, float lr, float beta1, float beta2, float eps,
+                   float weight_decay, int step, float grad_scale, void* stream);
+int ptd_multi_cast_bf16(const void* table, const void* blockmap, int n_blocks, void* stream);
+int ptd_multi_zero_grad(const void* table, const void* blockmap, int n_blocks, void* stream);
+int ptd_opt_chunk_elems(void);
+
+/* ---- tutorial-sized dense layers, fp32 on CUDA cores (Linear(20,1) ddp_gpus.py:77; MLP notebook 01 cell 4) ---- */
+int ptd_small_linear_fwd(const float* x, const float* w, const float* b, float* y, int B, int K, int N, int relu,
+                         void* stream);
+int ptd_small_linear_bwd(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db, int B,
+                         int K, int N, void* stream);
+/* weights / biases: host arrays of device pointers; dims: host array of n_layers + 1 widths */
+int ptd_mlp_fwd(const float* x, float* y, const float* const* weights, const float* const* biases, const int* dims,
+                int n_layers, int B, void* stream);
+
+/* ---- peer-to-peer runtime and collectives over NVLink (replaces the NCCL calls behind
+ *      DDP(model, device_ids=[gpu_id]) ddp_gpus.py:35,41 and nn.DataParallel notebook 01 cell 5-6) ---- */
+int ptd_p2p_malloc(long long bytes, void** out);
+int ptd_p2p_free(void* p);
+int ptd_p2p_ipc_handle_size(void);
+int ptd_p2p_ipc_get(void* p, void* handle_out);
+int ptd_p2p_ipc_open(const void* handle, void** out);
+int ptd_p2p_ipc_close(void* p);
+int ptd_p2p_enable_peer_access(int dev, int peer);
+int ptd_p2p_pad_bytes(void);
+int ptd_p2p_max_blocks(void);
+/* bufs / pads: host arrays of `world` device pointers (this process's mapping of every rank's buffer / signal pad).
+ * In-place average (scale = 1/world) or any scaled sum; kernels sharing a pad must be stream-ordered. */
+int ptd_allreduce_inplace(const void* const* bufs, const void* const* pads, int rank, int world, long long numel,
+                          int is_bf16, float scale, int blocks, void* stream);
+int ptd_broadcast_inplace(const void* const* bufs, const void* const* pads, int rank, int world, int root,
+                          long long nbytes, int blocks, void* stream);
+int ptd_p2p_barrier(const void* const* pads, int rank, int world, void* stream);
+/* single process, several devices: copy / sum over peer pointers from a kernel on the current device */
+int ptd_peer_copy(void* dst, const void* src, long long nbytes, void* stream);
+int ptd_reduce_sum_f32(float* dst, const void* const* srcs, int n_src, long long numel, float scale, int accumulate,
+                       void* stream);
+
+/* ---- gradient bucket planner / ready-tracking reducer (torch's C++ Reducer behind DDP) ---- */
+int ptd_plan_buckets(const long long* sizes_bytes, int n, long long first_cap, long long cap, int* bucket_of);
+int ptd_reducer_create(const int* bucket_of, int n_params, int n_buckets);
+int ptd_reducer_mark_ready(int id, int param);
+int ptd_reducer_all_done(int id);
+int ptd_reducer_ready_order(int id, int* out, int n);
+int ptd_reducer_incomplete(int id, int* out, int n);
+int ptd_reducer_reset(int id);
+int ptd_reducer_destroy(int id);
+
 #ifdef __cplusplus
 }
 #endif
