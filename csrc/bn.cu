@@ -7,6 +7,8 @@
 // written out by the apply pass when asked for.
 // Reference behaviour: nn.BatchNorm2d in torchvision Bottleneck (momentum 0.1, eps 1e-5),
 // reached from R/03 模型并行/03_model_parallel.ipynb#cell5.
+#include <mutex>
+
 #include "common.cuh"
 #include "ptdb200.h"
 
@@ -340,5 +342,95 @@ extern "C" int ptd_bn_bwd_apply(const void* dz, const void* z, const void* y, co
     else PTD_BWD(false, false);
 #undef PTD_BWD
     PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+// =================================================================================================
+// BatchNorm backward for callers that must not allocate device memory
+// =================================================================================================
+// ptd_bn_bwd_reduce / ptd_bn_bwd_apply above need a caller-provided, caller-zeroed scratch of 2*C floats for
+// the per-channel sums.  Some callers cannot provide one: a plug-in running inside another runtime's memory
+// plan (every byte of device memory already belongs to that runtime's arena, and a cudaMalloc from the side
+// would also stall all of its streams), a fixed-footprint service that sizes its buffers once at start-up,
+// or a plain C host that only owns its inputs and outputs.  For them the entry point below keeps the sums in
+// a small array that is part of this library's device image: nothing is allocated or freed, here or in any
+// routine it calls (cudaGetSymbolAddress, cudaMemsetAsync, cudaMemcpyAsync and kernel launches only).
+//
+// Limit: 2048 channels (2 * 2048 floats = 16 KiB, held by every GPU that loads the library until it exits).
+// A wider layer is refused with an error instead of silently overrunning the array.
+//
+// In host code the array's name is only a host-side handle, not a device address - a kernel handed the name
+// would fault (or quietly touch the wrong memory on a system where the GPU can reach host memory).  The real
+// address comes from cudaGetSymbolAddress, asked once per device with that device current, and is cached.
+// That lookup happens inside the FIRST call on each device; make that first call before starting any stream
+// capture on that device.
+//
+// The array is shared by all calls and keeps whatever the previous call left in it, so every call clears the
+// 2*C floats it is about to accumulate into, on the caller's stream, before the reduce pass.  Calls are
+// therefore safe back to back on one stream, but two calls whose GPU work can overlap (different streams,
+// or threads launching concurrently on one device) race on the array and must be ordered by the caller.
+namespace {
+
+constexpr int BN_STATIC_MAX_C = 2048;
+static __device__ __align__(256) float g_bn_static_sums[2 * BN_STATIC_MAX_C];
+
+// Device address of g_bn_static_sums for the current device (looked up once per device, then cached).
+int bn_static_sums_ptr(float** out) {
+    static std::mutex mu;
+    static float* cached[64] = {nullptr};
+    int dev = 0;
+    PTD_CUDA_CHECK(cudaGetDevice(&dev));
+    PTD_REQUIRE(dev >= 0 && dev < 64, "bn_backward_static: device index %d not supported", dev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (cached[dev] == nullptr) {
+        float* p = nullptr;
+        PTD_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_bn_static_sums));
+        PTD_REQUIRE(p != nullptr, "bn_backward_static: cudaGetSymbolAddress returned a null address");
+        cached[dev] = p;
+    }
+    *out = cached[dev];
+    return PTD_OK;
+}
+
+}  // namespace
+
+// dy = BN-backward(dz) with the ReLU mask taken from z when `relu`; g_out (optional) receives the masked
+// incoming gradient; dgamma / dbeta (fp32[C]) receive the parameter gradients.  Same math and kernels as
+// ptd_bn_bwd_reduce + ptd_bn_bwd_apply, but no scratch argument: see the block comment above.
+extern "C" int ptd_bn_backward_static(const void* dz, const void* z, const void* y, const float* mean,
+                                      const float* invstd, const float* gamma, void* dy, void* g_out, float* dgamma,
+                                      float* dbeta, long long M, int C, int relu, void* stream) {
+    PTD_REQUIRE(C <= BN_STATIC_MAX_C,
+                "bn_backward_static: C = %d exceeds the built-in scratch (max %d channels); use ptd_bn_bwd_reduce/"
+                "ptd_bn_bwd_apply with your own 2*C-float scratch instead", C, BN_STATIC_MAX_C);
+    PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
+    PTD_REQUIRE(dgamma != nullptr && dbeta != nullptr && dy != nullptr, "bn_backward_static: dy, dgamma and dbeta are required");
+    float* sums = nullptr;
+    int rc = bn_static_sums_ptr(&sums);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    float* sum_g = sums;          // -> dbeta
+    float* sum_gx = sums + C;     // -> dgamma
+    PTD_CUDA_CHECK(cudaMemsetAsync(sums, 0, 2 * (size_t)C * sizeof(float), st));     // leftovers of the previous call
+    const int rgrid = min(bn_grid(M, C), ptd_num_sms() * 4);
+    if (relu)
+        bn_bwd_reduce_kernel<true><<<rgrid, BN_THREADS, 2 * C * sizeof(float), st>>>(
+            (const bf16*)dz, (const bf16*)z, (const bf16*)y, mean, invstd, sum_g, sum_gx, M, C);
+    else
+        bn_bwd_reduce_kernel<false><<<rgrid, BN_THREADS, 2 * C * sizeof(float), st>>>(
+            (const bf16*)dz, (const bf16*)z, (const bf16*)y, mean, invstd, sum_g, sum_gx, M, C);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    const int agrid = bn_grid(M, C);
+#define PTD_BWD_S(RELU, GOUT)                                                                                          \
+    bn_bwd_apply_kernel<RELU, GOUT><<<agrid, BN_THREADS, 0, st>>>((const bf16*)dz, (const bf16*)z, (const bf16*)y, mean, \
+                                                                 invstd, gamma, sum_g, sum_gx, (bf16*)dy, (bf16*)g_out, M, C)
+    if (relu && g_out) PTD_BWD_S(true, true);
+    else if (relu) PTD_BWD_S(true, false);
+    else if (g_out) PTD_BWD_S(false, true);
+    else PTD_BWD_S(false, false);
+#undef PTD_BWD_S
+    PTD_CUDA_CHECK(cudaGetLastError());
+    PTD_CUDA_CHECK(cudaMemcpyAsync(dbeta, sum_g, (size_t)C * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    PTD_CUDA_CHECK(cudaMemcpyAsync(dgamma, sum_gx, (size_t)C * sizeof(float), cudaMemcpyDeviceToDevice, st));
     return PTD_OK;
 }

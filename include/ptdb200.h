@@ -63,6 +63,14 @@ int ptd_bn_bwd_reduce(const void* dz, const void* z, const void* y, const float*
 int ptd_bn_bwd_apply(const void* dz, const void* z, const void* y, const float* mean, const float* invstd,
                      const float* gamma, const float* sum_g, const float* sum_gx, void* dy, void* g_out, long long M,
                      int C, int relu, void* stream);
+/* BatchNorm backward (both passes) for callers that must not allocate: the 2*C-float scratch lives in a fixed array
+ * inside the library image instead of being passed in.  C <= 2048 (16 KiB per GPU), larger C is rejected.  The first
+ * call on a device looks up the array's address - make it before any stream capture on that device.  All calls share
+ * the array: overlapping calls on one device race, order them.  No counterpart in the reference (it has no native
+ * code and never manages device memory itself). */
+int ptd_bn_backward_static(const void* dz, const void* z, const void* y, const float* mean, const float* invstd,
+                           const float* gamma, void* dy, void* g_out, float* dgamma, float* dbeta, long long M, int C,
+                           int relu, void* stream);
 
 /* ---- pooling / layout (nn.MaxPool2d(3,2,1), nn.AdaptiveAvgPool2d(1), `.to(device)` input staging) ---- */
 int ptd_maxpool3x3s2_fwd(const void* x, void* y, void* argmax_u8, int N, int H, int W, int C, void* stream);

@@ -35,6 +35,7 @@ _SIGS: dict[str, list] = {
     "ptd_affine_act": [P, P, P, P, P, L, I, I, P],
     "ptd_bn_bwd_reduce": [P, P, P, P, P, P, P, L, I, I, P],
     "ptd_bn_bwd_apply": [P, P, P, P, P, P, P, P, P, P, L, I, I, P],
+    "ptd_bn_backward_static": [P, P, P, P, P, P, P, P, P, P, L, I, I, P],
     "ptd_maxpool3x3s2_fwd": [P, P, P, I, I, I, I, P],
     "ptd_maxpool3x3s2_bwd": [P, P, P, I, I, I, I, P],
     "ptd_avgpool_fwd": [P, P, I, I, I, P],
