@@ -1,0 +1,46 @@
+"""Wrappers on CPU: split-model bookkeeping, micro-batch splitting, DataParallel passthrough (reference C13, C16, C19)."""
+import pytest
+import torch
+
+from pytorchdistributed_b200.models import MLP, resnet50
+from pytorchdistributed_b200.parallel import DataParallel, ModelParallelResNet50, PipelineParallelResNet50
+
+
+@pytest.mark.parametrize("split", [1, 3, 4, 7, 20])
+def test_pipeline_output_independent_of_split_size(split):
+    torch.manual_seed(0)
+    pp = PipelineParallelResNet50(split_size=split, num_classes=10, devices=("cpu", "cpu")).eval()
+    plain = resnet50(num_classes=10).eval()
+    plain.load_state_dict(pp.state_dict())
+    x = torch.randn(7, 3, 64, 64)                 # 7 is not a multiple of most split sizes: uneven last micro-batch
+    with torch.no_grad():
+        assert torch.allclose(pp(x), plain(x), atol=1e-4)
+
+
+def test_model_parallel_state_dict_layouts():
+    mp = ModelParallelResNet50(num_classes=1000, devices=("cpu", "cpu"))
+    sd = mp.state_dict()
+    assert len(sd) == 320 and "seq1.0.weight" not in sd          # torchvision's keys only
+    ref = mp.reference_state_dict()
+    assert len(ref) == 638                                        # the reference class registers everything twice
+    assert ref["seq1.0.weight"] is sd["conv1.weight"] or torch.equal(ref["seq1.0.weight"], sd["conv1.weight"])
+    assert torch.equal(ref["seq2.1.2.bn3.weight"], sd["layer4.2.bn3.weight"])
+    assert sum(p.numel() for p in mp.parameters()) == 25_557_032
+
+
+def test_pipeline_trains_on_cpu():
+    torch.manual_seed(0)
+    pp = PipelineParallelResNet50(split_size=2, num_classes=10, devices=("cpu", "cpu")).train()
+    x, y = torch.randn(4, 3, 32, 32), torch.randint(0, 10, (4,))
+    loss = torch.nn.functional.cross_entropy(pp(x), y)
+    loss.backward()
+    assert all(p.grad is not None for p in pp.parameters())
+
+
+def test_data_parallel_without_gpu_is_passthrough():
+    m = MLP()
+    dp = DataParallel(m)
+    x = torch.randn(32, 10)
+    assert dp(x).shape == (32, 5)
+    assert torch.equal(dp(x), m(x))
+    assert list(dp.state_dict().keys())[0].startswith("module.")

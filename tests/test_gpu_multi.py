@@ -105,3 +105,82 @@ def test_ddp_p2p_replicas_identical_and_match_nccl_path(world):
     den = sum(float(nccl[0][1][k].norm()) for k in nccl[0][1] if "running" not in k and "num_b" not in k)
     assert num / den < 2e-2
     assert p2p[0][2]["iterations"] == 3 and p2p[0][2]["allreduce_launches"] >= 3
+
+
+def test_data_parallel_forward_backward_matches_single_device():
+    _need(2)
+    from pytorchdistributed_b200.models import MLP
+    from pytorchdistributed_b200.parallel import DataParallel
+    torch.manual_seed(0)
+    n = min(torch.cuda.device_count(), 4)
+    ref = MLP().cuda(0)
+    model = MLP().cuda(0)
+    model.load_state_dict(ref.state_dict())
+    dp = DataParallel(model, device_ids=list(range(n)))
+    x = torch.randn(32, 10, device="cuda:0")
+    t = torch.randn(32, 5, device="cuda:0")
+    out = dp(x)
+    assert out.shape == (32, 5) and out.device.index == 0          # notebook 01: "Outside: ... output_size [32, 5]"
+    assert torch.allclose(out, ref(x), atol=1e-5)
+    torch.nn.functional.mse_loss(out, t).backward()
+    torch.nn.functional.mse_loss(ref(x), t).backward()
+    for p, q in zip(model.parameters(), ref.parameters()):
+        assert torch.allclose(p.grad, q.grad, atol=1e-5)
+    # replicas are refreshed only when the root parameters change
+    c0 = dp.stats["replicate_copies"]
+    dp(x)
+    assert dp.stats["replicate_copies"] == c0 and dp.stats["replicate_skipped"] >= 1
+    with torch.no_grad():
+        for p in model.parameters():
+            p.add_(1.0)
+        for p in ref.parameters():
+            p.add_(1.0)
+    assert torch.allclose(dp(x), ref(x), atol=1e-4)
+    assert dp.stats["replicate_copies"] > c0
+
+
+def test_data_parallel_fused_loss_resnet():
+    _need(2)
+    from pytorchdistributed_b200.models import resnet50
+    from pytorchdistributed_b200.ops import functional as K
+    from pytorchdistributed_b200.parallel import DataParallel
+    torch.manual_seed(0)
+    model = resnet50(num_classes=64).cuda(0).train()
+    dp = DataParallel(model, device_ids=[0, 1], criterion=K.cross_entropy)
+    x = torch.randn(8, 3, 64, 64, device="cuda:0")
+    y = torch.randint(0, 64, (8,), device="cuda:0")
+    loss = dp(x, y)
+    assert loss.dim() == 0 and 3.0 < float(loss) < 6.0             # ~ln(64) at random init
+    loss.backward()
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in model.parameters())
+    assert float(model.fc.weight.grad.abs().sum()) > 0
+
+
+@pytest.mark.parametrize("transfer", ["nccl", "p2p"])
+def test_pipeline_matches_unsplit_model(transfer):
+    _need(2)
+    from pytorchdistributed_b200.models import resnet50
+    from pytorchdistributed_b200.ops import functional as K
+    from pytorchdistributed_b200.parallel import ModelParallelResNet50, PipelineParallelResNet50
+    torch.manual_seed(0)
+    pp = PipelineParallelResNet50(split_size=3, num_classes=32, transfer=transfer).eval()
+    single = resnet50(num_classes=32).cuda(0).eval()
+    single.load_state_dict(pp.state_dict())
+    x = torch.randn(8, 3, 64, 64, device="cuda:0")
+    with torch.no_grad():
+        a, b = pp(x), single(x)
+    assert a.device.index == 1 and a.shape == (8, 32)
+    assert torch.allclose(a.cpu(), b.cpu(), atol=2e-2, rtol=2e-2)   # eval mode: running stats, deterministic
+    # training step: finite loss, every parameter (on both devices) gets a gradient
+    pp.train()
+    y = torch.randint(0, 32, (8,), device="cuda:1")
+    loss = K.cross_entropy(pp(x), y)
+    loss.backward()
+    assert torch.isfinite(loss)
+    devs = {p.device.index for p in pp.parameters()}
+    assert devs == {0, 1}
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in pp.parameters())
+    mp_ = ModelParallelResNet50(num_classes=32, transfer=transfer).eval()
+    mp_.load_state_dict(pp.state_dict())
+    with torch.no_grad():
+        assert torch.allclose(mp_(x).cpu(), pp.eval()(x).cpu(), atol=2e-2, rtol=2e-2)
