@@ -11,8 +11,9 @@ script, one process per GPU.  Weak scaling: per-GPU work is fixed, ``value`` is 
 Two numbers per arm:
   * ``value``      - K steps on device-resident inputs (a different pre-staged batch each step; one batch is
                      154 MB fp32 > L2), timed with CUDA events between barrier+synchronize, max over ranks;
-  * ``e2e.value``  - the same K steps through the public API (``Trainer._run_batch``) where every step first
-                     copies its batch from pinned host memory and ends by reading the loss back to the host.
+  * ``e2e.value``  - the same K steps through the public API (``Trainer.run_batches`` for ours, the reference's own
+                     ``.to(gpu)`` + ``Trainer._run_batch`` loop for the reference arm): every step's batch is copied
+                     from pinned host memory and every step's result is read back to the host, inside the timed region.
 
 ``--impl reference`` runs the UNMODIFIED reference: ``Trainer``/``ddp_setup`` imported from the verbatim copy of
 ``ddp_gpus_torchrun.py`` under ``baseline/_ref`` (the reference is a pair of scripts, not an installable package -
@@ -84,6 +85,21 @@ def _timed(fn, steps: int, device) -> float:
     return float(ms.item())
 
 
+def _timed_block(fn, device) -> float:
+    """Milliseconds for one call of fn(), CUDA events, barrier + synchronize on both sides, max over ranks."""
+    dist.barrier()
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    fn()
+    e1.record()
+    torch.cuda.synchronize(device)
+    dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=device)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
 # ------------------------------------------------------------------------------------------------------
 def run_ours(args, rank, local_rank, world):
     from pytorchdistributed_b200 import _lib
@@ -100,7 +116,7 @@ def run_ours(args, rank, local_rank, world):
     torch.manual_seed(0)
     model = resnet50()
     opt = SGD(model.parameters(), lr=1e-3)
-    trainer = Trainer(model, train_dataloader=None, optimizer=opt, quiet=True)
+    trainer = Trainer(model, train_dataloader=None, optimizer=opt, quiet=True, cuda_graph=args.graph)
     n_stage = 2
     hx, hy = _make_batches(n_stage, args.batch, args.img, pinned=True, seed=1234 + rank)
     dx = [x.to(device) for x in hx]
@@ -109,29 +125,35 @@ def run_ours(args, rank, local_rank, world):
     def step_dev(i):
         trainer._run_batch(dx[i % n_stage], dy[i % n_stage])
 
-    host_loss = torch.zeros(1).pin_memory()
-
-    def step_e2e(i):
-        x = hx[i % n_stage].to(device, non_blocking=True)
-        y = hy[i % n_stage].to(device, non_blocking=True)
-        loss = trainer._run_batch(x, y)
-        host_loss.copy_(loss.reshape(1), non_blocking=False)      # device -> host read of the step's result
+    def run_e2e(steps):
+        """`steps` steps through the public loop (Trainer.run_batches): every step's batch is copied from pinned host
+        memory (prefetched on a copy stream while the previous step computes) and every step's loss is read back."""
+        losses = trainer.run_batches(((hx[i % n_stage], hy[i % n_stage]) for i in range(steps)))
+        return losses
 
     for i in range(args.warmup):
         step_dev(i)
+    if args.graph:                       # capture happens on the first step after the trainer's eager warm-up
+        for i in range(4):
+            if trainer._graph is not None or trainer._graph_failed:
+                break
+            step_dev(i)
+        step_dev(0)
     sampler = ClockSampler(local_rank).start() if rank == 0 else None
     l0 = _lib.LAUNCHES
     ms = _timed(step_dev, args.steps, device)
     launches = _lib.LAUNCHES - l0
+    if trainer._graph is not None:       # replayed steps re-issue the recorded entry-point launches on the device
+        launches += args.steps * trainer._graph["launches"]
     clocks = sampler.stop() if sampler else {}
-    for i in range(max(1, args.warmup // 2)):
-        step_e2e(i)
-    ms_e2e = _timed(step_e2e, args.steps, device)
+    run_e2e(max(2, args.warmup // 2))
+    ms_e2e = _timed_block(lambda: run_e2e(args.steps), device)
     final_loss = float(trainer.last_loss.item())
     stats = dict(trainer.model.stats)
     comm = getattr(trainer.model.backend, "name", "?")
     destroy_process_group()
-    return ms, ms_e2e, launches, clocks, {"final_loss": final_loss, "ddp": stats, "grad_comm": comm}
+    return ms, ms_e2e, launches, clocks, {"final_loss": final_loss, "ddp": stats, "grad_comm": comm,
+                                          "cuda_graph": bool(trainer._graph is not None)}
 
 
 def run_reference(args, rank, local_rank, world):
@@ -202,6 +224,8 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--batch", type=int, default=256, help="per-GPU batch (BASELINE config: 256)")
     ap.add_argument("--img", type=int, default=224)
+    ap.add_argument("--graph", type=int, default=int(os.environ.get("PTDB200_BENCH_GRAPH", "0")),
+                    help="replay the whole training step from a CUDA graph (ours arm)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

@@ -1,0 +1,122 @@
+// Native executors for a whole residual bottleneck: ONE call launches every kernel of the block's forward
+// (4-8 launches) or backward (12-16 launches) on the caller's stream.
+//
+// Why: at small per-stage work (pipeline micro-batches, late ResNet stages) the step is bound by the host issuing
+// launches; driving ~22 kernels of a block from Python costs ~0.6 ms, from here a few microseconds.  The reference
+// pays the same overhead through torch's module-by-module eager dispatch (R/03 模型并行/03_model_parallel.ipynb#cell12;
+// its split_size=1 run takes 4.87 s) - SURVEY.md 3.5 names launch overhead as the pipeline's real bound.
+//
+// The caller (ops/functional.py: _Bottleneck) owns all memory: it passes the activations to keep for the backward,
+// and scratch / gradient buffers that are zeroed here with cudaMemsetAsync.
+#include <string.h>
+
+#include "common.cuh"
+#include "ptdb200.h"
+
+namespace {
+
+struct UnitGeom {
+    int cin, cout, k, stride, pad, h_in, w_in, h_out, w_out;
+    long long m_out;
+};
+
+// conv1 1x1/1, conv2 3x3/stride, conv3 1x1/1, downsample 1x1/stride (on the block input)
+void geometry(int N, int H, int W, int inplanes, int planes, int stride, UnitGeom g[4]) {
+    const int OH = (H + 2 - 3) / stride + 1, OW = (W + 2 - 3) / stride + 1;
+    g[0] = {inplanes, planes, 1, 1, 0, H, W, H, W, (long long)N * H * W};
+    g[1] = {planes, planes, 3, stride, 1, H, W, OH, OW, (long long)N * OH * OW};
+    g[2] = {planes, planes * 4, 1, 1, 0, OH, OW, OH, OW, (long long)N * OH * OW};
+    g[3] = {inplanes, planes * 4, 1, stride, 0, H, W, OH, OW, (long long)N * OH * OW};
+}
+
+}  // namespace
+
+extern "C" int ptd_bottleneck_fwd(const PtdBottleneckFwd* d, void* stream) {
+    PTD_REQUIRE(d != nullptr, "bottleneck_fwd: null descriptor");
+    UnitGeom g[4];
+    geometry(d->N, d->H, d->W, d->inplanes, d->planes, d->stride, g);
+    const int nu = d->has_ds ? 4 : 3;
+    int off[5] = {0, 0, 0, 0, 0};
+    for (int i = 0; i < nu; ++i) off[i + 1] = off[i] + 2 * g[i].cout;
+    PTD_CUDA_CHECK(cudaMemsetAsync(d->stats, 0, (size_t)off[nu] * sizeof(float), (cudaStream_t)stream));
+    // order: conv1, conv2, (downsample), conv3 - conv3's BN consumes the identity / downsample output
+    const int order[4] = {0, 1, 3, 2};
+    for (int oi = 0; oi < 4; ++oi) {
+        const int i = order[oi];
+        if (i == 3 && !d->has_ds) continue;
+        const void* in = (i == 0 || i == 3) ? d->x : d->z[i - 1];
+        float* st = d->stats + off[i];
+        float* sv = d->saved + off[i];
+        int rc = ptd_conv_fprop(in, d->w[i], d->y[i], st, st + g[i].cout, d->N, g[i].h_in, g[i].w_in, g[i].cin, g[i].cout,
+                                g[i].k, g[i].k, g[i].stride, g[i].pad, stream);
+        if (rc) return rc;
+        const void* residual = nullptr;
+        int relu = 1;
+        if (i == 2) residual = d->has_ds ? d->z[3] : d->x;
+        if (i == 3) relu = 0;
+        rc = ptd_bn_apply(d->y[i], residual, d->z[i], st, st + g[i].cout, d->gamma[i], d->beta[i], d->running_mean[i],
+                          d->running_var[i], sv, sv + g[i].cout, g[i].m_out, g[i].cout, d->eps, d->momentum, relu, stream);
+        if (rc) return rc;
+    }
+    return PTD_OK;
+}
+
+extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
+    PTD_REQUIRE(d != nullptr, "bottleneck_bwd: null descriptor");
+    UnitGeom g[4];
+    geometry(d->N, d->H, d->W, d->inplanes, d->planes, d->stride, g);
+    const int nu = d->has_ds ? 4 : 3;
+    int off[5] = {0, 0, 0, 0, 0};
+    for (int i = 0; i < nu; ++i) off[i + 1] = off[i] + 2 * g[i].cout;
+    cudaStream_t st = (cudaStream_t)stream;
+    PTD_CUDA_CHECK(cudaMemsetAsync(d->sums, 0, (size_t)off[nu] * sizeof(float), st));
+    PTD_CUDA_CHECK(cudaMemsetAsync(d->dw_all, 0, (size_t)d->dw_all_bytes, st));
+    int rc;
+#define BN_BWD(i, dz_, relu_, gout_)                                                                                   \
+    do {                                                                                                               \
+        float* sm = d->sums + off[i];                                                                                  \
+        const float* sv = d->saved + off[i];                                                                           \
+        rc = ptd_bn_bwd_reduce(dz_, d->z[i], d->y[i], sv, sv + g[i].cout, sm, sm + g[i].cout, g[i].m_out, g[i].cout,   \
+                               relu_, stream);                                                                         \
+        if (rc) return rc;                                                                                             \
+        rc = ptd_bn_bwd_apply(dz_, d->z[i], d->y[i], sv, sv + g[i].cout, d->gamma[i], sm, sm + g[i].cout, d->dy[i],   \
+                              gout_, g[i].m_out, g[i].cout, relu_, stream);                                            \
+        if (rc) return rc;                                                                                             \
+    } while (0)
+#define DGRAD(i, dx_, addend_)                                                                                         \
+    do {                                                                                                               \
+        rc = ptd_conv_dgrad(d->dy[i], d->w[i], dx_, addend_, d->N, g[i].h_in, g[i].w_in, g[i].cin, g[i].cout, g[i].k,   \
+                            g[i].k, g[i].stride, g[i].pad, stream);                                                    \
+        if (rc) return rc;                                                                                             \
+    } while (0)
+#define WGRAD(i, in_)                                                                                                  \
+    do {                                                                                                               \
+        rc = ptd_conv_wgrad(in_, d->dy[i], d->dw[i], d->N, g[i].h_in, g[i].w_in, g[i].cin, g[i].cout, g[i].k, g[i].k,   \
+                            g[i].stride, g[i].pad, stream);                                                            \
+        if (rc) return rc;                                                                                             \
+    } while (0)
+
+    BN_BWD(2, d->dz, 1, d->g_id);            // last BN: also emits the masked gradient of the identity branch
+    DGRAD(2, d->dz2, nullptr);
+    WGRAD(2, d->z[1]);
+    BN_BWD(1, d->dz2, 1, nullptr);
+    DGRAD(1, d->dz1, nullptr);
+    WGRAD(1, d->z[0]);
+    BN_BWD(0, d->dz1, 1, nullptr);
+    if (d->has_ds) {
+        BN_BWD(3, d->g_id, 0, nullptr);
+        WGRAD(3, d->x);
+        DGRAD(0, d->dx, nullptr);
+        // the shortcut convolution adds into dx in place (stride 2 touches only the strided quarter)
+        rc = ptd_conv_dgrad_accum(d->dy[3], d->w[3], d->dx, d->N, g[3].h_in, g[3].w_in, g[3].cin, g[3].cout, 1, 1,
+                                  g[3].stride, 0, stream);
+        if (rc) return rc;
+    } else {
+        DGRAD(0, d->dx, d->g_id);
+    }
+    WGRAD(0, d->x);
+#undef BN_BWD
+#undef DGRAD
+#undef WGRAD
+    return PTD_OK;
+}

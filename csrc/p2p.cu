@@ -106,23 +106,26 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_f32_kernel(PeerPtrs pp, 
     const long long per = (n4 + WORLD - 1) / WORLD;
     const long long begin = min(n4, per * rank), end = min(n4, begin + per);
     const long long stride = (long long)gridDim.x * AR_THREADS;
-    constexpr int UNROLL = 4;
+    // All WORLD x UNROLL loads are issued before the first add: NVLink round trips are ~2-3 us, so the amount of
+    // data in flight per thread is what sets the achieved bandwidth.
+    constexpr int UNROLL = WORLD <= 4 ? 4 : 2;
     long long i = begin + (long long)blockIdx.x * AR_THREADS + threadIdx.x;
     for (; i + (UNROLL - 1) * stride < end; i += UNROLL * stride) {
-        float4 acc[UNROLL];
-#pragma unroll
-        for (int u = 0; u < UNROLL; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 v[WORLD][UNROLL];
 #pragma unroll
         for (int r = 0; r < WORLD; ++r) {
             const int src = (rank + r) % WORLD;        // start at the local copy, spread peers over time
-            float4 v[UNROLL];
 #pragma unroll
-            for (int u = 0; u < UNROLL; ++u) v[u] = ld_f4(reinterpret_cast<const float4*>(pp.buf[src]) + i + u * stride);
-#pragma unroll
-            for (int u = 0; u < UNROLL; ++u) { acc[u].x += v[u].x; acc[u].y += v[u].y; acc[u].z += v[u].z; acc[u].w += v[u].w; }
+            for (int u = 0; u < UNROLL; ++u) v[r][u] = ld_f4(reinterpret_cast<const float4*>(pp.buf[src]) + i + u * stride);
         }
+        float4 acc[UNROLL];
 #pragma unroll
-        for (int u = 0; u < UNROLL; ++u) { acc[u].x *= scale; acc[u].y *= scale; acc[u].z *= scale; acc[u].w *= scale; }
+        for (int u = 0; u < UNROLL; ++u) {
+            acc[u] = v[0][u];
+#pragma unroll
+            for (int r = 1; r < WORLD; ++r) { acc[u].x += v[r][u].x; acc[u].y += v[r][u].y; acc[u].z += v[r][u].z; acc[u].w += v[r][u].w; }
+            acc[u].x *= scale; acc[u].y *= scale; acc[u].z *= scale; acc[u].w *= scale;
+        }
 #pragma unroll
         for (int r = 0; r < WORLD; ++r) {
             const int dst = (rank + r) % WORLD;
@@ -240,7 +243,7 @@ int pick_blocks(long long work_items, int requested) {
     if (requested > 0) return requested > MAX_BLOCKS ? MAX_BLOCKS : requested;
     long long b = (work_items + AR_THREADS * 4 - 1) / (AR_THREADS * 4);
     if (b < 1) b = 1;
-    if (b > 64) b = 64;      // enough loads in flight to fill NVLink; leaves the other SMs to backward
+    if (b > 96) b = 96;      // enough loads in flight to fill NVLink; leaves the other SMs to backward
     return (int)b;
 }
 

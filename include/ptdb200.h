@@ -40,6 +40,45 @@ int ptd_stem_fprop(const void* x4, const void* w4, void* y, float* stat_sum, flo
                    void* stream);
 int ptd_stem_wgrad(const void* x4, const void* dy, float* dw4, int N, int H, int W, void* stream);
 
+/* ---- a whole residual bottleneck per call (conv1x1-BN-ReLU, conv3x3-BN-ReLU, conv1x1-BN (+identity | +downsample
+ *      conv-BN) -ReLU; torchvision Bottleneck, R/03 模型并行/03_model_parallel.ipynb#cell5).  Index 0..2 = conv1..conv3,
+ *      3 = downsample.  The caller owns every buffer; scratch / gradient buffers are zeroed by the call. ------------- */
+typedef struct {
+    int N, H, W, inplanes, planes, stride, has_ds;
+    float eps, momentum;
+    const void* x;                 /* block input  [N,H,W,inplanes] bf16 */
+    const void* w[4];              /* bf16 weights [Cout][R][S][Cin] */
+    const float* gamma[4];
+    const float* beta[4];
+    float* running_mean[4];
+    float* running_var[4];
+    void* y[4];                    /* conv outputs (kept for the backward) */
+    void* z[4];                    /* BN(+ReLU) outputs; z[2] is the block output */
+    float* stats;                  /* scratch, 2*sum(Cout) floats */
+    float* saved;                  /* out: per unit [mean | invstd], 2*sum(Cout) floats */
+} PtdBottleneckFwd;
+typedef struct {
+    int N, H, W, inplanes, planes, stride, has_ds;
+    const void* x;
+    const void* dz;                /* gradient of the block output */
+    const void* w[4];
+    const float* gamma[4];
+    const void* y[4];
+    const void* z[4];
+    const float* saved;
+    float* sums;                   /* out: per unit [dbeta | dgamma], 2*sum(Cout) floats */
+    void* dw_all;                  /* one buffer holding dw[0..3]; zeroed here */
+    long long dw_all_bytes;
+    float* dw[4];                  /* out: fp32 weight gradients [Cout][R][S][Cin] */
+    void* dy[4];                   /* scratch: gradients w.r.t. the conv outputs */
+    void* g_id;                    /* scratch: masked incoming gradient (identity-branch gradient) */
+    void* dz2;                     /* scratch: gradient w.r.t. z[1] */
+    void* dz1;                     /* scratch: gradient w.r.t. z[0] */
+    void* dx;                      /* out: gradient w.r.t. x */
+} PtdBottleneckBwd;
+int ptd_bottleneck_fwd(const PtdBottleneckFwd* d, void* stream);
+int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream);
+
 /* ---- dense layers (fc 2048->1000 of ResNet-50; cuBLAS in the reference) ----------------------- */
 int ptd_linear_fwd(const void* a, const void* w, const float* bias, float* out, int M, int N, int K, void* stream);
 int ptd_linear_dgrad(const void* dout, const void* w, void* da, int M, int N, int K, void* stream);

@@ -25,6 +25,8 @@ _SIGS: dict[str, list] = {
     "ptd_conv_dgrad": [P, P, P, P, I, I, I, I, I, I, I, I, I, P],
     "ptd_conv_dgrad_accum": [P, P, P, I, I, I, I, I, I, I, I, I, P],
     "ptd_conv_wgrad": [P, P, P, I, I, I, I, I, I, I, I, I, P],
+    "ptd_bottleneck_fwd": [P, P],
+    "ptd_bottleneck_bwd": [P, P],
     "ptd_stem_fprop": [P, P, P, P, P, I, I, I, P],
     "ptd_stem_wgrad": [P, P, P, I, I, I, P],
     "ptd_linear_fwd": [P, P, P, P, I, I, I, P],
@@ -56,6 +58,23 @@ _SIGS: dict[str, list] = {
     "ptd_small_linear_bwd": [P, P, P, P, P, P, I, I, I, P],
     "ptd_mlp_fwd": [P, P, P, P, P, I, I, P],
 }
+
+
+
+class BottleneckFwd(ctypes.Structure):
+    """Mirror of PtdBottleneckFwd (include/ptdb200.h)."""
+    _fields_ = [("N", I), ("H", I), ("W", I), ("inplanes", I), ("planes", I), ("stride", I), ("has_ds", I),
+                ("eps", F), ("momentum", F), ("x", P), ("w", P * 4), ("gamma", P * 4), ("beta", P * 4),
+                ("running_mean", P * 4), ("running_var", P * 4), ("y", P * 4), ("z", P * 4), ("stats", P), ("saved", P)]
+
+
+class BottleneckBwd(ctypes.Structure):
+    """Mirror of PtdBottleneckBwd (include/ptdb200.h)."""
+    _fields_ = [("N", I), ("H", I), ("W", I), ("inplanes", I), ("planes", I), ("stride", I), ("has_ds", I),
+                ("x", P), ("dz", P), ("w", P * 4), ("gamma", P * 4), ("y", P * 4), ("z", P * 4), ("saved", P),
+                ("sums", P), ("dw_all", P), ("dw_all_bytes", L), ("dw", P * 4), ("dy", P * 4), ("g_id", P), ("dz2", P),
+                ("dz1", P), ("dx", P)]
+
 
 _LIB: Optional[ctypes.CDLL] = None
 _LOAD_ERROR: Optional[str] = None
@@ -121,6 +140,8 @@ def _conv(a: Any):
         return None
     if isinstance(a, torch.Tensor):
         return a.data_ptr()
+    if isinstance(a, ctypes.Structure):
+        return ctypes.addressof(a)
     return a
 
 

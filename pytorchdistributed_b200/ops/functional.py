@@ -15,6 +15,7 @@ Reference call sites: every layer of torchvision ``ResNet(Bottleneck,[3,4,6,3])`
 """
 from __future__ import annotations
 
+import ctypes
 from typing import Optional, Tuple
 
 import torch
@@ -424,133 +425,135 @@ def small_linear(x, w, b, relu=False):
 # ------------------------------------------------------------------------------------------------
 # a whole residual bottleneck as ONE autograd node
 # ------------------------------------------------------------------------------------------------
+def _ptr4(ts):
+    arr = (ctypes.c_void_p * 4)()
+    for i, t in enumerate(ts):
+        arr[i] = t.data_ptr() if t is not None else None
+    return arr
+
+
 class _Bottleneck(torch.autograd.Function):
-    """conv1x1-BN-ReLU, conv3x3-BN-ReLU, conv1x1-BN (+identity or +downsample conv-BN) -ReLU.
+    """conv1x1-BN-ReLU, conv3x3-BN-ReLU, conv1x1-BN (+identity or +downsample conv-BN) -ReLU as ONE autograd node
+    whose forward and backward are ONE native call each (``csrc/block.cu``).
 
-    One node instead of four keeps the Python/autograd overhead per block small and lets the backward
-    fuse what autograd would do with separate kernels: the gradient of the identity branch (the masked
-    incoming gradient, emitted by the BN backward of the last unit) is added inside the epilogue of the
-    first convolution's data-gradient kernel, and all per-channel statistic / weight-gradient buffers of
-    the block are carved from one zero-filled allocation each.
+    One node instead of four keeps the Python/autograd overhead per block small and lets the backward fuse what
+    autograd would do with separate kernels: the gradient of the identity branch (the masked incoming gradient,
+    emitted by the BN backward of the last unit) is added inside the epilogue of the first convolution's
+    data-gradient kernel, the shortcut convolution's data gradient accumulates in place, and every buffer of the
+    block comes from two allocations per direction.
 
-    ``tensors`` = for each unit (conv1, conv2, conv3[, downsample]): weight, w_bf16, gamma, beta,
-    running_mean, running_var.  ``cfg`` = (stride, eps, momentum, has_downsample).
+    ``tensors`` = for each unit (conv1, conv2, conv3[, downsample]): weight, w_bf16, gamma, beta, running_mean,
+    running_var.  ``cfg`` = (stride, eps, momentum, has_downsample).
     """
 
     @staticmethod
     def forward(ctx, x, cfg, *tensors):
         stride, eps, momentum, has_ds = cfg
         x = as_nhwc_bf16(x)
-        units = [tensors[i * 6:(i + 1) * 6] for i in range(4 if has_ds else 3)]
-        couts = [u[0].shape[0] for u in units]
-        stats_all = torch.zeros(2 * sum(couts), device=x.device, dtype=torch.float32)
-        saved_all = torch.empty(2 * sum(couts), device=x.device, dtype=torch.float32)
-        offs, o = [], 0
-        for c in couts:
-            offs.append(o)
-            o += 2 * c
-
-        def unit(i, inp, s, pad, relu, residual=None):
-            w, wb, gamma, beta, rm, rv = units[i]
-            n, cin, h, wd = inp.shape
-            cout, _, r, _ = w.shape
-            oh, ow = out_hw(h, wd, r, r, s, pad)
-            y = _empty_act(n, cout, oh, ow, inp.device)
-            st = stats_all[offs[i]:offs[i] + 2 * cout]
-            sv = saved_all[offs[i]:offs[i] + 2 * cout]
-            _lib.call("ptd_conv_fprop", inp, wb, y, st[:cout], st[cout:], n, h, wd, cin, cout, r, r, s, pad, _stream())
-            z = torch.empty_like(y, memory_format=CL)
-            _lib.call("ptd_bn_apply", y, residual, z, st[:cout], st[cout:], gamma, beta, rm, rv, sv[:cout], sv[cout:],
-                      n * oh * ow, cout, float(eps), float(momentum), int(relu), _stream())
-            return y, z
-
-        y1, z1 = unit(0, x, 1, 0, True)
-        y2, z2 = unit(1, z1, stride, 1, True)
-        if has_ds:
-            yd, zd = unit(3, x, stride, 0, False)
-            identity = zd
-        else:
-            yd, identity = None, x
-        y3, z3 = unit(2, z2, 1, 0, True, residual=identity)
+        nu = 4 if has_ds else 3
+        units = [tensors[i * 6:(i + 1) * 6] for i in range(nu)]
+        n, inplanes, h, w = x.shape
+        planes = units[0][0].shape[0]
+        oh, ow = out_hw(h, w, 3, 3, stride, 1)
+        shapes = [(n, planes, h, w), (n, planes, oh, ow), (n, planes * 4, oh, ow), (n, planes * 4, oh, ow)][:nu]
+        couts = [s_[1] for s_ in shapes]
+        numels = [s_[0] * s_[1] * s_[2] * s_[3] for s_ in shapes]
+        # y tensors (kept for the backward) and z tensors in one allocation each
+        ybuf = torch.empty(sum(numels), device=x.device, dtype=torch.bfloat16)
+        zbuf = torch.empty(sum(numels), device=x.device, dtype=torch.bfloat16)
+        ys, zs, o = [], [], 0
+        for shp, nel in zip(shapes, numels):
+            nn_, c_, h_, w_ = shp
+            strides = (h_ * w_ * c_, 1, w_ * c_, c_)
+            ys.append(torch.as_strided(ybuf, shp, strides, o))
+            zs.append(torch.as_strided(zbuf, shp, strides, o))
+            o += nel
+        fbuf = torch.empty(4 * sum(couts), device=x.device, dtype=torch.float32)   # [stats | saved]
+        stats, saved = fbuf[:2 * sum(couts)], fbuf[2 * sum(couts):]
+        d = _lib.BottleneckFwd()
+        d.N, d.H, d.W, d.inplanes, d.planes, d.stride, d.has_ds = n, h, w, inplanes, planes, stride, int(has_ds)
+        d.eps, d.momentum = float(eps), float(momentum)
+        d.x = x.data_ptr()
+        d.w = _ptr4([u[1] for u in units])
+        d.gamma = _ptr4([u[2] for u in units])
+        d.beta = _ptr4([u[3] for u in units])
+        d.running_mean = _ptr4([u[4] for u in units])
+        d.running_var = _ptr4([u[5] for u in units])
+        d.y, d.z = _ptr4(ys), _ptr4(zs)
+        d.stats, d.saved = stats.data_ptr(), saved.data_ptr()
+        _lib.call("ptd_bottleneck_fwd", d, _stream())
         ctx.cfg = cfg
-        ctx.offs = offs
+        ctx.geom = (n, h, w, inplanes, planes, shapes)
         ctx.w_shapes = [tuple(u[0].shape) for u in units]
-        keep = [x, y1, z1, y2, z2, y3, z3, saved_all] + [u[1] for u in units] + [u[2] for u in units]
-        if has_ds:
-            keep += [yd, zd]
-        ctx.save_for_backward(*keep)
-        return z3
+        ctx.save_for_backward(x, ybuf, zbuf, saved, *[u[1] for u in units], *[u[2] for u in units])
+        return zs[2]
 
     @staticmethod
     def backward(ctx, dz):
         stride, eps, momentum, has_ds = ctx.cfg
         nu = 4 if has_ds else 3
+        n, h, w, inplanes, planes, shapes = ctx.geom
         sv_t = ctx.saved_tensors
-        x, y1, z1, y2, z2, y3, z3, saved_all = sv_t[:8]
-        wbs = sv_t[8:8 + nu]
-        gammas = sv_t[8 + nu:8 + 2 * nu]
-        yd, zd = (sv_t[8 + 2 * nu], sv_t[9 + 2 * nu]) if has_ds else (None, None)
-        offs, w_shapes = ctx.offs, ctx.w_shapes
+        x, ybuf, zbuf, saved = sv_t[:4]
+        wbs = sv_t[4:4 + nu]
+        gammas = sv_t[4 + nu:4 + 2 * nu]
+        w_shapes = ctx.w_shapes
         dz = as_nhwc_bf16(dz)
         dev = dz.device
-        couts = [s[0] for s in w_shapes]
-        sums_all = torch.zeros(2 * sum(couts), device=dev, dtype=torch.float32)
-        w_numels = [s[0] * s[1] * s[2] * s[3] for s in w_shapes]
-        dw_all = torch.zeros(sum(w_numels), device=dev, dtype=torch.float32)
+        couts = [s_[1] for s_ in shapes]
+        numels = [s_[0] * s_[1] * s_[2] * s_[3] for s_ in shapes]
+        esz = 2
+        ys_ptr, zs_ptr, o = [], [], 0
+        for nel in numels:
+            ys_ptr.append(ybuf.data_ptr() + o * esz)
+            zs_ptr.append(zbuf.data_ptr() + o * esz)
+            o += nel
+        # scratch: dy per unit, g_id (block-output sized), dz2 (z[1] sized), dz1 (z[0] sized); output dx
+        x_numel = x.numel()
+        sizes = numels + [numels[2], numels[1], numels[0], x_numel]
+        abuf = torch.empty(sum(sizes), device=dev, dtype=torch.bfloat16)
+        offs, o = [], 0
+        for sz in sizes:
+            offs.append(o)
+            o += sz
+        base = abuf.data_ptr()
+        w_numels = [s_[0] * s_[1] * s_[2] * s_[3] for s_ in w_shapes]
+        gbuf = torch.empty(2 * sum(couts) + sum(w_numels), device=dev, dtype=torch.float32)   # [sums | dw_all]
+        sums = gbuf[:2 * sum(couts)]
+        dw_all = gbuf[2 * sum(couts):]
         dws, o = [], 0
         for shp, nel in zip(w_shapes, w_numels):
             co, ci, r, s_ = shp
-            dws.append(torch.as_strided(dw_all, shp, (ci * r * s_, 1, s_ * ci, ci), o))   # channels_last view
+            # as_strided offsets are absolute in the storage: dw_all starts after the sums
+            dws.append(torch.as_strided(gbuf, shp, (ci * r * s_, 1, s_ * ci, ci), 2 * sum(couts) + o))   # channels_last view
             o += nel
-
-        def bn_bwd(i, dzz, z, y, relu, want_g):
+        d = _lib.BottleneckBwd()
+        d.N, d.H, d.W, d.inplanes, d.planes, d.stride, d.has_ds = n, h, w, inplanes, planes, stride, int(has_ds)
+        d.x, d.dz = x.data_ptr(), dz.data_ptr()
+        d.w, d.gamma = _ptr4(wbs), _ptr4(gammas)
+        ya, za = (ctypes.c_void_p * 4)(), (ctypes.c_void_p * 4)()
+        for i in range(nu):
+            ya[i], za[i] = ys_ptr[i], zs_ptr[i]
+        d.y, d.z = ya, za
+        d.saved, d.sums = saved.data_ptr(), sums.data_ptr()
+        d.dw_all, d.dw_all_bytes = dw_all.data_ptr(), dw_all.numel() * 4
+        d.dw = _ptr4(dws)
+        dya = (ctypes.c_void_p * 4)()
+        for i in range(nu):
+            dya[i] = base + offs[i] * esz
+        d.dy = dya
+        d.g_id = base + offs[nu] * esz
+        d.dz2 = base + offs[nu + 1] * esz
+        d.dz1 = base + offs[nu + 2] * esz
+        d.dx = base + offs[nu + 3] * esz
+        _lib.call("ptd_bottleneck_bwd", d, _stream())
+        xs = x.shape
+        dx = torch.as_strided(abuf, xs, (xs[2] * xs[3] * xs[1], 1, xs[3] * xs[1], xs[1]), offs[nu + 3])
+        so, grads = 0, [dx, None]
+        for i in range(nu):
             c = couts[i]
-            sv = saved_all[offs[i]:offs[i] + 2 * c]
-            sm = sums_all[offs[i]:offs[i] + 2 * c]
-            n, _, h, w = y.shape
-            m = n * h * w
-            _lib.call("ptd_bn_bwd_reduce", dzz, z, y, sv[:c], sv[c:], sm[:c], sm[c:], m, c, int(relu), _stream())
-            dy = torch.empty_like(y, memory_format=CL)
-            g = torch.empty_like(y, memory_format=CL) if want_g else None
-            _lib.call("ptd_bn_bwd_apply", dzz, z, y, sv[:c], sv[c:], gammas[i], sm[:c], sm[c:], dy, g, m, c, int(relu),
-                      _stream())
-            return dy, g, sm[c:], sm[:c]          # dy, masked grad, dgamma, dbeta
-
-        def dgrad(i, dy, inp_shape, s, pad, addend=None):
-            n, cin, h, w = inp_shape
-            cout, _, r, _ = w_shapes[i]
-            dx = _empty_act(n, cin, h, w, dev)
-            _lib.call("ptd_conv_dgrad", dy, wbs[i], dx, addend, n, h, w, cin, cout, r, r, s, pad, _stream())
-            return dx
-
-        def wgrad(i, inp, dy, s, pad):
-            n, cin, h, w = inp.shape
-            cout, _, r, _ = w_shapes[i]
-            _lib.call("ptd_conv_wgrad", inp, dy, dws[i], n, h, w, cin, cout, r, r, s, pad, _stream())
-
-        dy3, g_id, dg3, db3 = bn_bwd(2, dz, z3, y3, True, True)
-        dz2 = dgrad(2, dy3, z2.shape, 1, 0)
-        wgrad(2, z2, dy3, 1, 0)
-        dy2, _, dg2, db2 = bn_bwd(1, dz2, z2, y2, True, False)
-        dz1 = dgrad(1, dy2, z1.shape, stride, 1)
-        wgrad(1, z1, dy2, stride, 1)
-        dy1, _, dg1, db1 = bn_bwd(0, dz1, z1, y1, True, False)
-        if has_ds:
-            dyd, _, dgd, dbd = bn_bwd(3, g_id, zd, yd, False, False)
-            wgrad(3, x, dyd, stride, 0)
-            dx = dgrad(0, dy1, x.shape, 1, 0)
-            # shortcut branch accumulates straight into dx (stride 2: only the strided quarter is touched)
-            n, cin, h, w = x.shape
-            _lib.call("ptd_conv_dgrad_accum", dyd, wbs[3], dx, n, h, w, cin, w_shapes[3][0], 1, 1, stride, 0, _stream())
-        else:
-            dx = dgrad(0, dy1, x.shape, 1, 0, addend=g_id)
-        wgrad(0, x, dy1, 1, 0)
-        grads = [dx, None,
-                 dws[0], None, dg1, db1, None, None,
-                 dws[1], None, dg2, db2, None, None,
-                 dws[2], None, dg3, db3, None, None]
-        if has_ds:
-            grads += [dws[3], None, dgd, dbd, None, None]
+            grads += [dws[i], None, sums[so + c:so + 2 * c], sums[so:so + c], None, None]
+            so += 2 * c
         return tuple(grads)
 
 

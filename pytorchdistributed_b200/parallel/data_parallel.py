@@ -313,7 +313,16 @@ class _ParallelApply(torch.autograd.Function):
                 ev.record(torch.cuda.current_stream(rep.device))
                 return ev
 
-        evs = dp.parallel_apply(run, len(reps))
+        # The replica that lives on this node's own device must run its backward on THIS thread (re-entrant
+        # autograd): its nodes belong to the engine thread we are occupying, a pool thread would wait for it forever.
+        # The other replicas run from pool threads and overlap with it.
+        here = grad_out.device
+        futs = {i: dp._pool.submit(run, i) for i in range(len(reps)) if reps[i].device != here}
+        evs = []
+        for i in range(len(reps)):
+            if reps[i].device == here:
+                evs.append(run(i))
+        evs += [f.result() for f in futs.values()]
         with torch.cuda.device(root.device), torch.no_grad():
             st = torch.cuda.current_stream(root.device)
             for ev in evs:

@@ -88,11 +88,14 @@ class Trainer:
         try:
             sx, sy = xs.clone(), ys.clone()
             torch.cuda.synchronize(self.device)
+            from .. import _lib
             graph = torch.cuda.CUDAGraph()
+            l0 = _lib.LAUNCHES
             with torch.cuda.graph(graph):
                 loss = self._step_eager(sx, sy)
             torch.cuda.synchronize(self.device)
-            self._graph = {"graph": graph, "x": sx, "y": sy, "loss": loss}
+            # "launches": native entry-point calls recorded into the graph (each replay re-issues them on the device)
+            self._graph = {"graph": graph, "x": sx, "y": sy, "loss": loss, "launches": _lib.LAUNCHES - l0}
         except Exception as e:  # noqa: BLE001 - fall back to eager, keep training
             self._graph_failed = True
             self._graph = None
@@ -112,6 +115,49 @@ class Trainer:
             xs = xs.to(self.device, non_blocking=True)
             ys = ys.to(self.device, non_blocking=True)
             self._run_batch(xs, ys)
+
+    def run_batches(self, batches):
+        """Train on an iterable of HOST batches ``(xs, ys)`` (pinned memory recommended) and return the per-step
+        losses as Python floats.  The copy of batch i+1 runs on a side stream while step i computes, and the loss of
+        step i is read back (device -> host) while step i+1 runs, so neither transfer stalls the GPU."""
+        if self.device.type != "cuda":
+            return [float(self._run_batch(xs, ys)) for xs, ys in batches]
+        if not hasattr(self, "_copy_stream"):
+            self._copy_stream = torch.cuda.Stream(self.device)
+        it = iter(batches)
+        cur_stream = torch.cuda.current_stream(self.device)
+
+        def stage(batch):
+            with torch.cuda.stream(self._copy_stream):
+                xs = batch[0].to(self.device, non_blocking=True)
+                ys = batch[1].to(self.device, non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self._copy_stream)
+            return xs, ys, ev
+
+        losses, pending = [], None
+        nxt = next(it, None)
+        staged = stage(nxt) if nxt is not None else None
+        while staged is not None:
+            xs, ys, ev = staged
+            cur_stream.wait_event(ev)
+            xs.record_stream(cur_stream)
+            ys.record_stream(cur_stream)
+            loss = self._run_batch(xs, ys)
+            nxt = next(it, None)
+            staged = stage(nxt) if nxt is not None else None       # overlaps with the step just launched
+            host = torch.empty(1, dtype=torch.float32, pin_memory=True)
+            host.copy_(loss.detach().reshape(1).float(), non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(cur_stream)
+            if pending is not None:                                  # read the previous step's loss now
+                pending[1].synchronize()
+                losses.append(float(pending[0]))
+            pending = (host, done)
+        if pending is not None:
+            pending[1].synchronize()
+            losses.append(float(pending[0]))
+        return losses
 
     def train(self, max_epoch: int):
         for epoch in range(self.epochs_run, max_epoch):
