@@ -17,6 +17,8 @@
 // Replaces what the reference reaches through NCCL: DDP's bucket all-reduce and parameter/buffer
 // broadcast (R/02 DDP基本概念/ddp_gpus.py:35,41) and nn.DataParallel's
 // broadcast_coalesced / gather / reduce_add_coalesced (R/01 数据并行/...ipynb#cell5-6; K6-K9).
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "ptdb200.h"
 
@@ -88,6 +90,16 @@ __device__ __forceinline__ float4 ld_f4(const float4* p) {
 __device__ __forceinline__ void st_f4(float4* p, const float4& v) {
     asm volatile("st.global.relaxed.sys.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
+// Weak variants: the data itself needs no per-access system-scope ordering - the release/acquire flag barriers
+// (plus __threadfence_system) order it.  L1::no_allocate keeps once-read peer lines out of L1.
+__device__ __forceinline__ float4 ld_f4_weak(const float4* p) {
+    float4 v;
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void st_f4_weak(float4* p, const float4& v) {
+    asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
 __device__ __forceinline__ uint4 ld_u4(const uint4* p) {
     uint4 v;
     asm volatile("ld.global.relaxed.sys.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
@@ -99,7 +111,7 @@ __device__ __forceinline__ void st_u4(uint4* p, const uint4& v) {
 
 // ---- two-shot all-reduce, fp32 storage ------------------------------------------------------------
 // n4 = number of float4 elements (buffer length is padded to a multiple of 4 floats by the caller).
-template <int WORLD>
+template <int WORLD, bool WEAK>
 __global__ void __launch_bounds__(AR_THREADS) allreduce_f32_kernel(PeerPtrs pp, int rank, long long n4, float scale) {
     const uint32_t seq = seq_begin(pp, rank);
     rank_barrier(pp, rank, WORLD, seq);
@@ -116,7 +128,7 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_f32_kernel(PeerPtrs pp, 
         for (int r = 0; r < WORLD; ++r) {
             const int src = (rank + r) % WORLD;        // start at the local copy, spread peers over time
 #pragma unroll
-            for (int u = 0; u < UNROLL; ++u) v[r][u] = ld_f4(reinterpret_cast<const float4*>(pp.buf[src]) + i + u * stride);
+            for (int u = 0; u < UNROLL; ++u) v[r][u] = (WEAK ? ld_f4_weak : ld_f4)(reinterpret_cast<const float4*>(pp.buf[src]) + i + u * stride);
         }
         float4 acc[UNROLL];
 #pragma unroll
@@ -130,19 +142,19 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_f32_kernel(PeerPtrs pp, 
         for (int r = 0; r < WORLD; ++r) {
             const int dst = (rank + r) % WORLD;
 #pragma unroll
-            for (int u = 0; u < UNROLL; ++u) st_f4(reinterpret_cast<float4*>(pp.buf[dst]) + i + u * stride, acc[u]);
+            for (int u = 0; u < UNROLL; ++u) (WEAK ? st_f4_weak : st_f4)(reinterpret_cast<float4*>(pp.buf[dst]) + i + u * stride, acc[u]);
         }
     }
     for (; i < end; i += stride) {
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
         for (int r = 0; r < WORLD; ++r) {
-            const float4 v = ld_f4(reinterpret_cast<const float4*>(pp.buf[(rank + r) % WORLD]) + i);
+            const float4 v = (WEAK ? ld_f4_weak : ld_f4)(reinterpret_cast<const float4*>(pp.buf[(rank + r) % WORLD]) + i);
             acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
         }
         acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
 #pragma unroll
-        for (int r = 0; r < WORLD; ++r) st_f4(reinterpret_cast<float4*>(pp.buf[(rank + r) % WORLD]) + i, acc);
+        for (int r = 0; r < WORLD; ++r) (WEAK ? st_f4_weak : st_f4)(reinterpret_cast<float4*>(pp.buf[(rank + r) % WORLD]) + i, acc);
     }
     rank_barrier(pp, rank, WORLD, seq + 1);
     seq_end(pp, rank, seq + 1);
@@ -318,10 +330,13 @@ extern "C" int ptd_allreduce_inplace(const void* const* bufs, const void* const*
     const long long nvec = numel / per_vec;
     const int grid = pick_blocks((nvec + world - 1) / world, blocks);
     cudaStream_t st = (cudaStream_t)stream;
+    static int weak = -1;
+    if (weak < 0) { const char* e = getenv("PTDB200_AR_WEAK"); weak = e ? atoi(e) : 1; }
 #define PTD_AR(W)                                                                                   \
     case W:                                                                                         \
         if (is_bf16) allreduce_bf16_kernel<W><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale); \
-        else allreduce_f32_kernel<W><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale);      \
+        else if (weak) allreduce_f32_kernel<W, true><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale); \
+        else allreduce_f32_kernel<W, false><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale);      \
         break;
     switch (world) {
         PTD_AR(1) PTD_AR(2) PTD_AR(3) PTD_AR(4) PTD_AR(5) PTD_AR(6) PTD_AR(7) PTD_AR(8)
