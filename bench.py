@@ -224,8 +224,9 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--batch", type=int, default=256, help="per-GPU batch (BASELINE config: 256)")
     ap.add_argument("--img", type=int, default=224)
-    ap.add_argument("--graph", type=int, default=int(os.environ.get("PTDB200_BENCH_GRAPH", "0")),
-                    help="replay the whole training step from a CUDA graph (ours arm)")
+    ap.add_argument("--graph", type=int, default=int(os.environ.get("PTDB200_BENCH_GRAPH", "1")),
+                    help="ours arm: Trainer(cuda_graph=True) - replay the whole step (fwd, bwd with the overlapped all-reduce, "
+                         "optimizer) from one CUDA graph after an eager warm-up; falls back to eager if capture fails")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

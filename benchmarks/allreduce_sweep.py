@@ -4,8 +4,10 @@
         benchmarks/allreduce_sweep.py [--max-mb 1024] [--out gpurun_out/allreduce_N.json]
 
 Per size: CUDA-event time of `iters` back-to-back calls after warm-up, max over ranks.  Bus bandwidth is
-2(N-1)/N * bytes / time; the roofline is the pool's measured NVLink peer-copy rate (770 GB/s per direction,
-B200_PROFILING.md) - each GPU must move (N-1)/N of the buffer in each direction.
+2(N-1)/N * bytes / time = the bytes every GPU must push through EACH direction of its NVLink port (it serves its
+peers' reads of (N-1)/N of its buffer and writes its reduced slice to N-1 peers; symmetrically on the way in),
+so the roofline is bus bandwidth / 770 GB/s, the pool's measured peer-copy rate per direction (B200_PROFILING.md).
+`benchmarks/p2p_bw.py` measures what the link gives plain push / pull kernels on the same box (680-715 GB/s).
 """
 import argparse
 import json
@@ -65,7 +67,7 @@ def main():
         bus = 2.0 * (world - 1) / world * size
         row = {"bytes": size, "ours_us": round(t_ours, 2), "nccl_us": round(t_nccl, 2),
                "ours_busbw_gbs": round(bus / t_ours / 1e3, 1), "nccl_busbw_gbs": round(bus / t_nccl / 1e3, 1),
-               "frac_nvlink_roofline_of_measured": round(bus / 2 / t_ours / 1e3 / NVLINK_GBS, 3), "correct": ok}
+               "frac_nvlink_roofline_of_measured": round(bus / t_ours / 1e3 / NVLINK_GBS, 3), "correct": ok}
         rows.append(row)
         if rank == 0:
             print(f"{size:>11d} B  ours {t_ours:9.1f} us ({row['ours_busbw_gbs']:7.1f} GB/s bus, "

@@ -167,6 +167,8 @@ int ptd_broadcast_inplace(const void* const* bufs, const void* const* pads, int 
 int ptd_p2p_barrier(const void* const* pads, int rank, int world, void* stream);
 /* single process, several devices: copy / sum over peer pointers from a kernel on the current device */
 int ptd_peer_copy(void* dst, const void* src, long long nbytes, void* stream);
+/* same through the bulk-copy engine (cp.async.bulk both ways); nbytes a multiple of 16 KiB */
+int ptd_peer_copy_bulk(void* dst, const void* src, long long nbytes, int blocks, void* stream);
 int ptd_reduce_sum_f32(float* dst, const void* const* srcs, int n_src, long long numel, float scale, int accumulate,
                        void* stream);
 

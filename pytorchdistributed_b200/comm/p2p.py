@@ -37,6 +37,7 @@ _lib.register("ptd_broadcast_inplace", [P, P, I, I, I, L, I, P])
 _lib.register("ptd_p2p_barrier", [P, I, I, P])
 _lib.register("ptd_peer_copy", [P, P, L, P])
 _lib.register("ptd_reduce_sum_f32", [P, P, I, L, F, I, P])
+_lib.register("ptd_peer_copy_bulk", [P, P, L, I, P])
 
 _LIVE: "weakref.WeakSet[SymmetricBuffer]" = weakref.WeakSet()
 
