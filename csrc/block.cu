@@ -8,7 +8,10 @@
 //
 // The caller (ops/functional.py: _Bottleneck) owns all memory: it passes the activations to keep for the backward,
 // and scratch / gradient buffers that are zeroed here with cudaMemsetAsync.
+#include <stdlib.h>
 #include <string.h>
+
+#include <mutex>
 
 #include "common.cuh"
 #include "ptdb200.h"
@@ -27,6 +30,35 @@ void geometry(int N, int H, int W, int inplanes, int planes, int stride, UnitGeo
     g[1] = {planes, planes, 3, stride, 1, H, W, OH, OW, (long long)N * OH * OW};
     g[2] = {planes, planes * 4, 1, 1, 0, OH, OW, OH, OW, (long long)N * OH * OW};
     g[3] = {inplanes, planes * 4, 1, stride, 0, H, W, OH, OW, (long long)N * OH * OW};
+}
+
+// One side stream + a ring of events per device: the weight-gradient kernels of a block only depend on the BN
+// backward of their own unit, so they run beside the data-gradient chain and fill the tails of the small
+// late-stage GEMMs (98 tiles on 148 SMs).  Fork/join is event-based, so it is also recorded when the step is
+// being captured into a CUDA graph.
+struct SideStream {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[16] = {nullptr};
+    int next = 0;
+};
+SideStream* side_stream() {
+    static SideStream per_dev[64];
+    static std::mutex mu;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lk(mu);
+    SideStream& s = per_dev[dev];
+    if (s.stream == nullptr) {
+        if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        for (auto& e : s.ev)
+            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    }
+    return &s;
+}
+bool overlap_enabled() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("PTDB200_WGRAD_OVERLAP"); v = e ? atoi(e) : 1; }
+    return v == 1;
 }
 
 }  // namespace
@@ -91,11 +123,19 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
     } while (0)
 #define WGRAD(i, in_)                                                                                                  \
     do {                                                                                                               \
+        void* ws = stream;                                                                                             \
+        if (side != nullptr) {      /* fork: the side stream waits for everything issued so far (dy[i] is ready) */     \
+            cudaEvent_t e = side->ev[side->next++ & 15];                                                               \
+            PTD_CUDA_CHECK(cudaEventRecord(e, st));                                                                    \
+            PTD_CUDA_CHECK(cudaStreamWaitEvent(side->stream, e, 0));                                                   \
+            ws = (void*)side->stream;                                                                                  \
+        }                                                                                                              \
         rc = ptd_conv_wgrad(in_, d->dy[i], d->dw[i], d->N, g[i].h_in, g[i].w_in, g[i].cin, g[i].cout, g[i].k, g[i].k,   \
-                            g[i].stride, g[i].pad, stream);                                                            \
+                            g[i].stride, g[i].pad, ws);                                                                \
         if (rc) return rc;                                                                                             \
     } while (0)
 
+    SideStream* side = overlap_enabled() ? side_stream() : nullptr;
     BN_BWD(2, d->dz, 1, d->g_id);            // last BN: also emits the masked gradient of the identity branch
     DGRAD(2, d->dz2, nullptr);
     WGRAD(2, d->z[1]);
@@ -115,6 +155,11 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
         DGRAD(0, d->dx, d->g_id);
     }
     WGRAD(0, d->x);
+    if (side != nullptr) {          // join: the caller's stream continues only after the last weight gradient
+        cudaEvent_t e = side->ev[side->next++ & 15];
+        PTD_CUDA_CHECK(cudaEventRecord(e, side->stream));
+        PTD_CUDA_CHECK(cudaStreamWaitEvent(st, e, 0));
+    }
 #undef BN_BWD
 #undef DGRAD
 #undef WGRAD
