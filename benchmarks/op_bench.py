@@ -55,6 +55,7 @@ def main():
     ap.add_argument("--only", default=None)
     ap.add_argument("--once", action="store_true")
     ap.add_argument("--out", default=None)
+    ap.add_argument("--bn", action="store_true", help="with --once: also run the BN passes on the layer's output")
     args = ap.parse_args()
     dev = "cuda"
     peaks = {"bf16_tflops": 1643.2, "hbm_gbs": 6555.8}
@@ -92,6 +93,14 @@ def main():
             print(f"{name:28s} {opn:6s} {us:9.1f} us  {tf:7.1f} TFLOP/s ({tf / peaks['bf16_tflops']:.2f} of measured peak)"
                   f"  {gbs:6.0f} GB/s min-traffic ({gbs / peaks['hbm_gbs']:.2f} of measured HBM)", flush=True)
         # BN passes on this layer's output
+        if args.once and args.bn:
+            c = cout
+            gamma, beta = torch.ones(c, device=dev), torch.zeros(c, device=dev)
+            rm, rv = torch.zeros(c, device=dev), torch.ones(c, device=dev)
+            stats = K.bn_stats_raw(dy)
+            z, saved = K.bn_apply_raw(dy, stats, gamma, beta, rm, rv, 1e-5, 0.1, True)
+            K.bn_backward_raw(dy, z, dy, saved, gamma, True, False)
+            torch.cuda.synchronize()
         if not args.once and not args.only:
             c = cout
             y = dy

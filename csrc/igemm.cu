@@ -384,9 +384,9 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
         // ===================== Epilogue =====================
         const int q = warp & 3;
         const int half = warp >> 2;
-        float acc_sum[Cfg::CHUNKS_PER_WARP], acc_sq[Cfg::CHUNKS_PER_WARP];
-#pragma unroll
-        for (int c = 0; c < Cfg::CHUNKS_PER_WARP; ++c) acc_sum[c] = acc_sq[c] = 0.f;
+        // per-chunk BN partial sums, kept in four scalar pairs so the chunk loop need not be unrolled (the unrolled
+        // butterfly made the epilogue stall on instruction fetch: ncu stall_no_inst 27 %)
+        float as0 = 0.f, as1 = 0.f, as2 = 0.f, as3 = 0.f, aq0 = 0.f, aq1 = 0.f, aq2 = 0.f, aq3 = 0.f;
         const bool do_stats = (EPI == 0) && p.stat_sum != nullptr;
         int it = 0;
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
@@ -396,7 +396,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
             const bool row_ok = m < p.M;      // fp32 epilogue: one row per lane
             mbar_wait(&bars->tmem_full[acc], acc_phase);
             tc_fence_after();
-#pragma unroll
+#pragma unroll 1
             for (int c = 0; c < Cfg::CHUNKS_PER_WARP; ++c) {
                 const int col = half * (BLOCK_N / 2) + c * 32;
                 uint32_t raw[32];
@@ -458,8 +458,11 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                         float sq[32];
 #pragma unroll
                         for (int i = 0; i < 32; ++i) sq[i] = v[i] * v[i];
-                        acc_sum[c] += transpose_reduce32(v, lane);
-                        acc_sq[c] += transpose_reduce32(sq, lane);
+                        const float cs = transpose_reduce32(v, lane), cq = transpose_reduce32(sq, lane);
+                        as0 += c == 0 ? cs : 0.f; aq0 += c == 0 ? cq : 0.f;
+                        as1 += c == 1 ? cs : 0.f; aq1 += c == 1 ? cq : 0.f;
+                        as2 += c == 2 ? cs : 0.f; aq2 += c == 2 ? cq : 0.f;
+                        as3 += c == 3 ? cs : 0.f; aq3 += c == 3 ? cq : 0.f;
                     }
                 } else {
                     if (row_ok) {
@@ -476,11 +479,12 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
             mbar_arrive(&bars->tmem_empty[acc]);
         }
         if (do_stats) {
+            const float fs[4] = {as0, as1, as2, as3}, fq[4] = {aq0, aq1, aq2, aq3};
 #pragma unroll
             for (int c = 0; c < Cfg::CHUNKS_PER_WARP; ++c) {
                 const int n = n0 + half * (BLOCK_N / 2) + c * 32 + lane;
-                atomicAdd(p.stat_sum + n, acc_sum[c]);
-                atomicAdd(p.stat_sq + n, acc_sq[c]);
+                atomicAdd(p.stat_sum + n, fs[c]);
+                atomicAdd(p.stat_sq + n, fq[c]);
             }
         }
     } else if (!A_TMA) {
@@ -734,7 +738,12 @@ int launch_w(WParams& p, cudaStream_t stream) {
     p.n_blocks = p.Kw / (64 * NSUB);
     p.num_kb = ceil_div_i(p.P, 64);
     const int tiles = p.m_blocks * p.n_blocks;
-    int splits = ceil_div_i(2 * ptd_num_sms(), tiles);          // ~2 CTAs per SM keeps the tail short
+    // One CTA per SM (shared memory) => size the grid to whole waves.  ncu: a 2.07-wave grid (306 CTAs) took three
+    // CTA lifetimes, each with ~20 us of fixed cost (TMEM alloc, pipeline fill, 32K reduction atomics) around a
+    // ~17 us main loop; one wave with a longer K range per CTA halves the kernel.
+    static float waves = -1.f;
+    if (waves < 0.f) { const char* e = getenv("PTD_WGRAD_WAVES"); waves = e ? (float)atof(e) : 1.f; }
+    int splits = (int)(ptd_num_sms() * waves) / tiles;
     if (splits > p.num_kb) splits = p.num_kb;
     if (splits < 1) splits = 1;
     p.kb_per_split = ceil_div_i(p.num_kb, splits);

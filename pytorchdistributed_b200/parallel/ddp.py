@@ -30,6 +30,7 @@ import torch.distributed as dist
 from torch import nn
 
 from .. import _lib
+from ..utils.nvtx import nvtx_range
 
 _MiB = 1024 * 1024
 
@@ -319,7 +320,7 @@ class DistributedDataParallel(nn.Module):
         if self._comm_stream is not None:
             b.ready_event.record(torch.cuda.current_stream(self.device))
             self._comm_stream.wait_event(b.ready_event)
-            with torch.cuda.stream(self._comm_stream):
+            with torch.cuda.stream(self._comm_stream), nvtx_range("ddp/bucket_allreduce"):
                 self.backend.all_reduce_avg(b.flat)
                 b.done_event.record(self._comm_stream)
         else:

@@ -25,13 +25,16 @@ from torch.utils.data import DataLoader
 
 from ..ops import functional as K
 from ..parallel.ddp import DistributedDataParallel as DDP
+from ..utils.metrics import JsonlWriter, StepMeter
+from ..utils.nvtx import nvtx_range
 
 
 class Trainer:
     def __init__(self, model: torch.nn.Module, train_dataloader: DataLoader, optimizer: torch.optim.Optimizer,
                  gpu_id: Optional[int] = None, *, save_every: int = 0, snapshot_path: str = "snapshot.pt",
                  loss_fn: Optional[Callable] = None, resume: bool = False, ddp_kwargs: Optional[dict] = None,
-                 quiet: bool = False, cuda_graph: bool = False, graph_warmup: int = 3) -> None:
+                 quiet: bool = False, cuda_graph: bool = False, graph_warmup: int = 3,
+                 metrics_path: Optional[str] = None) -> None:
         self.gpu_id = int(os.environ.get("LOCAL_RANK", 0)) if gpu_id is None else gpu_id
         self.device = torch.device("cuda", self.gpu_id) if torch.cuda.is_available() else torch.device("cpu")
         self.model = model.to(self.device)
@@ -43,6 +46,8 @@ class Trainer:
         self.quiet = quiet
         self.epochs_run = 0
         self.last_loss: Optional[torch.Tensor] = None
+        self.meter = StepMeter(self.device)
+        self._metrics = JsonlWriter(metrics_path if self._is_rank0() else None)
         if resume and os.path.exists(snapshot_path):
             self._load_snapshot(snapshot_path)
         kw = dict(ddp_kwargs or {})
@@ -111,10 +116,14 @@ class Trainer:
         sampler = getattr(self.train_dataloader, "sampler", None)
         if hasattr(sampler, "set_epoch"):
             sampler.set_epoch(epoch)
-        for xs, ys in self.train_dataloader:
+        for step, (xs, ys) in enumerate(self.train_dataloader):
             xs = xs.to(self.device, non_blocking=True)
             ys = ys.to(self.device, non_blocking=True)
-            self._run_batch(xs, ys)
+            with nvtx_range(f"train_step/e{epoch}"):
+                self._run_batch(xs, ys)
+            stats = self.meter.step(len(xs))
+            if stats is not None:
+                self._metrics.write(epoch=epoch, step=step, loss=float(self.last_loss), **stats)
 
     def run_batches(self, batches):
         """Train on an iterable of HOST batches ``(xs, ys)`` (pinned memory recommended) and return the per-step

@@ -149,3 +149,24 @@ def test_spawn_cli_requires_max_epochs_like_reference():
     cmd = [sys.executable, os.path.join(ROOT, "scripts", "train_ddp_spawn.py"), "--world_size", "1", "--port", "29635"]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=120, cwd=ROOT)
     assert out.returncode != 0            # range(None) - the reference has no default either (ddp_gpus.py:90)
+
+
+def test_checkpoint_resume_roundtrip(tmp_path):
+    """--save_every writes rank 0's module state; --resume picks the epoch counter and the weights up again."""
+    snap = tmp_path / "snap.pt"
+    base = [sys.executable, "-m", "torch.distributed.run", "--nproc-per-node=2", "--master-addr", "127.0.0.1"]
+    script = [os.path.join(ROOT, "scripts", "train_ddp_torchrun.py"), "--batch_size", "64", "--save_every", "1",
+              "--snapshot_path", str(snap), "--loss", "mse"]
+    out1 = subprocess.run(base + ["--master-port", "29641"] + script + ["--max_epochs", "1"], capture_output=True,
+                          text=True, timeout=300, cwd=ROOT)
+    assert out1.returncode == 0, out1.stderr[-1500:]
+    first = torch.load(snap)
+    assert first["EPOCHS_RUN"] == 1
+    out2 = subprocess.run(base + ["--master-port", "29643"] + script + ["--max_epochs", "2", "--resume"],
+                          capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert out2.returncode == 0, out2.stderr[-1500:]
+    assert "Resuming training from snapshot at epoch 1" in out2.stdout
+    assert "Epoch: 0 |" not in out2.stdout and "Epoch: 1 |" in out2.stdout       # epoch 0 is not repeated
+    second = torch.load(snap)
+    assert second["EPOCHS_RUN"] == 2
+    assert not torch.equal(first["MODEL_STATE"]["weight"], second["MODEL_STATE"]["weight"])
