@@ -82,6 +82,7 @@ struct alignas(64) WParams {
     int P, Cout, Kw;
     int m_blocks, n_blocks, splits, kb_per_split, num_kb;
     float* dw;
+    int dbg;             // experiment switches (PTD_IGEMM_DBG): 1 = skip B loads, 2 = skip MMA issue
 };
 
 // ------------------------------------------------------------------------------------------
@@ -552,7 +553,11 @@ __device__ __forceinline__ void w_gather_loop(const WParams& p, Barriers<Cfg::ST
     }
 }
 
-template <int NSUB, int B_MODE>
+// CL2: launched as clusters of two CTAs that work on neighbouring Cout blocks of the same (n block, split): the
+// im2col / activation tile (B) is identical for both, so each CTA fetches half of its sub-tiles and TMA-multicasts
+// them into both shared memories - the L2 traffic of B halves (the kernel is L2-bandwidth bound: loads alone take
+// 89 of 97 us on layer3's 3x3, profiles/).  A stage is recycled only after BOTH MMAs released it (multicast commit).
+template <int NSUB, int B_MODE, bool CL2>
 __global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel(const __grid_constant__ WParams p) {
     using Cfg = WCfg<NSUB, B_MODE>;
     constexpr bool B_TMA = B_MODE != AM_GATHER;
@@ -567,9 +572,19 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel
 
     // CTA -> (split, m block, n block)
     int bid = blockIdx.x;
-    const int n_blk = bid % p.n_blocks; bid /= p.n_blocks;
-    const int m_blk = bid % p.m_blocks; bid /= p.m_blocks;
-    const int split = bid;
+    int n_blk, m_blk, split;
+    const uint32_t crank = CL2 ? cluster_ctarank() : 0;
+    if (CL2) {
+        int pq = bid >> 1;
+        n_blk = pq % p.n_blocks; pq /= p.n_blocks;
+        const int mpairs = p.m_blocks >> 1;
+        m_blk = (pq % mpairs) * 2 + (int)crank;
+        split = pq / mpairs;
+    } else {
+        n_blk = bid % p.n_blocks; bid /= p.n_blocks;
+        m_blk = bid % p.m_blocks; bid /= p.m_blocks;
+        split = bid;
+    }
     const int kb_begin = split * p.kb_per_split;
     const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
     const int nkb = kb_end - kb_begin;     // host guarantees >= 1
@@ -579,7 +594,7 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel
         if (B_TMA) tma_prefetch_desc(&p.tmB);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&bars->full[s], B_TMA ? 1 : 1 + NUM_GATHER_THREADS);
-            mbar_init(&bars->empty[s], 1);
+            mbar_init(&bars->empty[s], CL2 ? 2 : 1);
         }
         mbar_init(&bars->tmem_full[0], 1);
         mbar_fence_init();
@@ -587,6 +602,7 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel
     if (warp == MMA_WARP) tmem_alloc<Cfg::TMEM_COLS>(&bars->tmem_base);
     tc_fence_before();
     __syncthreads();
+    if (CL2) cluster_sync_all();          // the peer's barriers exist before anything is multicast at them
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_base;
 
@@ -598,16 +614,24 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel
                 mbar_wait(&bars->empty[stage], phase ^ 1);
                 const uint32_t a_dst = smem_base + stage * Cfg::STAGE_BYTES;
                 const uint32_t b_dst = a_dst + Cfg::A_BYTES;
-                mbar_arrive_expect_tx(&bars->full[stage], Cfg::A_BYTES + (B_TMA ? Cfg::B_BYTES : 0));
+                const bool skip_b = (p.dbg & 1) != 0;
+                mbar_arrive_expect_tx(&bars->full[stage], Cfg::A_BYTES + ((B_TMA && !skip_b) ? Cfg::B_BYTES : 0));
                 tma_load_2d(a_dst, &p.tmA, &bars->full[stage], m_blk * 128, kb * 64);
                 tma_load_2d(a_dst + SUB_TILE_BYTES, &p.tmA, &bars->full[stage], m_blk * 128 + 64, kb * 64);
-                if (B_MODE == AM_TILED) {
+                if (B_MODE == AM_TILED && !skip_b) {
 #pragma unroll
-                    for (int j = 0; j < NSUB; ++j)
-                        tma_load_2d(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage],
-                                    (n_blk * NSUB + j) * 64, kb * 64);
+                    for (int j = 0; j < NSUB; ++j) {
+                        if (CL2) {
+                            if ((j & 1) == (int)crank)
+                                tma_load_2d_mc(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage],
+                                               (n_blk * NSUB + j) * 64, kb * 64, 3);
+                        } else {
+                            tma_load_2d(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage],
+                                        (n_blk * NSUB + j) * 64, kb * 64);
+                        }
+                    }
                 }
-                if (B_MODE == AM_IM2COL) {
+                if (B_MODE == AM_IM2COL && !skip_b) {
                     // 64 output pixels starting at kb*64: one im2col load per (tap, channel block) sub-tile
                     const int hw = p.g.OH * p.g.OW;
                     const int p0 = kb * 64;
@@ -621,7 +645,13 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel
                         const int tap = sj / p.g.cblocks;
                         const int cb = sj - tap * p.g.cblocks;
                         const int r = tap / p.g.S, s_ = tap - r * p.g.S;
-                        tma_load_im2col(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage], cb * 64, iw0, ih0, n0, s_, r);
+                        if (CL2) {
+                            if ((j & 1) == (int)crank)
+                                tma_load_im2col_mc(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage], cb * 64, iw0, ih0,
+                                                   n0, s_, r, 3);
+                        } else {
+                            tma_load_im2col(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage], cb * 64, iw0, ih0, n0, s_, r);
+                        }
                     }
                 }
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -639,11 +669,13 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel
                 const uint32_t b_addr = a_addr + Cfg::A_BYTES;
 #pragma unroll
                 for (int kk = 0; kk < 4; ++kk) {
+                    if (p.dbg & 2) break;
                     const uint64_t adesc = umma_smem_desc(a_addr + kk * 2048, SUB_TILE_BYTES, 1024);
                     const uint64_t bdesc = umma_smem_desc(b_addr + kk * 2048, SUB_TILE_BYTES, 1024);
                     umma_f16(tmem_base, adesc, bdesc, idesc, (i | kk) != 0 ? 1u : 0u);
                 }
-                umma_commit(&bars->empty[stage]);
+                if (CL2) umma_commit_mc(&bars->empty[stage], 3);      // releases the stage in both CTAs of the pair
+                else umma_commit(&bars->empty[stage]);
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
             umma_commit(&bars->tmem_full[0]);
@@ -676,6 +708,7 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel
 
     tc_fence_before();
     __syncthreads();
+    if (CL2) cluster_sync_all();          // neither CTA leaves while the other may still signal or write into it
     if (warp == MMA_WARP) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
@@ -723,10 +756,10 @@ int pick_block_n(int n) {
     return 64;
 }
 
-template <int NSUB, int B_MODE>
-int launch_w(WParams& p, cudaStream_t stream) {
+template <int NSUB, int B_MODE, bool CL2>
+int launch_w_impl(WParams& p, int grid, cudaStream_t stream) {
     using Cfg = WCfg<NSUB, B_MODE>;
-    auto kern = igemm_w_kernel<NSUB, B_MODE>;
+    auto kern = igemm_w_kernel<NSUB, B_MODE, CL2>;
     static bool configured[64] = {false};
     int dev = 0;
     PTD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -734,6 +767,31 @@ int launch_w(WParams& p, cudaStream_t stream) {
         PTD_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
         configured[dev & 63] = true;
     }
+    if (!CL2) {
+        kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>(p);
+    } else {
+        cudaLaunchConfig_t cfg;
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(Cfg::THREADS);
+        cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        PTD_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p));
+    }
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+template <int NSUB, int B_MODE>
+int launch_w(WParams& p, cudaStream_t stream) {
+    { const char* e = getenv("PTD_IGEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
     p.m_blocks = ceil_div_i(p.Cout, 128);
     p.n_blocks = p.Kw / (64 * NSUB);
     p.num_kb = ceil_div_i(p.P, 64);
@@ -748,9 +806,14 @@ int launch_w(WParams& p, cudaStream_t stream) {
     if (splits < 1) splits = 1;
     p.kb_per_split = ceil_div_i(p.num_kb, splits);
     p.splits = ceil_div_i(p.num_kb, p.kb_per_split);            // no empty split
-    kern<<<tiles * p.splits, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>(p);
-    PTD_CUDA_CHECK(cudaGetLastError());
-    return PTD_OK;
+    const int grid = tiles * p.splits;
+    static int use_cluster = -1;
+    // measured: correct, but no faster than unicast on B200 (L2 already merges the pair's requests; the kernel is
+    // bound by per-SM ingress, which multicast does not reduce) - kept as an option, off by default
+    if (use_cluster < 0) { const char* e = getenv("PTD_WGRAD_CLUSTER"); use_cluster = e ? atoi(e) : 0; }
+    if (B_MODE != AM_GATHER && (NSUB % 2) == 0 && (p.m_blocks % 2) == 0 && use_cluster)
+        return launch_w_impl<NSUB, B_MODE, (B_MODE != AM_GATHER && NSUB % 2 == 0)>(p, grid, stream);
+    return launch_w_impl<NSUB, B_MODE, false>(p, grid, stream);
 }
 
 template <int B_MODE>
@@ -766,6 +829,8 @@ int dispatch_w(WParams& p, int nsub, cudaStream_t stream) {
 }
 
 int pick_nsub(int ksub) {   // ksub = Kw / 64
+    { static int f = -1; if (f < 0) { const char* e = getenv("PTD_WGRAD_NSUB"); f = e ? atoi(e) : 0; }
+      if (f > 0 && ksub % f == 0) return f; }
     if (ksub % 4 == 0) return 4;
     if (ksub % 3 == 0) return 3;
     if (ksub % 2 == 0) return 2;
