@@ -502,15 +502,18 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
 // ------------------------------------------------------------------------------------------
 // igemm_w
 // ------------------------------------------------------------------------------------------
-template <int NSUB, int B_MODE>
+// M2: the CTA owns TWO 128-row Cout blocks (two TMEM accumulators) that share every im2col / activation tile it
+// loads - a third fewer bytes into the SM per MMA (the kernel is bound by loads: ncu + the skip-MMA experiment).
+template <int NSUB, int B_MODE, bool M2 = false>
 struct WCfg {
     static constexpr int BLOCK_N = 64 * NSUB;
-    static constexpr int A_BYTES = 2 * SUB_TILE_BYTES;                 // [64 pixels][128 cout]
+    static constexpr int MSUB = M2 ? 4 : 2;                           // 64-wide Cout sub-tiles of A
+    static constexpr int A_BYTES = MSUB * SUB_TILE_BYTES;             // [64 pixels][128 or 256 cout]
     static constexpr int B_BYTES = NSUB * SUB_TILE_BYTES;              // [64 pixels][64*NSUB]
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES = NSUB >= 3 ? 4 : 6;
+    static constexpr int STAGES = M2 ? 3 : (NSUB >= 3 ? 4 : 6);
     static constexpr int THREADS = B_MODE != AM_GATHER ? (MMA_WARP + 1) * 32 : (GATHER_WARP0 + 4) * 32;
-    static constexpr int TMEM_COLS = NSUB == 1 ? 64 : (NSUB == 2 ? 128 : 256);
+    static constexpr int TMEM_COLS = M2 ? 512 : (NSUB == 1 ? 64 : (NSUB == 2 ? 128 : 256));
     static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + sizeof(Barriers<STAGES>);
 };
 
@@ -557,9 +560,10 @@ __device__ __forceinline__ void w_gather_loop(const WParams& p, Barriers<Cfg::ST
 // im2col / activation tile (B) is identical for both, so each CTA fetches half of its sub-tiles and TMA-multicasts
 // them into both shared memories - the L2 traffic of B halves (the kernel is L2-bandwidth bound: loads alone take
 // 89 of 97 us on layer3's 3x3, profiles/).  A stage is recycled only after BOTH MMAs released it (multicast commit).
-template <int NSUB, int B_MODE, bool CL2>
-__global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel(const __grid_constant__ WParams p) {
-    using Cfg = WCfg<NSUB, B_MODE>;
+template <int NSUB, int B_MODE, bool CL2, bool M2>
+__global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_kernel(const __grid_constant__ WParams p) {
+    using Cfg = WCfg<NSUB, B_MODE, M2>;
+    constexpr int MROWS = M2 ? 256 : 128;
     constexpr bool B_TMA = B_MODE != AM_GATHER;
     constexpr int STAGES = Cfg::STAGES;
     constexpr int BLOCK_N = Cfg::BLOCK_N;
@@ -616,8 +620,9 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel
                 const uint32_t b_dst = a_dst + Cfg::A_BYTES;
                 const bool skip_b = (p.dbg & 1) != 0;
                 mbar_arrive_expect_tx(&bars->full[stage], Cfg::A_BYTES + ((B_TMA && !skip_b) ? Cfg::B_BYTES : 0));
-                tma_load_2d(a_dst, &p.tmA, &bars->full[stage], m_blk * 128, kb * 64);
-                tma_load_2d(a_dst + SUB_TILE_BYTES, &p.tmA, &bars->full[stage], m_blk * 128 + 64, kb * 64);
+#pragma unroll
+                for (int j = 0; j < Cfg::MSUB; ++j)
+                    tma_load_2d(a_dst + j * SUB_TILE_BYTES, &p.tmA, &bars->full[stage], m_blk * MROWS + j * 64, kb * 64);
                 if (B_MODE == AM_TILED && !skip_b) {
 #pragma unroll
                     for (int j = 0; j < NSUB; ++j) {
@@ -668,11 +673,14 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel
                 const uint32_t a_addr = smem_base + stage * Cfg::STAGE_BYTES;
                 const uint32_t b_addr = a_addr + Cfg::A_BYTES;
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk) {
-                    if (p.dbg & 2) break;
-                    const uint64_t adesc = umma_smem_desc(a_addr + kk * 2048, SUB_TILE_BYTES, 1024);
-                    const uint64_t bdesc = umma_smem_desc(b_addr + kk * 2048, SUB_TILE_BYTES, 1024);
-                    umma_f16(tmem_base, adesc, bdesc, idesc, (i | kk) != 0 ? 1u : 0u);
+                for (int h = 0; h < (M2 ? 2 : 1); ++h) {
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        if (p.dbg & 2) break;
+                        const uint64_t adesc = umma_smem_desc(a_addr + h * 2 * SUB_TILE_BYTES + kk * 2048, SUB_TILE_BYTES, 1024);
+                        const uint64_t bdesc = umma_smem_desc(b_addr + kk * 2048, SUB_TILE_BYTES, 1024);
+                        umma_f16(tmem_base + h * BLOCK_N, adesc, bdesc, idesc, (i | kk) != 0 ? 1u : 0u);
+                    }
                 }
                 if (CL2) umma_commit_mc(&bars->empty[stage], 3);      // releases the stage in both CTAs of the pair
                 else umma_commit(&bars->empty[stage]);
@@ -683,21 +691,23 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE>::THREADS, 1) igemm_w_kernel
     } else if (warp < NUM_EPI_WARPS) {
         const int q = warp & 3;
         const int half = warp >> 2;
-        const int cout = m_blk * 128 + q * 32 + lane;
         mbar_wait(&bars->tmem_full[0], 0);
         tc_fence_after();
         // 32-column chunks split between the two warps sharing a lane quarter
         constexpr int NCHUNK = BLOCK_N / 32;
-        for (int c = half; c < NCHUNK; c += 2) {
-            uint32_t raw[32];
-            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, raw);
-            tmem_ld_wait();
-            if (cout < p.Cout) {
-                float* dst = p.dw + (size_t)cout * p.Kw + (size_t)n_blk * BLOCK_N + c * 32;
+        for (int h = 0; h < (M2 ? 2 : 1); ++h) {
+            const int cout = m_blk * MROWS + h * 128 + q * 32 + lane;
+            for (int c = half; c < NCHUNK; c += 2) {
+                uint32_t raw[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + h * BLOCK_N + c * 32, raw);
+                tmem_ld_wait();
+                if (cout < p.Cout) {
+                    float* dst = p.dw + (size_t)cout * p.Kw + (size_t)n_blk * BLOCK_N + c * 32;
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    red_add_v4(dst + j * 4, __uint_as_float(raw[j * 4]), __uint_as_float(raw[j * 4 + 1]),
-                               __uint_as_float(raw[j * 4 + 2]), __uint_as_float(raw[j * 4 + 3]));
+                    for (int j = 0; j < 8; ++j)
+                        red_add_v4(dst + j * 4, __uint_as_float(raw[j * 4]), __uint_as_float(raw[j * 4 + 1]),
+                                   __uint_as_float(raw[j * 4 + 2]), __uint_as_float(raw[j * 4 + 3]));
+                }
             }
         }
         tc_fence_before();
@@ -756,10 +766,10 @@ int pick_block_n(int n) {
     return 64;
 }
 
-template <int NSUB, int B_MODE, bool CL2>
+template <int NSUB, int B_MODE, bool CL2, bool M2>
 int launch_w_impl(WParams& p, int grid, cudaStream_t stream) {
-    using Cfg = WCfg<NSUB, B_MODE>;
-    auto kern = igemm_w_kernel<NSUB, B_MODE, CL2>;
+    using Cfg = WCfg<NSUB, B_MODE, M2>;
+    auto kern = igemm_w_kernel<NSUB, B_MODE, CL2, M2>;
     static bool configured[64] = {false};
     int dev = 0;
     PTD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -792,7 +802,11 @@ int launch_w_impl(WParams& p, int grid, cudaStream_t stream) {
 template <int NSUB, int B_MODE>
 int launch_w(WParams& p, cudaStream_t stream) {
     { const char* e = getenv("PTD_IGEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
-    p.m_blocks = ceil_div_i(p.Cout, 128);
+    static int dual_m = -1;
+    if (dual_m < 0) { const char* e = getenv("PTD_WGRAD_M2"); dual_m = e ? atoi(e) : 1; }
+    constexpr bool M2_OK = B_MODE != AM_GATHER && NSUB >= 3;          // 2 x (64*NSUB) TMEM columns, 3 stages of <= 64 KiB
+    const bool m2 = M2_OK && dual_m && p.Cout >= 256;
+    p.m_blocks = ceil_div_i(p.Cout, m2 ? 256 : 128);
     p.n_blocks = p.Kw / (64 * NSUB);
     p.num_kb = ceil_div_i(p.P, 64);
     const int tiles = p.m_blocks * p.n_blocks;
@@ -811,9 +825,10 @@ int launch_w(WParams& p, cudaStream_t stream) {
     // measured: correct, but no faster than unicast on B200 (L2 already merges the pair's requests; the kernel is
     // bound by per-SM ingress, which multicast does not reduce) - kept as an option, off by default
     if (use_cluster < 0) { const char* e = getenv("PTD_WGRAD_CLUSTER"); use_cluster = e ? atoi(e) : 0; }
+    if (m2) return launch_w_impl<NSUB, B_MODE, false, M2_OK>(p, grid, stream);
     if (B_MODE != AM_GATHER && (NSUB % 2) == 0 && (p.m_blocks % 2) == 0 && use_cluster)
-        return launch_w_impl<NSUB, B_MODE, (B_MODE != AM_GATHER && NSUB % 2 == 0)>(p, grid, stream);
-    return launch_w_impl<NSUB, B_MODE, false>(p, grid, stream);
+        return launch_w_impl<NSUB, B_MODE, (B_MODE != AM_GATHER && NSUB % 2 == 0), false>(p, grid, stream);
+    return launch_w_impl<NSUB, B_MODE, false, false>(p, grid, stream);
 }
 
 template <int B_MODE>
