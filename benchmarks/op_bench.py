@@ -32,6 +32,11 @@ SHAPES = [
 ]
 
 
+def x_like(t):
+    """A distinct tensor with the same values (so that dz and y of a BN backward are not the same memory)."""
+    return t.clone(memory_format=torch.preserve_format)
+
+
 def timeit(fn, flush, iters):
     fn()
     torch.cuda.synchronize()
@@ -99,7 +104,9 @@ def main():
             rm, rv = torch.zeros(c, device=dev), torch.ones(c, device=dev)
             stats = K.bn_stats_raw(dy)
             z, saved = K.bn_apply_raw(dy, stats, gamma, beta, rm, rv, 1e-5, 0.1, True)
-            K.bn_backward_raw(dy, z, dy, saved, gamma, True, False)
+            K.bn_backward_raw(dy, z, x_like(dy), saved, gamma, True, False)
+            z, saved, mask = K.bn_apply_raw(dy, stats, gamma, beta, rm, rv, 1e-5, 0.1, True, want_mask=True)
+            K.bn_backward_raw(dy, None, x_like(dy), saved, gamma, True, False, mask=mask)
             torch.cuda.synchronize()
         if not args.once and not args.only:
             c = cout
@@ -107,14 +114,21 @@ def main():
             gamma, beta = torch.ones(c, device=dev), torch.zeros(c, device=dev)
             rm, rv = torch.zeros(c, device=dev), torch.ones(c, device=dev)
             stats = K.bn_stats_raw(y)
-            z, saved = K.bn_apply_raw(y, stats, gamma, beta, rm, rv, 1e-5, 0.1, True)
+            z, saved, mask = K.bn_apply_raw(y, stats, gamma, beta, rm, rv, 1e-5, 0.1, True, want_mask=True)
+            y2 = x_like(y)
+            # minimum traffic in units of one bf16 pass over the tensor: apply 2 (+1/16 mask); backward reads
+            # dz, y, z twice and writes dy = 7, or 5 + 1/8 when the bit mask stands in for z
             for opn, fn, nb in (("bn_apply", lambda: K.bn_apply_raw(y, stats, gamma, beta, rm, rv, 1e-5, 0.1, True), 2),
-                                ("bn_bwd", lambda: K.bn_backward_raw(y, z, y, saved, gamma, True, False), 7)):
+                                ("bn_apply_m", lambda: K.bn_apply_raw(y, stats, gamma, beta, rm, rv, 1e-5, 0.1, True,
+                                                                     want_mask=True), 2.0625),
+                                ("bn_bwd", lambda: K.bn_backward_raw(y2, z, y, saved, gamma, True, False), 7),
+                                ("bn_bwd_m", lambda: K.bn_backward_raw(y2, None, y, saved, gamma, True, False, mask=mask),
+                                 5.125)):
                 us = timeit(fn, flush, args.iters)
                 gbs = nb * y.numel() * 2 / us / 1e3
                 rows.append({"layer": name, "op": opn, "us": round(us, 1), "gbs": round(gbs, 0),
                              "frac_hbm_of_measured": round(gbs / peaks["hbm_gbs"], 3)})
-                print(f"{name:28s} {opn:8s} {us:9.1f} us  {gbs:6.0f} GB/s ({gbs / peaks['hbm_gbs']:.2f} of measured HBM)", flush=True)
+                print(f"{name:28s} {opn:10s} {us:9.1f} us  {gbs:6.0f} GB/s ({gbs / peaks['hbm_gbs']:.2f} of measured HBM)", flush=True)
     if args.out:
         json.dump(rows, open(args.out, "w"), indent=1)
 

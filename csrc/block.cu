@@ -86,8 +86,9 @@ extern "C" int ptd_bottleneck_fwd(const PtdBottleneckFwd* d, void* stream) {
         int relu = 1;
         if (i == 2) residual = d->has_ds ? d->z[3] : d->x;
         if (i == 3) relu = 0;
-        rc = ptd_bn_apply(d->y[i], residual, d->z[i], st, st + g[i].cout, d->gamma[i], d->beta[i], d->running_mean[i],
-                          d->running_var[i], sv, sv + g[i].cout, g[i].m_out, g[i].cout, d->eps, d->momentum, relu, stream);
+        rc = ptd_bn_apply_mask(d->y[i], residual, d->z[i], d->mask[i], st, st + g[i].cout, d->gamma[i], d->beta[i],
+                               d->running_mean[i], d->running_var[i], sv, sv + g[i].cout, g[i].m_out, g[i].cout, d->eps,
+                               d->momentum, relu, stream);
         if (rc) return rc;
     }
     return PTD_OK;
@@ -108,11 +109,14 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
     do {                                                                                                               \
         float* sm = d->sums + off[i];                                                                                  \
         const float* sv = d->saved + off[i];                                                                           \
-        rc = ptd_bn_bwd_reduce(dz_, d->z[i], d->y[i], sv, sv + g[i].cout, sm, sm + g[i].cout, g[i].m_out, g[i].cout,   \
-                               relu_, stream);                                                                         \
+        const bool bits = relu_ && d->mask[i] != nullptr;    /* 1 bit per element instead of re-reading z */           \
+        const void* zm = bits ? d->mask[i] : d->z[i];                                                                  \
+        const int mode = bits ? 2 : relu_;                                                                             \
+        rc = ptd_bn_bwd_reduce(dz_, zm, d->y[i], sv, sv + g[i].cout, sm, sm + g[i].cout, g[i].m_out, g[i].cout,        \
+                               mode, stream);                                                                          \
         if (rc) return rc;                                                                                             \
-        rc = ptd_bn_bwd_apply(dz_, d->z[i], d->y[i], sv, sv + g[i].cout, d->gamma[i], sm, sm + g[i].cout, d->dy[i],   \
-                              gout_, g[i].m_out, g[i].cout, relu_, stream);                                            \
+        rc = ptd_bn_bwd_apply(dz_, zm, d->y[i], sv, sv + g[i].cout, d->gamma[i], sm, sm + g[i].cout, d->dy[i],        \
+                              gout_, g[i].m_out, g[i].cout, mode, stream);                                             \
         if (rc) return rc;                                                                                             \
     } while (0)
 #define DGRAD(i, dx_, addend_)                                                                                         \

@@ -90,12 +90,12 @@ __global__ void __launch_bounds__(BN_THREADS) bn_stats_kernel(const bf16* __rest
 
 // z = act( (y - mean) * invstd * gamma + beta  [+ residual] ), plus running-stat update by block 0.
 template <bool RELU, bool RES>
-__global__ void __launch_bounds__(BN_THREADS)
+__global__ void __launch_bounds__(BN_THREADS, 3)
 bn_apply_kernel(const bf16* __restrict__ y, const bf16* __restrict__ res, bf16* __restrict__ z,
                 const float* __restrict__ sum, const float* __restrict__ sq, const float* __restrict__ gamma,
                 const float* __restrict__ beta, float* __restrict__ running_mean, float* __restrict__ running_var,
-                float* __restrict__ save_mean, float* __restrict__ save_invstd, long long M, int C, float eps,
-                float momentum) {
+                float* __restrict__ save_mean, float* __restrict__ save_invstd, unsigned char* __restrict__ mask,
+                long long M, int C, float eps, float momentum) {
     const int cg = C >> 3;
     const int rows_per_iter = BN_THREADS / cg;
     const int g = threadIdx.x % cg;
@@ -121,20 +121,42 @@ bn_apply_kernel(const bf16* __restrict__ y, const bf16* __restrict__ res, bf16* 
     }
     long long row = (long long)blockIdx.x * rows_per_iter + threadIdx.x / cg;
     const long long row_step = (long long)gridDim.x * rows_per_iter;
-    for (; row < M; row += row_step) {
-        const size_t off = (size_t)row * C + g * 8;
-        float f[8];
-        unpack8(*reinterpret_cast<const uint4*>(y + off), f);
-        float r[8];
-        if (RES) unpack8(*reinterpret_cast<const uint4*>(res + off), r);
+    // The loop is latency-bound (load -> math -> store per warp), so every thread keeps U independent rows in flight.
+    constexpr int U = RES ? 2 : 4;
+    for (; row < M; row += U * row_step) {
+        uint4 ry[U], rr[RES ? U : 1];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            float v = fmaf(f[i], scale[i], shift[i]);
-            if (RES) v += r[i];
-            if (RELU) v = fmaxf(v, 0.f);
-            f[i] = v;
+        for (int u = 0; u < U; ++u) {
+            const long long ru = row + u * row_step;
+            if (ru < M) {
+                const size_t off = (size_t)ru * C + g * 8;
+                ry[u] = *reinterpret_cast<const uint4*>(y + off);
+                if (RES) rr[RES ? u : 0] = *reinterpret_cast<const uint4*>(res + off);
+            }
         }
-        *reinterpret_cast<uint4*>(z + off) = pack8(f);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long ru = row + u * row_step;
+            if (ru >= M) break;
+            const size_t off = (size_t)ru * C + g * 8;
+            float f[8], r[8];
+            unpack8(ry[u], f);
+            if (RES) unpack8(rr[RES ? u : 0], r);
+            unsigned bits = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float v = fmaf(f[i], scale[i], shift[i]);
+                if (RES) v += r[i];
+                if (RELU) {
+                    if (v > 0.f) bits |= 1u << i;
+                    v = fmaxf(v, 0.f);
+                }
+                f[i] = v;
+            }
+            *reinterpret_cast<uint4*>(z + off) = pack8(f);
+            // one bit per element that survived the ReLU: the backward reads this byte instead of 16 bytes of z
+            if (RELU && mask != nullptr) mask[(size_t)ru * cg + g] = (unsigned char)bits;
+        }
     }
 }
 
@@ -168,34 +190,42 @@ affine_act_kernel(const bf16* __restrict__ y, const bf16* __restrict__ res, bf16
 }
 
 // Backward pass 1: sum_g[c] += g, sum_gx[c] += g * xhat with g = dz * (z > 0 if RELU).
-template <bool RELU>
-__global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_reduce_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ z, const bf16* __restrict__ y,
+// RELU: 0 = no activation, 1 = mask recomputed from z (> 0), 2 = mask read from the packed bit tensor that
+// bn_apply wrote (z then points at [M][C/8] bytes).
+template <int RELU>
+__global__ void __launch_bounds__(BN_THREADS, 2)
+bn_bwd_reduce_kernel(const bf16* __restrict__ dz, const void* __restrict__ zm, const bf16* __restrict__ y,
                      const float* __restrict__ mean, const float* __restrict__ invstd, float* __restrict__ sum_g,
                      float* __restrict__ sum_gx, long long M, int C) {
     const int cg = C >> 3;
     const int rows_per_iter = BN_THREADS / cg;
     const int g = threadIdx.x % cg;
-    float mu[8], is[8], s[8], q[8];
+    float mu[8], s[8], q[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) { mu[i] = mean[g * 8 + i]; is[i] = invstd[g * 8 + i]; s[i] = q[i] = 0.f; }
+    for (int i = 0; i < 8; ++i) { mu[i] = mean[g * 8 + i]; s[i] = q[i] = 0.f; }
     long long row = (long long)blockIdx.x * rows_per_iter + threadIdx.x / cg;
     const long long row_step = (long long)gridDim.x * rows_per_iter;
-    constexpr int U = 4;                      // rows in flight per thread (independent 16-byte loads)
+    const bf16* z = reinterpret_cast<const bf16*>(zm);
+    const unsigned char* mask = reinterpret_cast<const unsigned char*>(zm);
+    // rows in flight per thread (independent 16-byte loads); two resident blocks per SM keep ~128 KB on the wire
+    constexpr int U = RELU == 1 ? 4 : (RELU == 2 ? 6 : 8);
     for (; row < M; row += U * row_step) {
-        uint4 rd[U], rx[U], ra[U];
+        uint4 rd[U], rx[U], ra[RELU == 1 ? U : 1];
+        unsigned rb[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const long long ru = row + u * row_step;
+            rb[u] = 0;
             if (ru < M) {
                 const size_t off = (size_t)ru * C + g * 8;
                 rd[u] = *reinterpret_cast<const uint4*>(dz + off);
                 rx[u] = *reinterpret_cast<const uint4*>(y + off);
-                if (RELU) ra[u] = *reinterpret_cast<const uint4*>(z + off);
+                if (RELU == 1) ra[RELU == 1 ? u : 0] = *reinterpret_cast<const uint4*>(z + off);
+                if (RELU == 2) rb[u] = mask[(size_t)ru * cg + g];
             } else {
                 rd[u] = make_uint4(0, 0, 0, 0);
                 rx[u] = make_uint4(0, 0, 0, 0);
-                ra[u] = make_uint4(0, 0, 0, 0);
+                if (RELU == 1) ra[RELU == 1 ? u : 0] = make_uint4(0, 0, 0, 0);
             }
         }
 #pragma unroll
@@ -203,63 +233,94 @@ bn_bwd_reduce_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ z, co
             float d[8], a[8], x[8];
             unpack8(rd[u], d);
             unpack8(rx[u], x);
-            if (RELU) unpack8(ra[u], a);
+            if (RELU == 1) unpack8(ra[RELU == 1 ? u : 0], a);
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-                const float gi = (RELU && !(a[i] > 0.f)) ? 0.f : d[i];
+                const bool dead = RELU == 1 ? !(a[i] > 0.f) : (RELU == 2 ? !((rb[u] >> i) & 1u) : false);
+                const float gi = dead ? 0.f : d[i];
                 s[i] += gi;
-                q[i] += gi * (x[i] - mu[i]) * is[i];
+                q[i] = fmaf(gi, x[i] - mu[i], q[i]);
             }
         }
     }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) q[i] *= invstd[g * 8 + i];       // xhat = (x - mean) * invstd, factored out of the loop
     extern __shared__ float sh_red[];
     block_channel_reduce(s, q, cg, g, sum_g, sum_gx, sh_red);
 }
 
 // Backward pass 2: dy = gamma*invstd * (g - sum_g/M - xhat*sum_gx/M); optionally g_out = g.
-template <bool RELU, bool GOUT>
-__global__ void __launch_bounds__(BN_THREADS)
-bn_bwd_apply_kernel(const bf16* __restrict__ dz, const bf16* __restrict__ z, const bf16* __restrict__ y,
+template <int RELU, bool GOUT>
+__global__ void __launch_bounds__(BN_THREADS, 3)
+bn_bwd_apply_kernel(const bf16* __restrict__ dz, const void* __restrict__ zm, const bf16* __restrict__ y,
                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
                     const float* __restrict__ sum_g, const float* __restrict__ sum_gx, bf16* __restrict__ dy,
                     bf16* __restrict__ g_out, long long M, int C) {
     const int cg = C >> 3;
     const int rows_per_iter = BN_THREADS / cg;
     const int g = threadIdx.x % cg;
-    float mu[8], is[8], k[8], mg[8], mgx[8];
+    // dy = k * (g - mg - xhat * mgx) with xhat = (x - mu) * is, folded to dy = k * g + (a0 + a1 * x)
+    float k[8], a0[8], a1[8];
     const float inv_m = 1.f / (float)M;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         const int c = g * 8 + i;
-        mu[i] = mean[c]; is[i] = invstd[c]; k[i] = gamma[c] * is[i];
-        mg[i] = sum_g[c] * inv_m; mgx[i] = sum_gx[c] * inv_m;
+        const float is = invstd[c], mu = mean[c];
+        k[i] = gamma[c] * is;
+        const float t = k[i] * sum_gx[c] * inv_m * is;
+        a1[i] = -t;
+        a0[i] = fmaf(t, mu, -k[i] * sum_g[c] * inv_m);
     }
+    const bf16* z = reinterpret_cast<const bf16*>(zm);
+    const unsigned char* mask = reinterpret_cast<const unsigned char*>(zm);
     long long row = (long long)blockIdx.x * rows_per_iter + threadIdx.x / cg;
     const long long row_step = (long long)gridDim.x * rows_per_iter;
-    for (; row < M; row += row_step) {
-        const size_t off = (size_t)row * C + g * 8;
-        float d[8], a[8], x[8], o[8];
-        unpack8(*reinterpret_cast<const uint4*>(dz + off), d);
-        unpack8(*reinterpret_cast<const uint4*>(y + off), x);
-        if (RELU) unpack8(*reinterpret_cast<const uint4*>(z + off), a);
+    constexpr int U = RELU == 1 ? 2 : 3;      // rows in flight per thread
+    for (; row < M; row += U * row_step) {
+        uint4 rd[U], rx[U], ra[RELU == 1 ? U : 1];
+        unsigned rb[U];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const float gi = (RELU && !(a[i] > 0.f)) ? 0.f : d[i];
-            d[i] = gi;
-            const float xhat = (x[i] - mu[i]) * is[i];
-            o[i] = k[i] * (gi - mg[i] - xhat * mgx[i]);
+        for (int u = 0; u < U; ++u) {
+            const long long ru = row + u * row_step;
+            rb[u] = 0;
+            if (ru < M) {
+                const size_t off = (size_t)ru * C + g * 8;
+                rd[u] = *reinterpret_cast<const uint4*>(dz + off);
+                rx[u] = *reinterpret_cast<const uint4*>(y + off);
+                if (RELU == 1) ra[RELU == 1 ? u : 0] = *reinterpret_cast<const uint4*>(z + off);
+                if (RELU == 2) rb[u] = mask[(size_t)ru * cg + g];
+            }
         }
-        *reinterpret_cast<uint4*>(dy + off) = pack8(o);
-        if (GOUT) *reinterpret_cast<uint4*>(g_out + off) = pack8(d);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long ru = row + u * row_step;
+            if (ru >= M) break;
+            const size_t off = (size_t)ru * C + g * 8;
+            float d[8], a[8], x[8], o[8];
+            unpack8(rd[u], d);
+            unpack8(rx[u], x);
+            if (RELU == 1) unpack8(ra[RELU == 1 ? u : 0], a);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const bool dead = RELU == 1 ? !(a[i] > 0.f) : (RELU == 2 ? !((rb[u] >> i) & 1u) : false);
+                const float gi = dead ? 0.f : d[i];
+                d[i] = gi;
+                o[i] = fmaf(k[i], gi, fmaf(a1[i], x[i], a0[i]));
+            }
+            *reinterpret_cast<uint4*>(dy + off) = pack8(o);
+            if (GOUT) *reinterpret_cast<uint4*>(g_out + off) = pack8(d);
+        }
     }
 }
 
-int bn_grid(long long M, int C) {
+// `per_sm` = blocks of the kernel that are resident per SM (its launch bound): large tensors get exactly one wave
+// of grid-striding blocks.
+int bn_grid(long long M, int C, int per_sm = 8) {
     const int rows_per_iter = BN_THREADS / (C >> 3);
     // >= 8 row groups per block: small tensors get few blocks, so the per-block tail (shared-memory
     // reduction + one atomic per channel) and the launch itself stay cheap
     long long blocks = ((M + rows_per_iter - 1) / rows_per_iter + 7) / 8;
-    const long long cap = (long long)ptd_num_sms() * 8;
+    const long long cap = (long long)ptd_num_sms() * per_sm;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     return (int)blocks;
@@ -280,13 +341,24 @@ extern "C" int ptd_bn_apply(const void* y, const void* residual, void* z, const 
                             const float* gamma, const float* beta, float* running_mean, float* running_var,
                             float* save_mean, float* save_invstd, long long M, int C, float eps, float momentum,
                             int relu, void* stream) {
+    return ptd_bn_apply_mask(y, residual, z, nullptr, sum, sq, gamma, beta, running_mean, running_var, save_mean,
+                             save_invstd, M, C, eps, momentum, relu, stream);
+}
+
+// Same, and when `relu` and `mask` are set also writes one bit per element ([M][C/8] bytes, bit i of byte
+// (row, g) = element (row, 8g+i) survived the ReLU).  ptd_bn_bwd_reduce / ptd_bn_bwd_apply take that tensor in
+// place of z with relu = 2, which cuts a sixth of the bytes the BatchNorm backward has to read.
+extern "C" int ptd_bn_apply_mask(const void* y, const void* residual, void* z, void* mask, const float* sum,
+                                 const float* sq, const float* gamma, const float* beta, float* running_mean,
+                                 float* running_var, float* save_mean, float* save_invstd, long long M, int C, float eps,
+                                 float momentum, int relu, void* stream) {
     PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
-    const int grid = bn_grid(M, C);
+    const int grid = bn_grid(M, C, 3);
     cudaStream_t st = (cudaStream_t)stream;
 #define PTD_BN_APPLY(RELU, RES)                                                                                     \
     bn_apply_kernel<RELU, RES><<<grid, BN_THREADS, 0, st>>>((const bf16*)y, (const bf16*)residual, (bf16*)z, sum, sq, \
                                                            gamma, beta, running_mean, running_var, save_mean,      \
-                                                           save_invstd, M, C, eps, momentum)
+                                                           save_invstd, (unsigned char*)mask, M, C, eps, momentum)
     if (relu && residual) PTD_BN_APPLY(true, true);
     else if (relu) PTD_BN_APPLY(true, false);
     else if (residual) PTD_BN_APPLY(false, true);
@@ -315,14 +387,15 @@ extern "C" int ptd_affine_act(const void* y, const void* residual, void* z, cons
 extern "C" int ptd_bn_bwd_reduce(const void* dz, const void* z, const void* y, const float* mean, const float* invstd,
                                  float* sum_g, float* sum_gx, long long M, int C, int relu, void* stream) {
     PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
-    const int grid = min(bn_grid(M, C), ptd_num_sms() * 4);
+    const int grid = min(bn_grid(M, C), ptd_num_sms() * 2);      // two resident blocks per SM (launch bounds)
     cudaStream_t st = (cudaStream_t)stream;
-    if (relu)
-        bn_bwd_reduce_kernel<true><<<grid, BN_THREADS, 2 * C * sizeof(float), st>>>((const bf16*)dz, (const bf16*)z, (const bf16*)y, mean,
-                                                                invstd, sum_g, sum_gx, M, C);
+    const size_t sh = 2 * C * sizeof(float);
+    if (relu == 2)
+        bn_bwd_reduce_kernel<2><<<grid, BN_THREADS, sh, st>>>((const bf16*)dz, z, (const bf16*)y, mean, invstd, sum_g, sum_gx, M, C);
+    else if (relu)
+        bn_bwd_reduce_kernel<1><<<grid, BN_THREADS, sh, st>>>((const bf16*)dz, z, (const bf16*)y, mean, invstd, sum_g, sum_gx, M, C);
     else
-        bn_bwd_reduce_kernel<false><<<grid, BN_THREADS, 2 * C * sizeof(float), st>>>((const bf16*)dz, (const bf16*)z, (const bf16*)y, mean,
-                                                                 invstd, sum_g, sum_gx, M, C);
+        bn_bwd_reduce_kernel<0><<<grid, BN_THREADS, sh, st>>>((const bf16*)dz, z, (const bf16*)y, mean, invstd, sum_g, sum_gx, M, C);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }
@@ -331,15 +404,17 @@ extern "C" int ptd_bn_bwd_apply(const void* dz, const void* z, const void* y, co
                                 const float* gamma, const float* sum_g, const float* sum_gx, void* dy, void* g_out,
                                 long long M, int C, int relu, void* stream) {
     PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
-    const int grid = bn_grid(M, C);
+    const int grid = bn_grid(M, C, 3);
     cudaStream_t st = (cudaStream_t)stream;
 #define PTD_BWD(RELU, GOUT)                                                                                         \
-    bn_bwd_apply_kernel<RELU, GOUT><<<grid, BN_THREADS, 0, st>>>((const bf16*)dz, (const bf16*)z, (const bf16*)y, mean, \
+    bn_bwd_apply_kernel<RELU, GOUT><<<grid, BN_THREADS, 0, st>>>((const bf16*)dz, z, (const bf16*)y, mean,             \
                                                                 invstd, gamma, sum_g, sum_gx, (bf16*)dy, (bf16*)g_out, M, C)
-    if (relu && g_out) PTD_BWD(true, true);
-    else if (relu) PTD_BWD(true, false);
-    else if (g_out) PTD_BWD(false, true);
-    else PTD_BWD(false, false);
+    if (relu == 2 && g_out) PTD_BWD(2, true);
+    else if (relu == 2) PTD_BWD(2, false);
+    else if (relu && g_out) PTD_BWD(1, true);
+    else if (relu) PTD_BWD(1, false);
+    else if (g_out) PTD_BWD(0, true);
+    else PTD_BWD(0, false);
 #undef PTD_BWD
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
@@ -412,22 +487,22 @@ extern "C" int ptd_bn_backward_static(const void* dz, const void* z, const void*
     float* sum_g = sums;          // -> dbeta
     float* sum_gx = sums + C;     // -> dgamma
     PTD_CUDA_CHECK(cudaMemsetAsync(sums, 0, 2 * (size_t)C * sizeof(float), st));     // leftovers of the previous call
-    const int rgrid = min(bn_grid(M, C), ptd_num_sms() * 4);
+    const int rgrid = min(bn_grid(M, C), ptd_num_sms() * 2);
     if (relu)
-        bn_bwd_reduce_kernel<true><<<rgrid, BN_THREADS, 2 * C * sizeof(float), st>>>(
+        bn_bwd_reduce_kernel<1><<<rgrid, BN_THREADS, 2 * C * sizeof(float), st>>>(
             (const bf16*)dz, (const bf16*)z, (const bf16*)y, mean, invstd, sum_g, sum_gx, M, C);
     else
-        bn_bwd_reduce_kernel<false><<<rgrid, BN_THREADS, 2 * C * sizeof(float), st>>>(
+        bn_bwd_reduce_kernel<0><<<rgrid, BN_THREADS, 2 * C * sizeof(float), st>>>(
             (const bf16*)dz, (const bf16*)z, (const bf16*)y, mean, invstd, sum_g, sum_gx, M, C);
     PTD_CUDA_CHECK(cudaGetLastError());
-    const int agrid = bn_grid(M, C);
+    const int agrid = bn_grid(M, C, 3);
 #define PTD_BWD_S(RELU, GOUT)                                                                                          \
     bn_bwd_apply_kernel<RELU, GOUT><<<agrid, BN_THREADS, 0, st>>>((const bf16*)dz, (const bf16*)z, (const bf16*)y, mean, \
                                                                  invstd, gamma, sum_g, sum_gx, (bf16*)dy, (bf16*)g_out, M, C)
-    if (relu && g_out) PTD_BWD_S(true, true);
-    else if (relu) PTD_BWD_S(true, false);
-    else if (g_out) PTD_BWD_S(false, true);
-    else PTD_BWD_S(false, false);
+    if (relu && g_out) PTD_BWD_S(1, true);
+    else if (relu) PTD_BWD_S(1, false);
+    else if (g_out) PTD_BWD_S(0, true);
+    else PTD_BWD_S(0, false);
 #undef PTD_BWD_S
     PTD_CUDA_CHECK(cudaGetLastError());
     PTD_CUDA_CHECK(cudaMemcpyAsync(dbeta, sum_g, (size_t)C * sizeof(float), cudaMemcpyDeviceToDevice, st));

@@ -56,6 +56,7 @@ typedef struct {
     void* z[4];                    /* BN(+ReLU) outputs; z[2] is the block output */
     float* stats;                  /* scratch, 2*sum(Cout) floats */
     float* saved;                  /* out: per unit [mean | invstd], 2*sum(Cout) floats */
+    void* mask[4];                 /* out (optional, NULL = none): ReLU bit masks of units 0..2, u8[M][Cout/8] */
 } PtdBottleneckFwd;
 typedef struct {
     int N, H, W, inplanes, planes, stride, has_ds;
@@ -75,6 +76,7 @@ typedef struct {
     void* dz2;                     /* scratch: gradient w.r.t. z[1] */
     void* dz1;                     /* scratch: gradient w.r.t. z[0] */
     void* dx;                      /* out: gradient w.r.t. x */
+    const void* mask[4];           /* the forward's ReLU bit masks; a NULL entry recomputes the mask from z[i] */
 } PtdBottleneckBwd;
 int ptd_bottleneck_fwd(const PtdBottleneckFwd* d, void* stream);
 int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream);
@@ -92,10 +94,16 @@ int ptd_bn_stats(const void* y, float* sum, float* sq, long long M, int C, void*
 int ptd_bn_apply(const void* y, const void* residual, void* z, const float* sum, const float* sq, const float* gamma,
                  const float* beta, float* running_mean, float* running_var, float* save_mean, float* save_invstd,
                  long long M, int C, float eps, float momentum, int relu, void* stream);
+/* same; with relu and a non-NULL mask also writes one bit per element (u8[M][C/8]; bit i of byte (row, g) is set when
+ * element (row, 8g+i) is > 0 after the ReLU) for the backward passes to read in place of z */
+int ptd_bn_apply_mask(const void* y, const void* residual, void* z, void* mask, const float* sum, const float* sq,
+                      const float* gamma, const float* beta, float* running_mean, float* running_var, float* save_mean,
+                      float* save_invstd, long long M, int C, float eps, float momentum, int relu, void* stream);
 /* z = act(y * scale[c] + shift[c] [+ residual])  (inference-mode BN) */
 int ptd_affine_act(const void* y, const void* residual, void* z, const float* scale, const float* shift, long long M,
                    int C, int relu, void* stream);
-/* backward pass 1: sum_g[c] += g, sum_gx[c] += g * xhat (caller-zeroed fp32[C] each), g = dz * (z > 0 if relu) */
+/* backward pass 1: sum_g[c] += g, sum_gx[c] += g * xhat (caller-zeroed fp32[C] each), g = dz * (z > 0 if relu).
+ * relu = 2 (both passes): `z` is the bit mask ptd_bn_apply_mask wrote, not the activation */
 int ptd_bn_bwd_reduce(const void* dz, const void* z, const void* y, const float* mean, const float* invstd,
                       float* sum_g, float* sum_gx, long long M, int C, int relu, void* stream);
 /* backward pass 2: dy from the sums; g_out (optional) = masked incoming gradient (identity-branch gradient) */

@@ -34,6 +34,7 @@ _SIGS: dict[str, list] = {
     "ptd_linear_wgrad": [P, P, P, I, I, I, P],
     "ptd_bn_stats": [P, P, P, L, I, P],
     "ptd_bn_apply": [P, P, P, P, P, P, P, P, P, P, P, L, I, F, F, I, P],
+    "ptd_bn_apply_mask": [P, P, P, P, P, P, P, P, P, P, P, P, L, I, F, F, I, P],
     "ptd_affine_act": [P, P, P, P, P, L, I, I, P],
     "ptd_bn_bwd_reduce": [P, P, P, P, P, P, P, L, I, I, P],
     "ptd_bn_bwd_apply": [P, P, P, P, P, P, P, P, P, P, L, I, I, P],
@@ -65,7 +66,7 @@ class BottleneckFwd(ctypes.Structure):
     """Mirror of PtdBottleneckFwd (include/ptdb200.h)."""
     _fields_ = [("N", I), ("H", I), ("W", I), ("inplanes", I), ("planes", I), ("stride", I), ("has_ds", I),
                 ("eps", F), ("momentum", F), ("x", P), ("w", P * 4), ("gamma", P * 4), ("beta", P * 4),
-                ("running_mean", P * 4), ("running_var", P * 4), ("y", P * 4), ("z", P * 4), ("stats", P), ("saved", P)]
+                ("running_mean", P * 4), ("running_var", P * 4), ("y", P * 4), ("z", P * 4), ("stats", P), ("saved", P), ("mask", P * 4)]
 
 
 class BottleneckBwd(ctypes.Structure):
@@ -73,7 +74,7 @@ class BottleneckBwd(ctypes.Structure):
     _fields_ = [("N", I), ("H", I), ("W", I), ("inplanes", I), ("planes", I), ("stride", I), ("has_ds", I),
                 ("x", P), ("dz", P), ("w", P * 4), ("gamma", P * 4), ("y", P * 4), ("z", P * 4), ("saved", P),
                 ("sums", P), ("dw_all", P), ("dw_all_bytes", L), ("dw", P * 4), ("dy", P * 4), ("g_id", P), ("dz2", P),
-                ("dz1", P), ("dx", P)]
+                ("dz1", P), ("dx", P), ("mask", P * 4)]
 
 
 _LIB: Optional[ctypes.CDLL] = None

@@ -87,13 +87,17 @@ def conv_wgrad_raw(x: torch.Tensor, dy: torch.Tensor, w_shape, stride: int, pad:
     return out
 
 
-def bn_apply_raw(y, stats, gamma, beta, running_mean, running_var, eps, momentum, relu, residual=None):
+def bn_apply_raw(y, stats, gamma, beta, running_mean, running_var, eps, momentum, relu, residual=None,
+                 want_mask: bool = False):
+    """Returns ``(z, saved)``, or ``(z, saved, mask)`` with ``want_mask``: ``mask`` is the packed ReLU bit tensor
+    (uint8 ``[M, C/8]``) that :func:`bn_backward_raw` reads instead of ``z`` (``None`` when ``relu`` is off)."""
     n, c, h, w = y.shape
     z = torch.empty_like(y, memory_format=CL)
     saved = torch.empty((2, c), device=y.device, dtype=torch.float32)
-    _lib.call("ptd_bn_apply", y, residual, z, stats[0], stats[1], gamma, beta, running_mean, running_var,
+    mask = torch.empty((n * h * w, c // 8), device=y.device, dtype=torch.uint8) if (want_mask and relu) else None
+    _lib.call("ptd_bn_apply_mask", y, residual, z, mask, stats[0], stats[1], gamma, beta, running_mean, running_var,
               saved[0], saved[1], n * h * w, c, float(eps), float(momentum), int(relu), _stream())
-    return z, saved
+    return (z, saved, mask) if want_mask else (z, saved)
 
 
 def bn_stats_raw(y: torch.Tensor) -> torch.Tensor:
@@ -103,14 +107,16 @@ def bn_stats_raw(y: torch.Tensor) -> torch.Tensor:
     return stats
 
 
-def bn_backward_raw(dz, z, y, saved, gamma, relu: bool, want_gout: bool):
+def bn_backward_raw(dz, z, y, saved, gamma, relu: bool, want_gout: bool, mask: Optional[torch.Tensor] = None):
+    """``mask`` (from ``bn_apply_raw(..., want_mask=True)``) replaces ``z`` as the source of the ReLU mask."""
     n, c, h, w = y.shape
     m = n * h * w
     sums = torch.zeros((2, c), device=y.device, dtype=torch.float32)   # [0] = dbeta, [1] = dgamma
-    _lib.call("ptd_bn_bwd_reduce", dz, z, y, saved[0], saved[1], sums[0], sums[1], m, c, int(relu), _stream())
+    mode, zm = (2, mask) if (relu and mask is not None) else (int(relu), z)
+    _lib.call("ptd_bn_bwd_reduce", dz, zm, y, saved[0], saved[1], sums[0], sums[1], m, c, mode, _stream())
     dy = torch.empty_like(y, memory_format=CL)
     gout = torch.empty_like(y, memory_format=CL) if want_gout else None
-    _lib.call("ptd_bn_bwd_apply", dz, z, y, saved[0], saved[1], gamma, sums[0], sums[1], dy, gout, m, c, int(relu),
+    _lib.call("ptd_bn_bwd_apply", dz, zm, y, saved[0], saved[1], gamma, sums[0], sums[1], dy, gout, m, c, mode,
               _stream())
     return dy, gout, sums[1], sums[0]
 
@@ -127,18 +133,20 @@ class _ConvBnAct(torch.autograd.Function):
             y, stats = stem_fprop_raw(x, w_bf16)
         else:
             y, stats = conv_fprop_raw(x, w_bf16, stride, pad, True)
-        z, saved = bn_apply_raw(y, stats, gamma, beta, running_mean, running_var, eps, momentum, relu, residual)
-        ctx.save_for_backward(x, w_bf16, y, z, saved, gamma)
+        z, saved, mask = bn_apply_raw(y, stats, gamma, beta, running_mean, running_var, eps, momentum, relu, residual,
+                                      want_mask=True)
+        ctx.save_for_backward(x, w_bf16, y, mask, saved, gamma)     # the bit mask stands in for z
         ctx.cfg = (stride, pad, relu, stem, residual is not None, tuple(weight.shape))
         return z
 
     @staticmethod
     def backward(ctx, dz):
-        x, w_bf16, y, z, saved, gamma = ctx.saved_tensors
+        x, w_bf16, y, mask, saved, gamma = ctx.saved_tensors
         stride, pad, relu, stem, has_res, w_shape = ctx.cfg
         dz = as_nhwc_bf16(dz)
         need_x, need_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
-        dy, gout, dgamma, dbeta = bn_backward_raw(dz, z, y, saved, gamma, relu, has_res and ctx.needs_input_grad[7])
+        dy, gout, dgamma, dbeta = bn_backward_raw(dz, None, y, saved, gamma, relu,
+                                                  has_res and ctx.needs_input_grad[7], mask=mask)
         dx = dw = None
         if stem:
             if need_w:
@@ -191,17 +199,19 @@ class _BnAct(torch.autograd.Function):
     def forward(ctx, y, gamma, beta, running_mean, running_var, residual, eps, momentum, relu):
         y = as_nhwc_bf16(y)
         stats = bn_stats_raw(y)
-        z, saved = bn_apply_raw(y, stats, gamma, beta, running_mean, running_var, eps, momentum, relu, residual)
-        ctx.save_for_backward(y, z, saved, gamma)
+        z, saved, mask = bn_apply_raw(y, stats, gamma, beta, running_mean, running_var, eps, momentum, relu, residual,
+                                      want_mask=True)
+        ctx.save_for_backward(y, mask, saved, gamma)
         ctx.cfg = (relu, residual is not None)
         return z
 
     @staticmethod
     def backward(ctx, dz):
-        y, z, saved, gamma = ctx.saved_tensors
+        y, mask, saved, gamma = ctx.saved_tensors
         relu, has_res = ctx.cfg
         dz = as_nhwc_bf16(dz)
-        dy, gout, dgamma, dbeta = bn_backward_raw(dz, z, y, saved, gamma, relu, has_res and ctx.needs_input_grad[5])
+        dy, gout, dgamma, dbeta = bn_backward_raw(dz, None, y, saved, gamma, relu,
+                                                  has_res and ctx.needs_input_grad[5], mask=mask)
         return dy, dgamma, dbeta, None, None, gout, None, None, None
 
 
@@ -481,11 +491,18 @@ class _Bottleneck(torch.autograd.Function):
         d.running_var = _ptr4([u[5] for u in units])
         d.y, d.z = _ptr4(ys), _ptr4(zs)
         d.stats, d.saved = stats.data_ptr(), saved.data_ptr()
+        # ReLU bit masks of the three main-path units (1 bit per element): what the BN backward reads instead of z
+        mbuf = torch.empty(sum(numels[:3]) // 8, device=x.device, dtype=torch.uint8)
+        ma, o = (ctypes.c_void_p * 4)(), 0
+        for i in range(3):
+            ma[i] = mbuf.data_ptr() + o
+            o += numels[i] // 8
+        d.mask = ma
         _lib.call("ptd_bottleneck_fwd", d, _stream())
         ctx.cfg = cfg
         ctx.geom = (n, h, w, inplanes, planes, shapes)
         ctx.w_shapes = [tuple(u[0].shape) for u in units]
-        ctx.save_for_backward(x, ybuf, zbuf, saved, *[u[1] for u in units], *[u[2] for u in units])
+        ctx.save_for_backward(x, ybuf, zbuf, saved, mbuf, *[u[1] for u in units], *[u[2] for u in units])
         return zs[2]
 
     @staticmethod
@@ -494,9 +511,9 @@ class _Bottleneck(torch.autograd.Function):
         nu = 4 if has_ds else 3
         n, h, w, inplanes, planes, shapes = ctx.geom
         sv_t = ctx.saved_tensors
-        x, ybuf, zbuf, saved = sv_t[:4]
-        wbs = sv_t[4:4 + nu]
-        gammas = sv_t[4 + nu:4 + 2 * nu]
+        x, ybuf, zbuf, saved, mbuf = sv_t[:5]
+        wbs = sv_t[5:5 + nu]
+        gammas = sv_t[5 + nu:5 + 2 * nu]
         w_shapes = ctx.w_shapes
         dz = as_nhwc_bf16(dz)
         dev = dz.device
@@ -535,6 +552,11 @@ class _Bottleneck(torch.autograd.Function):
         for i in range(nu):
             ya[i], za[i] = ys_ptr[i], zs_ptr[i]
         d.y, d.z = ya, za
+        ma, o = (ctypes.c_void_p * 4)(), 0
+        for i in range(3):
+            ma[i] = mbuf.data_ptr() + o
+            o += numels[i] // 8
+        d.mask = ma
         d.saved, d.sums = saved.data_ptr(), sums.data_ptr()
         d.dw_all, d.dw_all_bytes = dw_all.data_ptr(), dw_all.numel() * 4
         d.dw = _ptr4(dws)

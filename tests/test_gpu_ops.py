@@ -159,6 +159,26 @@ def test_bn_forward_backward(c, relu, res):
         assert _rel(r1.grad, rf.grad) < 1e-2
 
 
+@pytest.mark.parametrize("c,res", [(64, False), (1024, True)])
+def test_bn_relu_bit_mask_equals_mask_from_z(c, res):
+    """The packed 1-bit ReLU mask written by the forward gives the same gradients as re-deriving the mask from z."""
+    n, h = 3, 11
+    y, dz = _act(n, c, h, h, scale=2.0), _act(n, c, h, h, seed=5)
+    r = _act(n, c, h, h, seed=9) if res else None
+    gamma, beta = torch.rand(c, device=DEV) + 0.5, torch.randn(c, device=DEV) * 0.1
+    stats = K.bn_stats_raw(y)
+    z, saved, mask = K.bn_apply_raw(y, stats, gamma, beta, None, None, 1e-5, 0.1, True, r, want_mask=True)
+    assert mask.shape == (n * h * h, c // 8) and mask.dtype == torch.uint8
+    zf = z.permute(0, 2, 3, 1).reshape(-1, c // 8, 8)
+    expect = ((zf > 0).to(torch.int32) << torch.arange(8, device=DEV, dtype=torch.int32)).sum(-1).to(torch.uint8)
+    assert torch.equal(mask, expect)
+    a = K.bn_backward_raw(dz, z, y, saved, gamma, True, res)
+    b = K.bn_backward_raw(dz, None, y, saved, gamma, True, res, mask=mask)
+    for ta, tb in zip(a, b):
+        if ta is not None:          # equal up to the order of the atomic adds into the per-channel sums
+            assert _rel(ta, tb) < 1e-4
+
+
 def test_conv_bn_act_fused_matches_unfused():
     x, c = _act(4, 64, 16, 16), 128
     w = _wt(c, 64, 3).float().contiguous(memory_format=CL).requires_grad_()
