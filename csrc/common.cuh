@@ -149,6 +149,14 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* m, 
         : "memory");
 }
 
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
+                                            int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+
 // im2col-mode load: (c, w, h, n) is the input-space position of the first pixel's top-left tap, (off_w, off_h) the
 // filter tap; the box is [pixels][64 channels].
 __device__ __forceinline__ void tma_load_im2col(uint32_t dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h,

@@ -211,7 +211,10 @@ __device__ __forceinline__ float transpose_reduce32(float (&v)[32], uint32_t lan
 // ------------------------------------------------------------------------------------------
 // igemm_f
 // ------------------------------------------------------------------------------------------
-enum { AM_GATHER = 0, AM_TILED = 1, AM_IM2COL = 2 };   // how the pixel-row operand reaches shared memory
+// How the pixel-row operand reaches shared memory.  AM_PATCH: a 4-D tiled descriptor whose box is a [rows x 16]
+// patch of output pixels (x 64 contiguous elements); used by the space-to-depth stem, where the row of output pixel
+// (oh, ow) for k-block r' is the 128-byte window at pixel (oh + r', ow) of the input.
+enum { AM_GATHER = 0, AM_TILED = 1, AM_IM2COL = 2, AM_PATCH = 3 };
 
 template <int BLOCK_N, int A_MODE, bool B_MN, int EPI /*0 = bf16 (+stats/+addend), 1 = fp32 + bias*/>
 struct FCfg {
@@ -323,12 +326,22 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                     iw0 = ow * p.g.stride - p.g.pad;
                     ih0 = oh * p.g.stride - p.g.pad;
                 }
+                int px0 = 0, py0 = 0, pn = 0;           // patch mode: first pixel of the tile's 8 x 16 patch
+                if (A_MODE == AM_PATCH) {
+                    const int mt = t / p.n_blocks, tiles_x = p.g.OW >> 4, per_img = tiles_x * (p.g.OH >> 3);
+                    pn = mt / per_img;
+                    const int rem = mt - pn * per_img;
+                    const int ty = rem / tiles_x;
+                    py0 = ty * 8;
+                    px0 = (rem - ty * tiles_x) * 16;
+                }
                 for (int kb = 0; kb < p.num_kb; ++kb) {
                     mbar_wait(&bars->empty[stage], phase ^ 1);
                     const uint32_t a_dst = smem_base + stage * Cfg::STAGE_BYTES;
                     const uint32_t b_dst = a_dst + A_TILE_BYTES;
                     mbar_arrive_expect_tx(&bars->full[stage], Cfg::B_TILE_BYTES + (A_TMA ? A_TILE_BYTES : 0));
                     if (A_MODE == AM_TILED) tma_load_2d(a_dst, &p.tmA, &bars->full[stage], kb * BLOCK_K, m0);
+                    if (A_MODE == AM_PATCH) tma_load_4d(a_dst, &p.tmA, &bars->full[stage], 0, px0, py0 + kb, pn);
                     if (A_MODE == AM_IM2COL) {
                         const int te = kb / p.g.cblocks;
                         const int cb = kb - te * p.g.cblocks;
@@ -432,7 +445,14 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                         const long long mr = m_base + row;
                         if (mr < p.M) {
                             long long orow = mr;
-                            if (p.map_mul != 0) {
+                            if (A_MODE == AM_PATCH) {
+                                // tile = 8 x 16 patch of output pixels, row r of the tile = pixel (r / 16, r % 16) of it
+                                const int mt = t / p.n_blocks, tiles_x = p.g.OW >> 4, per_img = tiles_x * (p.g.OH >> 3);
+                                const int n_ = mt / per_img, rem_ = mt - n_ * per_img;
+                                const int ty = rem_ / tiles_x, tx = rem_ - ty * tiles_x;
+                                const int r_ = q * 32 + row;
+                                orow = ((long long)n_ * p.g.OH + ty * 8 + (r_ >> 4)) * p.g.OW + tx * 16 + (r_ & 15);
+                            } else if (p.map_mul != 0) {
                                 const int n_ = (int)(mr / p.map_sub_ohw);
                                 const int rem_ = (int)(mr - (long long)n_ * p.map_sub_ohw);
                                 const int a_ = rem_ / p.map_sub_ow, b_ = rem_ - a_ * p.map_sub_ow;
@@ -620,9 +640,27 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_ke
                 const uint32_t b_dst = a_dst + Cfg::A_BYTES;
                 const bool skip_b = (p.dbg & 1) != 0;
                 mbar_arrive_expect_tx(&bars->full[stage], Cfg::A_BYTES + ((B_TMA && !skip_b) ? Cfg::B_BYTES : 0));
+                int px0 = 0, py0 = 0, pn = 0;           // patch mode: k-block = a 4 x 16 patch of output pixels
+                if (B_MODE == AM_PATCH) {
+                    const int patches_x = p.g.OW >> 4, per_img = patches_x * (p.g.OH >> 2);
+                    pn = kb / per_img;
+                    const int rem = kb - pn * per_img;
+                    const int py = rem / patches_x;
+                    py0 = py * 4;
+                    px0 = (rem - py * patches_x) * 16;
+                }
 #pragma unroll
-                for (int j = 0; j < Cfg::MSUB; ++j)
-                    tma_load_2d(a_dst + j * SUB_TILE_BYTES, &p.tmA, &bars->full[stage], m_blk * MROWS + j * 64, kb * 64);
+                for (int j = 0; j < Cfg::MSUB; ++j) {
+                    if (B_MODE == AM_PATCH)
+                        tma_load_4d(a_dst + j * SUB_TILE_BYTES, &p.tmA, &bars->full[stage], m_blk * MROWS + j * 64, px0, py0, pn);
+                    else
+                        tma_load_2d(a_dst + j * SUB_TILE_BYTES, &p.tmA, &bars->full[stage], m_blk * MROWS + j * 64, kb * 64);
+                }
+                if (B_MODE == AM_PATCH && !skip_b) {
+#pragma unroll
+                    for (int j = 0; j < NSUB; ++j)      // sub-tile j of this n block = filter row r' = n_blk * NSUB + j
+                        tma_load_4d(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage], 0, px0, py0 + n_blk * NSUB + j, pn);
+                }
                 if (B_MODE == AM_TILED && !skip_b) {
 #pragma unroll
                     for (int j = 0; j < NSUB; ++j) {
@@ -827,8 +865,9 @@ int launch_w(WParams& p, cudaStream_t stream) {
     // bound by per-SM ingress, which multicast does not reduce) - kept as an option, off by default
     if (use_cluster < 0) { const char* e = getenv("PTD_WGRAD_CLUSTER"); use_cluster = e ? atoi(e) : 0; }
     if (m2) return launch_w_impl<NSUB, B_MODE, false, M2_OK>(p, grid, stream);
-    if (B_MODE != AM_GATHER && (NSUB % 2) == 0 && (p.m_blocks % 2) == 0 && use_cluster)
-        return launch_w_impl<NSUB, B_MODE, (B_MODE != AM_GATHER && NSUB % 2 == 0), false>(p, grid, stream);
+    constexpr bool CL_OK = (B_MODE == AM_TILED || B_MODE == AM_IM2COL) && NSUB % 2 == 0;
+    if (CL_OK && (p.m_blocks % 2) == 0 && use_cluster)
+        return launch_w_impl<NSUB, B_MODE, CL_OK, false>(p, grid, stream);
     return launch_w_impl<NSUB, B_MODE, false, false>(p, grid, stream);
 }
 
@@ -1053,6 +1092,55 @@ extern "C" int ptd_stem_wgrad(const void* x4, const void* dy, float* dw4, int N,
     if (rc) return rc;
     fill_geom(p.g, (const bf16*)x4, H, W, 4, OH, OW, 7, 7, 2, 3, GM_STEM);
     return dispatch_w<AM_GATHER>(p, 4, stream);
+}
+
+// Stem on the space-to-depth input (pool_layout.cu: nchw3_to_s2d_kernel): xs is [N][OH+3][OW+3][16].
+namespace {
+bool stem_s2d_shape_ok(int H, int W) { return H % 16 == 0 && W % 32 == 0; }      // OH % 8 == 0, OW % 16 == 0
+// rows of output pixels x 128-byte windows: element (e, ow, hs, n) sits at ((n*Hs + hs)*Ws + ow)*16 + e, e < 64
+int stem_window_map(CUtensorMap* out, const void* xs, int N, int OH, int OW, int box_rows) {
+    const uint64_t Hs = OH + 3, Ws = OW + 3;
+    const uint64_t dims[4] = {64, (uint64_t)OW, Hs, (uint64_t)N};
+    const uint64_t strides[3] = {32, Ws * 32, Hs * Ws * 32};
+    const uint32_t box[4] = {64, 16, (uint32_t)box_rows, 1};
+    return ptd_make_tmap_4d_bf16(out, xs, dims, strides, box);
+}
+}  // namespace
+
+extern "C" int ptd_stem_s2d_fprop(const void* xs, const void* w16, void* y, float* stat_sum, float* stat_sq, int N,
+                                  int H, int W, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    PTD_REQUIRE(stem_s2d_shape_ok(H, W), "stem_s2d: needs H %% 16 == 0 and W %% 32 == 0 (got %d x %d)", H, W);
+    const int OH = H / 2, OW = W / 2;
+    FParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = N * OH * OW; p.N = 64; p.num_kb = 4;
+    p.out = (bf16*)y; p.ldo = 64; p.stat_sum = stat_sum; p.stat_sq = stat_sq;
+    int rc = ptd_make_tmap_2d_bf16(&p.tmB, w16, 256, 64, 512, 64, 64);
+    if (rc) return rc;
+    rc = stem_window_map(&p.tmA, xs, N, OH, OW, 8);
+    if (rc) return rc;
+    fill_geom(p.g, (const bf16*)xs, OH + 3, OW + 3, 16, OH, OW, 4, 4, 1, 0, GM_FPROP);
+    return dispatch_f<AM_PATCH, false, 0>(p, 64, stream);
+}
+
+extern "C" int ptd_stem_s2d_wgrad(const void* xs, const void* dy, float* dw16, int N, int H, int W, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    PTD_REQUIRE(stem_s2d_shape_ok(H, W), "stem_s2d: needs H %% 16 == 0 and W %% 32 == 0 (got %d x %d)", H, W);
+    const int OH = H / 2, OW = W / 2;
+    WParams p;
+    memset(&p, 0, sizeof(p));
+    p.P = N * OH * OW; p.Cout = 64; p.Kw = 256; p.dw = dw16;
+    // dY as [4 x 16 pixel patch][64 channels] so that its rows pair up with the window rows of the same patch
+    const uint64_t dims[4] = {64, (uint64_t)OW, (uint64_t)OH, (uint64_t)N};
+    const uint64_t strides[3] = {128, (uint64_t)OW * 128, (uint64_t)OH * OW * 128};
+    const uint32_t box[4] = {64, 16, 4, 1};
+    int rc = ptd_make_tmap_4d_bf16(&p.tmA, dy, dims, strides, box);
+    if (rc) return rc;
+    rc = stem_window_map(&p.tmB, xs, N, OH, OW, 4);
+    if (rc) return rc;
+    fill_geom(p.g, (const bf16*)xs, OH + 3, OW + 3, 16, OH, OW, 4, 4, 1, 0, GM_FPROP);
+    return dispatch_w<AM_PATCH>(p, 4, stream);
 }
 
 // Classifier / generic dense layers.  a: [M][K] bf16, w: [N][K] bf16.

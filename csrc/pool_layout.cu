@@ -238,6 +238,80 @@ __global__ void __launch_bounds__(256) stem_unpack_kernel(const float* __restric
     }
 }
 
+// ---- space-to-depth stem input ---------------------------------------------------------------------
+// NCHW fp32 [N,3,H,W] -> bf16 [N][OH+3][OW+3][16]: pixel (hs, ws) holds the 2x2 block of the 3-padded image at
+// (2hs-3 .. 2hs-2, 2ws-3 .. 2ws-2), channel index (dy*2 + dx)*3 + ch, entries 12..15 zero.  In this layout the
+// 7x7 stride-2 convolution is a 4x4 stride-1 convolution over 16 channels, and the im2col row of output pixel
+// (oh, ow) for filter row r' is the 128 CONTIGUOUS bytes starting at pixel (oh + r', ow): a plain tiled TMA
+// descriptor with an overlapping pixel stride fetches it (igemm.cu, AM_PATCH).
+__global__ void __launch_bounds__(256) nchw3_to_s2d_kernel(const float* __restrict__ x, bf16* __restrict__ y, int N,
+                                                           int H, int W, int Hs, int Ws) {
+    const long long total = (long long)N * Hs * Ws;
+    const long long HW = (long long)H * W;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (long long)gridDim.x * blockDim.x) {
+        const int ws = (int)(t % Ws);
+        const long long t2 = t / Ws;
+        const int hs = (int)(t2 % Hs);
+        const long long n = t2 / Hs;
+        const float* src = x + n * 3 * HW;
+        float v[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = 0.f;
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy) {
+            const int ih = 2 * hs + dy - 3;
+#pragma unroll
+            for (int dx = 0; dx < 2; ++dx) {
+                const int iw = 2 * ws + dx - 3;
+                if (ih >= 0 && ih < H && iw >= 0 && iw < W) {
+#pragma unroll
+                    for (int ch = 0; ch < 3; ++ch) v[(dy * 2 + dx) * 3 + ch] = src[ch * HW + (long long)ih * W + iw];
+                }
+            }
+        }
+        uint4 o0, o1;
+        o0.x = pack_bf16x2(v[0], v[1]);   o0.y = pack_bf16x2(v[2], v[3]);
+        o0.z = pack_bf16x2(v[4], v[5]);   o0.w = pack_bf16x2(v[6], v[7]);
+        o1.x = pack_bf16x2(v[8], v[9]);   o1.y = pack_bf16x2(v[10], v[11]);
+        o1.z = 0u;                        o1.w = 0u;
+        uint4* dst = reinterpret_cast<uint4*>(y + t * 16);
+        dst[0] = o0;
+        dst[1] = o1;
+    }
+}
+
+// Stem weights for the space-to-depth form: bf16 [64][4 r'][4 s'][16 c'], c' = (dy*2+dx)*3 + ch, tap (2r'+dy, 2s'+dx).
+__device__ __forceinline__ bool s2d_decode(int t, int& k, int& ch, int& r, int& s) {
+    const int c = t & 15, sp = (t >> 4) & 3, rp = (t >> 6) & 3;
+    k = t >> 8;
+    if (c >= 12) return false;
+    const int q = c / 3;
+    ch = c - q * 3;
+    r = 2 * rp + (q >> 1);
+    s = 2 * sp + (q & 1);
+    return r < 7 && s < 7;
+}
+__global__ void __launch_bounds__(256) stem_pack_s2d_kernel(const float* __restrict__ w, bf16* __restrict__ w16,
+                                                            long long sk, long long sc, long long sr, long long ss) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= 64 * 256) return;
+    int k, ch, r, s;
+    const bool ok = s2d_decode(t, k, ch, r, s);
+    w16[t] = __float2bfloat16(ok ? w[k * sk + ch * sc + r * sr + s * ss] : 0.f);
+}
+__global__ void __launch_bounds__(256) stem_unpack_s2d_kernel(const float* __restrict__ dw16, float* __restrict__ dw,
+                                                              long long sk, long long sc, long long sr, long long ss,
+                                                              int accumulate) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= 64 * 256) return;
+    int k, ch, r, s;
+    if (s2d_decode(t, k, ch, r, s)) {
+        float* d = dw + k * sk + ch * sc + r * sr + s * ss;
+        *d = accumulate ? *d + dw16[t] : dw16[t];
+    }
+}
+
 int ew_grid(long long work_items, int threads) {
     long long blocks = (work_items + threads - 1) / threads;
     const long long cap = (long long)ptd_num_sms() * 16;
@@ -301,6 +375,25 @@ extern "C" int ptd_cast_f32_to_bf16(const float* x, void* y, long long n, void* 
     PTD_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 7) == 0,
                 "cast: pointers must be 16-/8-byte aligned");
     cast_f32_bf16_kernel<<<ew_grid(n / 4 + 1, 256), 256, 0, (cudaStream_t)stream>>>(x, (bf16*)y, n);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+extern "C" int ptd_nchw3_f32_to_s2d_bf16(const float* x, void* y, int N, int H, int W, void* stream) {
+    PTD_REQUIRE(H % 2 == 0 && W % 2 == 0, "s2d stem input: H (%d) and W (%d) must be even", H, W);
+    const int Hs = H / 2 + 3, Ws = W / 2 + 3;
+    nchw3_to_s2d_kernel<<<ew_grid((long long)N * Hs * Ws, 256), 256, 0, (cudaStream_t)stream>>>(x, (bf16*)y, N, H, W, Hs, Ws);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+extern "C" int ptd_stem_pack_weight_s2d(const float* w, void* w16, long long sk, long long sc, long long sr,
+                                        long long ss, void* stream) {
+    stem_pack_s2d_kernel<<<64, 256, 0, (cudaStream_t)stream>>>(w, (bf16*)w16, sk, sc, sr, ss);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+extern "C" int ptd_stem_unpack_wgrad_s2d(const float* dw16, float* dw, long long sk, long long sc, long long sr,
+                                         long long ss, int accumulate, void* stream) {
+    stem_unpack_s2d_kernel<<<64, 256, 0, (cudaStream_t)stream>>>(dw16, dw, sk, sc, sr, ss, accumulate);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }

@@ -110,6 +110,34 @@ int ptd_make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int W, 
     return PTD_OK;
 }
 
+int ptd_make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims_[4], const uint64_t strides_bytes[3],
+                          const uint32_t box_[4]) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) {
+        ptd_set_error("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
+        return PTD_ERR_CUDA;
+    }
+    if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || ((strides_bytes[0] | strides_bytes[1] | strides_bytes[2]) & 15) != 0) {
+        ptd_set_error("TMA needs a 16-byte aligned base (%p) and strides", base);
+        return PTD_ERR_ARG;
+    }
+    cuuint64_t dims[4] = {dims_[0], dims_[1], dims_[2], dims_[3]};
+    cuuint64_t strides[3] = {strides_bytes[0], strides_bytes[1], strides_bytes[2]};
+    cuuint32_t box[4] = {box_[0], box_[1], box_[2], box_[3]};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        ptd_set_error("cuTensorMapEncodeTiled (4-D) failed: %d (dims %llu %llu %llu %llu, strides %llu %llu %llu, box %u %u %u %u)",
+                      (int)r, (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)dims[2],
+                      (unsigned long long)dims[3], (unsigned long long)strides[0], (unsigned long long)strides[1],
+                      (unsigned long long)strides[2], box[0], box[1], box[2], box[3]);
+        return PTD_ERR_CUDA;
+    }
+    return PTD_OK;
+}
+
 int ptd_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t rows, uint64_t row_pitch_bytes,
                           uint32_t box_inner, uint32_t box_rows) {
     EncodeTiledFn enc = get_encode();

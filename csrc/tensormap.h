@@ -12,3 +12,8 @@ int ptd_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, ui
 // im2col-mode descriptor over an NHWC bf16 activation (see runtime.cu for the walk it describes).
 int ptd_make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int W, int H, int N, int lower_w, int lower_h,
                               int upper_w, int upper_h, int pixels, int stride);
+
+// General 4-D tiled descriptor (128-byte swizzle): dims[0] is the contiguous extent in elements, strides_bytes[i] the
+// byte stride of dimension i+1.  Strides may be smaller than the extent below them (overlapping windows).
+int ptd_make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint64_t strides_bytes[3],
+                          const uint32_t box[4]);

@@ -39,6 +39,12 @@ int ptd_conv_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W
 int ptd_stem_fprop(const void* x4, const void* w4, void* y, float* stat_sum, float* stat_sq, int N, int H, int W,
                    void* stream);
 int ptd_stem_wgrad(const void* x4, const void* dy, float* dw4, int N, int H, int W, void* stream);
+/* The same stem on a space-to-depth input xs = bf16 [N][H/2+3][W/2+3][16] (ptd_nchw3_f32_to_s2d_bf16): a 4x4/1
+ * convolution over 16 channels whose im2col rows are contiguous 128-byte windows, fetched by tiled TMA.
+ * w16 / dw16 are [64][4][4][16] (ptd_stem_pack_weight_s2d).  Needs H % 16 == 0 and W % 32 == 0. */
+int ptd_stem_s2d_fprop(const void* xs, const void* w16, void* y, float* stat_sum, float* stat_sq, int N, int H, int W,
+                       void* stream);
+int ptd_stem_s2d_wgrad(const void* xs, const void* dy, float* dw16, int N, int H, int W, void* stream);
 
 /* ---- a whole residual bottleneck per call (conv1x1-BN-ReLU, conv3x3-BN-ReLU, conv1x1-BN (+identity | +downsample
  *      conv-BN) -ReLU; torchvision Bottleneck, R/03 模型并行/03_model_parallel.ipynb#cell5).  Index 0..2 = conv1..conv3,
@@ -128,6 +134,11 @@ int ptd_nchw3_f32_to_nhwc4_bf16(const float* x, void* y, int N, int H, int W, vo
 int ptd_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int HW, void* stream);
 int ptd_nhwc_bf16_to_nchw_f32(const void* x, float* y, int N, int C, int HW, void* stream);
 int ptd_cast_f32_to_bf16(const float* x, void* y, long long n, void* stream);
+int ptd_nchw3_f32_to_s2d_bf16(const float* x, void* xs, int N, int H, int W, void* stream);
+int ptd_stem_pack_weight_s2d(const float* w, void* w16, long long sk, long long sc, long long sr, long long ss,
+                             void* stream);
+int ptd_stem_unpack_wgrad_s2d(const float* dw16, float* dw, long long sk, long long sc, long long sr, long long ss,
+                              int accumulate, void* stream);
 int ptd_stem_pack_weight(const float* w, void* w4, long long sk, long long sc, long long sr, long long ss, void* stream);
 int ptd_stem_unpack_wgrad(const float* dw4, float* dw, long long sk, long long sc, long long sr, long long ss,
                           int accumulate, void* stream);

@@ -29,6 +29,8 @@ _SIGS: dict[str, list] = {
     "ptd_bottleneck_bwd": [P, P],
     "ptd_stem_fprop": [P, P, P, P, P, I, I, I, P],
     "ptd_stem_wgrad": [P, P, P, I, I, I, P],
+    "ptd_stem_s2d_fprop": [P, P, P, P, P, I, I, I, P],
+    "ptd_stem_s2d_wgrad": [P, P, P, I, I, I, P],
     "ptd_linear_fwd": [P, P, P, P, I, I, I, P],
     "ptd_linear_dgrad": [P, P, P, I, I, I, P],
     "ptd_linear_wgrad": [P, P, P, I, I, I, P],
@@ -48,6 +50,9 @@ _SIGS: dict[str, list] = {
     "ptd_nhwc_bf16_to_nchw_f32": [P, P, I, I, I, P],
     "ptd_cast_f32_to_bf16": [P, P, L, P],
     "ptd_stem_pack_weight": [P, P, L, L, L, L, P],
+    "ptd_nchw3_f32_to_s2d_bf16": [P, P, I, I, I, P],
+    "ptd_stem_pack_weight_s2d": [P, P, L, L, L, L, P],
+    "ptd_stem_unpack_wgrad_s2d": [P, P, L, L, L, L, I, P],
     "ptd_stem_unpack_wgrad": [P, P, L, L, L, L, I, P],
     "ptd_softmax_ce": [P, P, P, P, P, I, I, I, I, F, P],
     "ptd_multi_sgd": [P, P, I, F, F, F, F, I, P],

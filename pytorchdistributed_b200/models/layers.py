@@ -48,7 +48,7 @@ class Conv2d(nn.Module):
         self._shadow_key = (self.weight.data_ptr(), self.weight._version)
 
     def shadow(self) -> torch.Tensor:
-        """bf16 copy in the kernel's layout: [Cout][R][S][Cin], or [64][8][8][4] for the stem."""
+        """bf16 copy in the kernel's layout: [Cout][R][S][Cin]; for the stem both packed forms (``F_.stem_pack``)."""
         w = self.weight
         key = (w.data_ptr(), w._version)
         if self._shadow is None or self._shadow_key != key or self._shadow.device != w.device:

@@ -73,7 +73,7 @@ class Stem(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.is_cuda:
-            x = F_.to_nhwc4(x)
+            x = F_.stem_input(x)
         return conv_bn_act(x, self.conv, self.bn, relu=True)
 
 
@@ -111,7 +111,7 @@ class ResNet(nn.Module):
     # -- pieces -----------------------------------------------------------------------------
     def stem(self, x: torch.Tensor) -> torch.Tensor:
         if x.is_cuda:
-            x = F_.to_nhwc4(x)
+            x = F_.stem_input(x)
         return conv_bn_act(x, self.conv1, self.bn1, relu=True)
 
     def features(self, x: torch.Tensor) -> torch.Tensor:

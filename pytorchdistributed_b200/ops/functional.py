@@ -18,6 +18,8 @@ from __future__ import annotations
 import ctypes
 from typing import Optional, Tuple
 
+import os
+
 import torch
 
 from .. import _lib
@@ -236,7 +238,7 @@ def affine_act(y, scale, shift, residual=None, relu=False):
 # stem helpers
 # ------------------------------------------------------------------------------------------------
 def to_nhwc4(x: torch.Tensor) -> torch.Tensor:
-    """fp32 NCHW image batch [N,3,H,W] -> bf16 NHWC with a zero 4th channel (stem input)."""
+    """fp32 NCHW image batch [N,3,H,W] -> bf16 NHWC with a zero 4th channel (stem input, any H x W)."""
     n, c, h, w = x.shape
     assert c == 3, "stem expects 3 input channels"
     x = x.contiguous().float()
@@ -245,29 +247,63 @@ def to_nhwc4(x: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def stem_s2d_ok(h: int, w: int) -> bool:
+    """The TMA stem works on whole 8 x 16 patches of output pixels."""
+    return h % 16 == 0 and w % 32 == 0 and os.environ.get("PTDB200_STEM_S2D", "1") != "0"
+
+
+def to_s2d(x: torch.Tensor) -> torch.Tensor:
+    """fp32 NCHW image batch [N,3,H,W] -> bf16 space-to-depth stem input, logical shape [N,16,H/2+3,W/2+3]
+    (channels_last): pixel (hs, ws) = the 2x2 block at (2hs-3, 2ws-3) of the zero-padded image, 12 of 16 channels
+    used.  On it the 7x7/2 stem is a 4x4/1 convolution whose im2col rows are contiguous (``csrc/igemm.cu``)."""
+    n, c, h, w = x.shape
+    assert c == 3 and stem_s2d_ok(h, w)
+    x = x.contiguous().float()
+    out = _empty_act(n, 16, h // 2 + 3, w // 2 + 3, x.device)
+    _lib.call("ptd_nchw3_f32_to_s2d_bf16", x, out, n, h, w, _stream())
+    return out
+
+
+def stem_input(x: torch.Tensor) -> torch.Tensor:
+    """The stem's input format for this image size: space-to-depth when the size allows, NHWC4 otherwise."""
+    return to_s2d(x) if stem_s2d_ok(x.shape[2], x.shape[3]) else to_nhwc4(x)
+
+
 def stem_pack(weight: torch.Tensor) -> torch.Tensor:
-    w4 = torch.empty((64, 256), device=weight.device, dtype=torch.bfloat16)
+    """bf16 [2][64][256]: [0] = [64][8][8][4] for the NHWC4 stem, [1] = [64][4][4][16] for the space-to-depth stem."""
+    wp = torch.empty((2, 64, 256), device=weight.device, dtype=torch.bfloat16)
     sk, sc, sr, ss = weight.stride()
-    _lib.call("ptd_stem_pack_weight", weight, w4, sk, sc, sr, ss, _stream())
-    return w4
+    _lib.call("ptd_stem_pack_weight", weight, wp[0], sk, sc, sr, ss, _stream())
+    _lib.call("ptd_stem_pack_weight_s2d", weight, wp[1], sk, sc, sr, ss, _stream())
+    return wp
 
 
-def stem_fprop_raw(x4: torch.Tensor, w4: torch.Tensor):
-    n, _, h, w = x4.shape
-    oh, ow = out_hw(h, w, 7, 7, 2, 3)
-    y = _empty_act(n, 64, oh, ow, x4.device)
-    stats = torch.zeros((2, 64), device=x4.device, dtype=torch.float32)
-    _lib.call("ptd_stem_fprop", x4, w4, y, stats[0], stats[1], n, h, w, _stream())
+def stem_fprop_raw(xin: torch.Tensor, wp: torch.Tensor):
+    """``xin`` from :func:`stem_input` (16 channels = space-to-depth, 4 = NHWC4), ``wp`` from :func:`stem_pack`."""
+    n, c, h, w = xin.shape
+    stats = torch.zeros((2, 64), device=xin.device, dtype=torch.float32)
+    if c == 16:
+        oh, ow = h - 3, w - 3
+        y = _empty_act(n, 64, oh, ow, xin.device)
+        _lib.call("ptd_stem_s2d_fprop", xin, wp[1], y, stats[0], stats[1], n, 2 * oh, 2 * ow, _stream())
+    else:
+        oh, ow = out_hw(h, w, 7, 7, 2, 3)
+        y = _empty_act(n, 64, oh, ow, xin.device)
+        _lib.call("ptd_stem_fprop", xin, wp[0], y, stats[0], stats[1], n, h, w, _stream())
     return y, stats
 
 
-def stem_wgrad_raw(x4: torch.Tensor, dy: torch.Tensor, w_shape) -> torch.Tensor:
-    n, _, h, w = x4.shape
-    dw4 = torch.zeros((64, 256), device=x4.device, dtype=torch.float32)
-    _lib.call("ptd_stem_wgrad", x4, dy, dw4, n, h, w, _stream())
-    dw = torch.empty(w_shape, device=x4.device, dtype=torch.float32, memory_format=CL)
+def stem_wgrad_raw(xin: torch.Tensor, dy: torch.Tensor, w_shape) -> torch.Tensor:
+    n, c, h, w = xin.shape
+    dwp = torch.zeros((64, 256), device=xin.device, dtype=torch.float32)
+    dw = torch.empty(w_shape, device=xin.device, dtype=torch.float32, memory_format=CL)
     sk, sc, sr, ss = dw.stride()
-    _lib.call("ptd_stem_unpack_wgrad", dw4, dw, sk, sc, sr, ss, 0, _stream())
+    if c == 16:
+        _lib.call("ptd_stem_s2d_wgrad", xin, dy, dwp, n, 2 * (h - 3), 2 * (w - 3), _stream())
+        _lib.call("ptd_stem_unpack_wgrad_s2d", dwp, dw, sk, sc, sr, ss, 0, _stream())
+    else:
+        _lib.call("ptd_stem_wgrad", xin, dy, dwp, n, h, w, _stream())
+        _lib.call("ptd_stem_unpack_wgrad", dwp, dw, sk, sc, sr, ss, 0, _stream())
     return dw
 
 

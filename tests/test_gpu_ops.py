@@ -110,6 +110,37 @@ def test_stem():
     assert _rel(dw, refw) < 1e-2
 
 
+@pytest.mark.parametrize("n,h,w", [(4, 64, 64), (3, 32, 96), (2, 224, 224)])
+def test_stem_space_to_depth(n, h, w):
+    """The TMA stem (space-to-depth input, 4x4/1 conv over 16 channels) against F.conv2d(7x7, stride 2, pad 3)."""
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(n, 3, h, w, generator=g).to(DEV)
+    wt = (torch.randn(64, 3, 7, 7, generator=g) * 0.1).to(DEV).contiguous(memory_format=CL)
+    assert K.stem_s2d_ok(h, w)
+    xs = K.stem_input(x)
+    assert xs.shape == (n, 16, h // 2 + 3, w // 2 + 3)
+    # layout: pixel (hs, ws), channel (dy*2+dx)*3+ch = padded image at (2hs+dy, 2ws+dx)
+    xp = F.pad(x.to(torch.bfloat16).float(), (3, 3, 3, 3))
+    ref_s2d = torch.zeros(n, 16, h // 2 + 3, w // 2 + 3, device=DEV)
+    for dy in range(2):
+        for dx in range(2):
+            for ch in range(3):
+                ref_s2d[:, (dy * 2 + dx) * 3 + ch] = xp[:, ch, dy::2, dx::2]
+    assert torch.equal(xs.float(), ref_s2d)
+    wp = K.stem_pack(wt)
+    y, stats = K.stem_fprop_raw(xs, wp)
+    ref = F.conv2d(x.to(torch.bfloat16).float(), wt.to(torch.bfloat16).float(), None, 2, 3)
+    assert y.shape == ref.shape
+    assert _rel(y, ref) < 1e-2
+    assert _rel(stats[1], (ref * ref).sum((0, 2, 3))) < 1e-2
+    y4, _ = K.stem_fprop_raw(K.to_nhwc4(x), wp)          # the gather stem computes the same thing
+    assert _rel(y, y4) < 1e-3
+    dy_ = _act(n, 64, h // 2, w // 2, seed=7)
+    dw = K.stem_wgrad_raw(xs, dy_, wt.shape)
+    refw = torch.nn.grad.conv2d_weight(x.to(torch.bfloat16).float(), wt.shape, dy_.float(), 2, 3)
+    assert _rel(dw, refw) < 1e-2
+
+
 @pytest.mark.parametrize("m,n,k", [(256, 1000, 2048), (120, 1000, 2048), (7, 16, 64), (300, 72, 128)])
 def test_linear(m, n, k):
     g = torch.Generator().manual_seed(0)
