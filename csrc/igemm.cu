@@ -66,6 +66,7 @@ struct alignas(64) FParams {
     const float* bias;
     int ldo;
     int dbg;             // experiment switches (PTD_IGEMM_DBG), 0 in production
+    int stats_smem;      // BN partial sums: 1 = column sums read back from the bf16 staging tile, 0 = register transpose
     // im2col tap table: k-block kb belongs to table entry kb / cblocks; `wtap` is the filter tap (r*S+s) whose
     // weights it multiplies, (off_w, off_h) the unsigned offsets handed to the im2col load.
     int ntaps;
@@ -400,8 +401,16 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
         const int half = warp >> 2;
         // per-chunk BN partial sums, kept in four scalar pairs so the chunk loop need not be unrolled (the unrolled
         // butterfly made the epilogue stall on instruction fetch: ncu stall_no_inst 27 %)
-        float as0 = 0.f, as1 = 0.f, as2 = 0.f, as3 = 0.f, aq0 = 0.f, aq1 = 0.f, aq2 = 0.f, aq3 = 0.f;
+        // BN partial sums: lane (cp = lane & 15, par = lane >> 4) accumulates columns 2cp, 2cp+1 of each of the warp's
+        // 32-column chunks over the rows of parity `par`, read back from the bf16 staging tile (the statistics then
+        // describe exactly the values that were stored).  A cross-lane transpose-reduce of the fp32 registers cost
+        // ~250 instructions per chunk; this is ~110 and needs no shuffles.
+        float4 acc0 = make_float4(0.f, 0.f, 0.f, 0.f), acc1 = acc0, acc2 = acc0, acc3 = acc0;   // (s_lo, s_hi, q_lo, q_hi)
+        // The register transpose-reduce (one column per lane: .x = sum, .z = sum of squares) stays for tiles with a
+        // long K loop: there the epilogue hides under the MMAs either way, and the denser instruction stream of the
+        // shared-memory variant was measured to slow the main loop down by 7-12 % (profiles/README.md).
         const bool do_stats = (EPI == 0) && p.stat_sum != nullptr;
+        const bool stats_smem = p.stats_smem != 0;
         int it = 0;
         for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
             const int acc = it & 1;
@@ -473,18 +482,39 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                             *reinterpret_cast<uint4*>(p.out + off) = o;
                         }
                     }
-                    __syncwarp();
-                    if (do_stats) {
-                        // Rows past M were zero-filled by the producers, so they add nothing.
+                    if (do_stats && !stats_smem) {
                         float sq[32];
 #pragma unroll
                         for (int i = 0; i < 32; ++i) sq[i] = v[i] * v[i];
                         const float cs = transpose_reduce32(v, lane), cq = transpose_reduce32(sq, lane);
-                        as0 += c == 0 ? cs : 0.f; aq0 += c == 0 ? cq : 0.f;
-                        as1 += c == 1 ? cs : 0.f; aq1 += c == 1 ? cq : 0.f;
-                        as2 += c == 2 ? cs : 0.f; aq2 += c == 2 ? cq : 0.f;
-                        as3 += c == 3 ? cs : 0.f; aq3 += c == 3 ? cq : 0.f;
+                        acc0.x += c == 0 ? cs : 0.f; acc0.z += c == 0 ? cq : 0.f;
+                        acc1.x += c == 1 ? cs : 0.f; acc1.z += c == 1 ? cq : 0.f;
+                        acc2.x += c == 2 ? cs : 0.f; acc2.z += c == 2 ? cq : 0.f;
+                        acc3.x += c == 3 ? cs : 0.f; acc3.z += c == 3 ? cq : 0.f;
                     }
+                    if (do_stats && stats_smem) {
+                        // Rows past M were zero-filled by the producers, so they add nothing.
+                        const uint32_t cp = lane & 15, par = lane >> 4;
+                        const uint32_t slot = cp >> 2, word = (cp & 3) << 2;
+                        float s_lo = 0.f, s_hi = 0.f, q_lo = 0.f, q_hi = 0.f;
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) {
+                            // row 2i + par: rows 2i and 2i+1 are 64 B apart -> the two half-warps hit disjoint banks
+                            const uint32_t a = stg + (2 * i + par) * 64 + ((slot ^ (uint32_t)(i & 3)) << 4) + word;
+                            uint32_t w2;
+                            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w2) : "r"(a));
+                            const float2 f = unpack_bf16x2(w2);
+                            s_lo += f.x; s_hi += f.y;
+                            q_lo = fmaf(f.x, f.x, q_lo); q_hi = fmaf(f.y, f.y, q_hi);
+                        }
+                        switch (c) {
+                            case 0: acc0.x += s_lo; acc0.y += s_hi; acc0.z += q_lo; acc0.w += q_hi; break;
+                            case 1: acc1.x += s_lo; acc1.y += s_hi; acc1.z += q_lo; acc1.w += q_hi; break;
+                            case 2: acc2.x += s_lo; acc2.y += s_hi; acc2.z += q_lo; acc2.w += q_hi; break;
+                            default: acc3.x += s_lo; acc3.y += s_hi; acc3.z += q_lo; acc3.w += q_hi; break;
+                        }
+                    }
+                    __syncwarp();
                 } else {
                     if (row_ok) {
                         float* dst = p.out_f32 + (size_t)m * p.ldo + n0 + col;
@@ -500,12 +530,20 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
             mbar_arrive(&bars->tmem_empty[acc]);
         }
         if (do_stats) {
-            const float fs[4] = {as0, as1, as2, as3}, fq[4] = {aq0, aq1, aq2, aq3};
+            const float4 fa[4] = {acc0, acc1, acc2, acc3};
 #pragma unroll
             for (int c = 0; c < Cfg::CHUNKS_PER_WARP; ++c) {
-                const int n = n0 + half * (BLOCK_N / 2) + c * 32 + lane;
-                atomicAdd(p.stat_sum + n, fs[c]);
-                atomicAdd(p.stat_sq + n, fq[c]);
+                const int nb = n0 + half * (BLOCK_N / 2) + c * 32;
+                if (stats_smem) {
+                    const int n = nb + 2 * (int)(lane & 15);
+                    atomicAdd(p.stat_sum + n, fa[c].x);
+                    atomicAdd(p.stat_sum + n + 1, fa[c].y);
+                    atomicAdd(p.stat_sq + n, fa[c].z);
+                    atomicAdd(p.stat_sq + n + 1, fa[c].w);
+                } else {
+                    atomicAdd(p.stat_sum + nb + lane, fa[c].x);
+                    atomicAdd(p.stat_sq + nb + lane, fa[c].z);
+                }
             }
         }
     } else if (!A_TMA) {
@@ -777,6 +815,11 @@ int launch_f(FParams& p, cudaStream_t stream) {
     p.m_blocks = ceil_div_i(p.M, BLOCK_M);
     p.n_blocks = ceil_div_i(p.N, BLOCK_N);
     { const char* e = getenv("PTD_IGEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
+    {   // PTD_STATS_SMEM_KB: largest K loop (in k-blocks) that still uses the shared-memory column sums
+        static int kb_max = -1;
+        if (kb_max < 0) { const char* e = getenv("PTD_STATS_SMEM_KB"); kb_max = e ? atoi(e) : 4; }
+        p.stats_smem = p.num_kb <= kb_max ? 1 : 0;
+    }
     const int tiles = p.m_blocks * p.n_blocks;
     int grid = ptd_num_sms();
     grid = (grid / p.n_blocks) * p.n_blocks;      // fixed n block per CTA (register-resident BN partial sums)
