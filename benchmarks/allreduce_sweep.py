@@ -64,15 +64,22 @@ def main():
         t_ours = timed(lambda: be.all_reduce_avg(ours), iters, dev)
         t_nccl = timed(lambda: dist.all_reduce(ref, op=dist.ReduceOp.AVG), iters, dev)
         ok = bool(torch.allclose(ours.float(), torch.ones_like(ours, dtype=torch.float32)))
+        t_one = None
+        if dtype == torch.float32 and size <= (4 << 20):          # one-shot variant (one NVLink round trip)
+            t_one = timed(lambda: be.all_reduce_oneshot(ours), iters, dev)
+            ok = ok and bool(torch.allclose(ours, torch.ones_like(ours)))
         bus = 2.0 * (world - 1) / world * size
         row = {"bytes": size, "ours_us": round(t_ours, 2), "nccl_us": round(t_nccl, 2),
                "ours_busbw_gbs": round(bus / t_ours / 1e3, 1), "nccl_busbw_gbs": round(bus / t_nccl / 1e3, 1),
                "frac_nvlink_roofline_of_measured": round(bus / t_ours / 1e3 / NVLINK_GBS, 3), "correct": ok}
+        if t_one is not None:
+            row["ours_oneshot_us"] = round(t_one, 2)
         rows.append(row)
         if rank == 0:
             print(f"{size:>11d} B  ours {t_ours:9.1f} us ({row['ours_busbw_gbs']:7.1f} GB/s bus, "
                   f"{row['frac_nvlink_roofline_of_measured']:.2f} of roofline)   nccl {t_nccl:9.1f} us "
-                  f"({row['nccl_busbw_gbs']:7.1f} GB/s)  speedup {t_nccl / t_ours:5.2f}x  ok={ok}", flush=True)
+                  f"({row['nccl_busbw_gbs']:7.1f} GB/s)  speedup {t_nccl / t_ours:5.2f}x  ok={ok}"
+                  + (f"  one-shot {t_one:7.1f} us" if t_one is not None else ""), flush=True)
         del ours, ref
         size *= 4
     if rank == 0 and args.out:

@@ -217,6 +217,96 @@ __global__ void __launch_bounds__(AR_THREADS) broadcast_pull_kernel(PeerPtrs pp,
     seq_end(pp, rank, seq + 1);
 }
 
+// ---- sharded collectives on a symmetric buffer of n16 16-byte vectors ------------------------------------
+// The buffer is cut into `world` shards of per = ceil(n16 / world) vectors; shard s belongs to rank s.
+//   SC_ALL_GATHER     every rank pulls shard s from rank s                   (each shard valid at its owner before)
+//   SC_GATHER         only `root` pulls
+//   SC_SCATTER        rank r pulls shard r out of root's buffer
+//   SC_REDUCE_SCATTER rank r: shard r = scale * sum over ranks of shard r    (fp32; other shards left as they were)
+//   SC_REDUCE         root: whole buffer = scale * sum over ranks            (fp32)
+//   SC_ALLREDUCE_1    one-shot all-reduce for small messages: every rank loads the whole buffer of every rank,
+//                     all ranks meet (nobody may overwrite what a peer has yet to read), then each stores its
+//                     own copy.  One NVLink round trip instead of the two of the two-shot kernel; needs the whole
+//                     message in the grid's registers (n16 <= gridDim.x * AR_THREADS * 4).
+// Every op starts with a barrier (inputs are final everywhere) and ends with one (peers are done reading).
+enum { SC_ALL_GATHER = 0, SC_GATHER = 1, SC_SCATTER = 2, SC_REDUCE_SCATTER = 3, SC_REDUCE = 4, SC_ALLREDUCE_1 = 5 };
+
+__device__ __forceinline__ void pull_range(uint4* dst, const uint4* src, long long begin, long long end) {
+    const long long stride = (long long)gridDim.x * AR_THREADS;
+    long long i = begin + (long long)blockIdx.x * AR_THREADS + threadIdx.x;
+    for (; i + 3 * stride < end; i += 4 * stride) {
+        const uint4 v0 = ld_u4(src + i), v1 = ld_u4(src + i + stride), v2 = ld_u4(src + i + 2 * stride),
+                    v3 = ld_u4(src + i + 3 * stride);
+        dst[i] = v0; dst[i + stride] = v1; dst[i + 2 * stride] = v2; dst[i + 3 * stride] = v3;
+    }
+    for (; i < end; i += stride) dst[i] = ld_u4(src + i);
+}
+
+__device__ __forceinline__ void reduce_range(const PeerPtrs& pp, int rank, int world, long long begin, long long end,
+                                             float scale) {
+    const long long stride = (long long)gridDim.x * AR_THREADS;
+    float4* dst = reinterpret_cast<float4*>(pp.buf[rank]);
+    for (long long i = begin + (long long)blockIdx.x * AR_THREADS + threadIdx.x; i < end; i += stride) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int r = 0; r < world; ++r) {
+            const float4 v = ld_f4(reinterpret_cast<const float4*>(pp.buf[(rank + r) % world]) + i);
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+        acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+        dst[i] = acc;
+    }
+}
+
+__global__ void __launch_bounds__(AR_THREADS) shard_collective_kernel(PeerPtrs pp, int rank, int world, int root, int op,
+                                                                      long long n16, float scale) {
+    const uint32_t seq = seq_begin(pp, rank);
+    rank_barrier(pp, rank, world, seq);
+    const long long per = (n16 + world - 1) / world;
+    uint4* mine = reinterpret_cast<uint4*>(pp.buf[rank]);
+    if (op == SC_ALL_GATHER || (op == SC_GATHER && rank == root)) {
+        for (int k = 1; k < world; ++k) {
+            const int s = (rank + k) % world;
+            pull_range(mine, reinterpret_cast<const uint4*>(pp.buf[s]), min(n16, per * s), min(n16, per * (s + 1)));
+        }
+    } else if (op == SC_SCATTER) {
+        if (rank != root)
+            pull_range(mine, reinterpret_cast<const uint4*>(pp.buf[root]), min(n16, per * rank), min(n16, per * (rank + 1)));
+    } else if (op == SC_REDUCE_SCATTER) {
+        reduce_range(pp, rank, world, min(n16, per * rank), min(n16, per * (rank + 1)), scale);
+    } else if (op == SC_REDUCE) {
+        // the root's own buffer is both an input and the output: element i is read and written by the same thread
+        if (rank == root) reduce_range(pp, rank, world, 0, n16, scale);
+    } else if (op == SC_ALLREDUCE_1) {
+        const long long stride = (long long)gridDim.x * AR_THREADS;
+        const long long i0 = (long long)blockIdx.x * AR_THREADS + threadIdx.x;
+        float4 acc[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            const long long i = i0 + u * stride;
+            if (i < n16) {
+                for (int r = 0; r < world; ++r) {
+                    const float4 v = ld_f4(reinterpret_cast<const float4*>(pp.buf[(rank + r) % world]) + i);
+                    acc[u].x += v.x; acc[u].y += v.y; acc[u].z += v.z; acc[u].w += v.w;
+                }
+            }
+        }
+        rank_barrier(pp, rank, world, seq + 1);         // every rank holds its sums: the inputs may be overwritten
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const long long i = i0 + u * stride;
+            if (i < n16) {
+                acc[u].x *= scale; acc[u].y *= scale; acc[u].z *= scale; acc[u].w *= scale;
+                reinterpret_cast<float4*>(mine)[i] = acc[u];
+            }
+        }
+        seq_end(pp, rank, seq + 1);                     // outputs are local: no closing barrier needed
+        return;
+    }
+    rank_barrier(pp, rank, world, seq + 1);
+    seq_end(pp, rank, seq + 1);
+}
+
 __global__ void __launch_bounds__(AR_THREADS) barrier_only_kernel(PeerPtrs pp, int rank, int world) {
     const uint32_t seq = seq_begin(pp, rank);
     rank_barrier(pp, rank, world, seq);
@@ -389,6 +479,30 @@ extern "C" int ptd_broadcast_inplace(const void* const* bufs, const void* const*
     PTD_REQUIRE(nbytes % 16 == 0, "broadcast: nbytes (%lld) must be a multiple of 16", nbytes);
     const int grid = pick_blocks(nbytes / 16, blocks);
     broadcast_pull_kernel<<<grid, AR_THREADS, 0, (cudaStream_t)stream>>>(pp, rank, world, root, nbytes / 16);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+// op: 0 all-gather, 1 gather (to root), 2 scatter (from root), 3 reduce-scatter, 4 reduce (to root), 5 one-shot
+// all-reduce (ops 3-5: fp32 data, `scale` applied to the sum).  nbytes a multiple of 16; shard s of the buffer
+// (ceil(nbytes/16/world) vectors) belongs to rank s.  See shard_collective_kernel.
+extern "C" int ptd_shard_collective(const void* const* bufs, const void* const* pads, int rank, int world, int root,
+                                    int op, long long nbytes, float scale, int blocks, void* stream) {
+    PeerPtrs pp;
+    int rc = fill_peers(pp, bufs, pads, world);
+    if (rc) return rc;
+    PTD_REQUIRE(nbytes % 16 == 0, "shard_collective: nbytes (%lld) must be a multiple of 16", nbytes);
+    PTD_REQUIRE(op >= SC_ALL_GATHER && op <= SC_ALLREDUCE_1, "shard_collective: unknown op %d", op);
+    PTD_REQUIRE(root >= 0 && root < world, "shard_collective: root %d outside the group", root);
+    const long long n16 = nbytes / 16;
+    int grid = pick_blocks(op == SC_REDUCE || op == SC_ALLREDUCE_1 ? n16 : (n16 + world - 1) / world, blocks);
+    if (op == SC_ALLREDUCE_1) {
+        const long long need = (n16 + AR_THREADS * 4 - 1) / (AR_THREADS * 4);
+        PTD_REQUIRE(need <= MAX_BLOCKS, "one-shot all-reduce: %lld bytes exceed the %d-byte limit (use the two-shot kernel)",
+                    nbytes, MAX_BLOCKS * AR_THREADS * 4 * 16);
+        if (grid < need) grid = (int)need;
+    }
+    shard_collective_kernel<<<grid, AR_THREADS, 0, (cudaStream_t)stream>>>(pp, rank, world, root, op, n16, scale);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }

@@ -183,6 +183,11 @@ int ptd_allreduce_inplace(const void* const* bufs, const void* const* pads, int 
                           int is_bf16, float scale, int blocks, void* stream);
 int ptd_broadcast_inplace(const void* const* bufs, const void* const* pads, int rank, int world, int root,
                           long long nbytes, int blocks, void* stream);
+/* Sharded collectives on a symmetric buffer (shard s = rank s's part): op 0 all-gather, 1 gather to root, 2 scatter
+ * from root, 3 reduce-scatter, 4 reduce to root, 5 one-shot all-reduce for messages up to 4 MiB (3-5: fp32, sum * scale).
+ * NCCL's all_gather / gather / scatter / reduce_scatter / reduce in the reference's stack. */
+int ptd_shard_collective(const void* const* bufs, const void* const* pads, int rank, int world, int root, int op,
+                         long long nbytes, float scale, int blocks, void* stream);
 int ptd_p2p_barrier(const void* const* pads, int rank, int world, void* stream);
 /* single process, several devices: copy / sum over peer pointers from a kernel on the current device */
 int ptd_peer_copy(void* dst, const void* src, long long nbytes, void* stream);

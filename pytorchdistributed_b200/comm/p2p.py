@@ -35,6 +35,8 @@ _lib.register("ptd_p2p_max_blocks", [])
 _lib.register("ptd_allreduce_inplace", [P, P, I, I, L, I, F, I, P])
 _lib.register("ptd_broadcast_inplace", [P, P, I, I, I, L, I, P])
 _lib.register("ptd_p2p_barrier", [P, I, I, P])
+_lib.register("ptd_shard_collective", [P, P, I, I, I, I, L, F, I, P])
+_OPS = {"all_gather": 0, "gather": 1, "scatter": 2, "reduce_scatter": 3, "reduce": 4, "all_reduce_oneshot": 5}
 _lib.register("ptd_peer_copy", [P, P, L, P])
 _lib.register("ptd_reduce_sum_f32", [P, P, I, L, F, I, P])
 _lib.register("ptd_peer_copy_bulk", [P, P, L, I, P])
@@ -163,6 +165,50 @@ class P2PCollectives:
         _lib.call("ptd_allreduce_inplace", ctypes.cast(sb.ptr_array, P), ctypes.cast(self.pads[0].ptr_array, P),
                   self.rank, self.world, n_pad, int(is_bf16), float(1.0 / self.world if scale is None else scale),
                   self.blocks, torch.cuda.current_stream(self.device).cuda_stream)
+
+    # -- sharded collectives (in place on a tensor from alloc(); shard s = rank s's part) ----------------------
+    def shard(self, flat: torch.Tensor, rank: Optional[int] = None) -> torch.Tensor:
+        """The slice of ``flat`` that belongs to ``rank`` (default: this rank) in the sharded collectives:
+        ``ceil(nbytes / 16 / world)`` 16-byte vectors per rank, the last shard may be short or empty."""
+        rank = self.rank if rank is None else rank
+        esz = flat.element_size()
+        n16 = (flat.numel() * esz + 15) // 16
+        per = (n16 + self.world - 1) // self.world * 16 // esz
+        return flat[min(flat.numel(), per * rank):min(flat.numel(), per * (rank + 1))]
+
+    def _sharded(self, op: str, flat: torch.Tensor, root: int = 0, scale: float = 1.0) -> None:
+        sb = self._sym(flat)
+        if op in ("reduce_scatter", "reduce", "all_reduce_oneshot") and flat.dtype != torch.float32:
+            raise RuntimeError(f"{op}: fp32 only (got {flat.dtype})")
+        nbytes = (flat.numel() * flat.element_size() + 15) // 16 * 16      # buffers are padded to 256 B
+        _lib.call("ptd_shard_collective", ctypes.cast(sb.ptr_array, P), ctypes.cast(self.pads[1].ptr_array, P),
+                  self.rank, self.world, root, _OPS[op], nbytes, float(scale), self.blocks,
+                  torch.cuda.current_stream(self.device).cuda_stream)
+
+    def all_gather(self, flat: torch.Tensor) -> None:
+        """Every rank wrote ``shard(flat)``; afterwards every rank holds all shards (dist.all_gather_into_tensor)."""
+        self._sharded("all_gather", flat)
+
+    def gather(self, flat: torch.Tensor, dst: int = 0) -> None:
+        """Like :meth:`all_gather`, but only ``dst`` ends up with all shards (dist.gather)."""
+        self._sharded("gather", flat, dst)
+
+    def scatter(self, flat: torch.Tensor, src: int = 0) -> None:
+        """Rank r receives ``shard(flat, r)`` of ``src``'s tensor into the same slice of its own (dist.scatter)."""
+        self._sharded("scatter", flat, src)
+
+    def reduce_scatter(self, flat: torch.Tensor, scale: float = 1.0) -> None:
+        """``shard(flat)`` becomes ``scale *`` the sum over ranks of that slice (dist.reduce_scatter_tensor);
+        the rest of ``flat`` keeps this rank's own contribution."""
+        self._sharded("reduce_scatter", flat, 0, scale)
+
+    def reduce(self, flat: torch.Tensor, dst: int = 0, scale: float = 1.0) -> None:
+        """``dst``'s tensor becomes ``scale *`` the sum over ranks (dist.reduce); the others keep theirs."""
+        self._sharded("reduce", flat, dst, scale)
+
+    def all_reduce_oneshot(self, flat: torch.Tensor, scale: Optional[float] = None) -> None:
+        """All-reduce for small fp32 messages (<= 4 MiB): one NVLink round trip instead of two."""
+        self._sharded("all_reduce_oneshot", flat, 0, 1.0 / self.world if scale is None else scale)
 
     def broadcast(self, flat: torch.Tensor, src: int = 0) -> None:
         sb = self._by_ptr.get(flat.data_ptr())

@@ -60,6 +60,88 @@ def test_p2p_collectives_match_nccl(world):
         assert not bad, bad
 
 
+def _sharded(rank, world):
+    import torch
+    import torch.distributed as dist
+    from pytorchdistributed_b200.comm.p2p import P2PCollectives
+    dev = torch.device("cuda", rank)
+    be = P2PCollectives(None, dev)
+    out = {}
+    for n in (8, 1001, 65536 + 20, 3 * 1024 * 1024 + 4):
+        def fresh(seed_rank=rank):
+            g = torch.Generator(device="cpu").manual_seed(1000 * seed_rank + n)
+            return torch.randint(-8, 9, (n,), generator=g).float().to(dev)       # exact sums in any order
+        every = [fresh(r) for r in range(world)]
+        total = torch.stack(every).sum(0)
+        flat = be.alloc(n, torch.float32, dev)
+        sl = [be.shard(flat, r) for r in range(world)]
+        lo = [s_.storage_offset() - flat.storage_offset() for s_ in sl]
+        out[(n, "shards_cover")] = sum(s_.numel() for s_ in sl) == n
+        # all_gather: every rank contributes its own shard of rank-specific data
+        flat.fill_(-1.0)
+        be.shard(flat).copy_(every[rank][lo[rank]:lo[rank] + sl[rank].numel()])
+        be.all_gather(flat)
+        exp = torch.cat([every[r][lo[r]:lo[r] + sl[r].numel()] for r in range(world)])
+        torch.cuda.synchronize()
+        out[(n, "all_gather")] = bool(torch.equal(flat, exp))
+        # gather to the last rank
+        flat.fill_(-1.0)
+        be.shard(flat).copy_(every[rank][lo[rank]:lo[rank] + sl[rank].numel()])
+        be.gather(flat, dst=world - 1)
+        torch.cuda.synchronize()
+        if rank == world - 1:
+            out[(n, "gather")] = bool(torch.equal(flat, exp))
+        else:
+            out[(n, "gather")] = bool((flat[:lo[rank]] == -1).all())
+        # scatter from rank 0
+        flat.copy_(every[rank])
+        be.scatter(flat, src=0)
+        torch.cuda.synchronize()
+        out[(n, "scatter")] = bool(torch.equal(be.shard(flat), every[0][lo[rank]:lo[rank] + sl[rank].numel()]))
+        # reduce_scatter
+        flat.copy_(every[rank])
+        be.reduce_scatter(flat)
+        torch.cuda.synchronize()
+        out[(n, "reduce_scatter")] = bool(torch.equal(be.shard(flat), total[lo[rank]:lo[rank] + sl[rank].numel()]))
+        # reduce to rank 0
+        flat.copy_(every[rank])
+        be.reduce(flat, dst=0)
+        torch.cuda.synchronize()
+        out[(n, "reduce")] = bool(torch.equal(flat, total if rank == 0 else every[rank]))
+        # one-shot all-reduce against NCCL
+        flat.copy_(every[rank])
+        if n * 4 <= (4 << 20):
+            ref = every[rank].clone()
+            dist.all_reduce(ref)
+            be.all_reduce_oneshot(flat, scale=1.0)
+            torch.cuda.synchronize()
+            out[(n, "oneshot")] = bool(torch.equal(flat, ref))
+        else:                                   # larger than the grid's registers: refused, not truncated
+            try:
+                be.all_reduce_oneshot(flat, scale=1.0)
+                out[(n, "oneshot_refused")] = False
+            except RuntimeError:
+                out[(n, "oneshot_refused")] = True
+    # reduce_scatter followed by all_gather == all-reduce, back to back without host syncs
+    flat = be.alloc(1 << 18, torch.float32, dev)
+    for it in range(10):
+        flat.fill_(float(rank + it))
+        be.reduce_scatter(flat, scale=1.0 / world)
+        be.all_gather(flat)
+    torch.cuda.synchronize()
+    out["rs_ag"] = bool(torch.allclose(flat, torch.full_like(flat, sum(r + 9 for r in range(world)) / world)))
+    be.close()
+    return out
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_p2p_sharded_collectives(world):
+    _need(world)
+    for res in run_ranks(_sharded, world, backend="nccl"):
+        bad = [k for k, v in res.items() if not v]
+        assert not bad, bad
+
+
 def _ddp(rank, world, comm):
     import torch
     import torch.nn.functional as F
