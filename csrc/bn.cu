@@ -313,6 +313,193 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dz, const void* __restrict__ zm, co
     }
 }
 
+// =================================================================================================
+// BatchNorm + ReLU + 3x3/2 max-pool in one pass each way (the ResNet stem's tail)
+// =================================================================================================
+// Forward: p = maxpool(relu(bn(y))) straight from the convolution output; the 112x112 activation between BN and
+// the pool is never written (or read back by the pool, or by the BN backward).  idx keeps the winning tap per
+// element (0..8, first maximum in scan order as torch does), or POOL_DEAD when the maximum is <= 0: the ReLU then
+// blocks the gradient, so the backward needs no separate ReLU mask.
+// Backward: the gradient that reaches BN output pixel (h, w) is the sum of dp over the (at most four) windows whose
+// arg-max is (h, w); it is rebuilt on the fly in both BN backward passes from dp and idx (4x smaller than the
+// activation) instead of being materialised by a pooling backward kernel.
+constexpr unsigned POOL_DEAD = 15u;
+
+__global__ void __launch_bounds__(BN_THREADS)
+bn_relu_pool_fwd_kernel(const bf16* __restrict__ y, bf16* __restrict__ p, uint8_t* __restrict__ idx,
+                        const float* __restrict__ sum, const float* __restrict__ sq, const float* __restrict__ gamma,
+                        const float* __restrict__ beta, float* __restrict__ running_mean, float* __restrict__ running_var,
+                        float* __restrict__ save_mean, float* __restrict__ save_invstd, int N, int H, int W, int C,
+                        float eps, float momentum) {
+    const int cg = C >> 3;
+    const int g = threadIdx.x % cg;
+    const int OH = H >> 1, OW = W >> 1;
+    const long long M = (long long)N * H * W;
+    float scale[8], shift[8];
+    const float inv_m = 1.f / (float)M;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = g * 8 + i;
+        const float mean = sum[c] * inv_m;
+        const float var = fmaxf(sq[c] * inv_m - mean * mean, 0.f);
+        const float invstd = rsqrtf(var + eps);
+        scale[i] = gamma[c] * invstd;
+        shift[i] = beta[c] - mean * scale[i];
+        if (blockIdx.x == 0 && threadIdx.x < cg) {
+            save_mean[c] = mean;
+            save_invstd[c] = invstd;
+            if (running_mean != nullptr) {
+                const float unbiased = M > 1 ? var * ((float)M / (float)(M - 1)) : var;
+                running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+                running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+            }
+        }
+    }
+    const int pix_per_iter = BN_THREADS / cg;
+    const long long total = (long long)N * OH * OW;
+    for (long long pix = (long long)blockIdx.x * pix_per_iter + threadIdx.x / cg; pix < total;
+         pix += (long long)gridDim.x * pix_per_iter) {
+        const int ow = (int)(pix % OW);
+        const long long t2 = pix / OW;
+        const int oh = (int)(t2 % OH);
+        const long long n = t2 / OH;
+        // all nine taps are loaded up front (clamped coordinates), validity is applied afterwards
+        uint4 raw[9];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            const int hi = min(max(oh * 2 - 1 + r, 0), H - 1);
+#pragma unroll
+            for (int s_ = 0; s_ < 3; ++s_) {
+                const int wi = min(max(ow * 2 - 1 + s_, 0), W - 1);
+                raw[r * 3 + s_] = *reinterpret_cast<const uint4*>(y + ((size_t)(n * H + hi) * W + wi) * C + g * 8);
+            }
+        }
+        float best[8];
+        unsigned bi[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { best[i] = 0.f; bi[i] = POOL_DEAD; }      // relu floor: only a tap > 0 can win
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            const bool hv = (oh * 2 - 1 + r) >= 0;          // H, W even: the window never runs past the far edge
+#pragma unroll
+            for (int s_ = 0; s_ < 3; ++s_) {
+                const bool ok = hv && (ow * 2 - 1 + s_) >= 0;
+                float f[8];
+                unpack8(raw[r * 3 + s_], f);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const float v = fmaf(f[i], scale[i], shift[i]);
+                    if (ok && v > best[i]) { best[i] = v; bi[i] = r * 3 + s_; }
+                }
+            }
+        }
+        const size_t off = (size_t)pix * C + g * 8;
+        *reinterpret_cast<uint4*>(p + off) = pack8(best);
+        uint2 packed;
+        packed.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24);
+        packed.y = bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24);
+        *reinterpret_cast<uint2*>(idx + off) = packed;
+    }
+}
+
+// Gradient reaching the four BN-output pixels of the 2x2 block (2a.., 2b..) from the (up to) four windows that
+// cover it: window (a, b) owns taps (1,1) (1,2) (2,1) (2,2) of the block, (a, b+1) taps (1,0) (2,0), (a+1, b) taps
+// (0,1) (0,2), (a+1, b+1) tap (0,0).  gq[q][i]: q = 2 * (row in block) + (col in block).
+__device__ __forceinline__ void pool_block_grad(const bf16* __restrict__ dp, const uint8_t* __restrict__ idx, long long n,
+                                                int a, int b, int OH, int OW, int C, int g, float (&gq)[4][8]) {
+    const int a1 = min(a + 1, OH - 1), b1 = min(b + 1, OW - 1);
+    const bool va = a + 1 < OH, vb = b + 1 < OW;
+    const size_t o00 = ((size_t)(n * OH + a) * OW + b) * C + g * 8, o01 = ((size_t)(n * OH + a) * OW + b1) * C + g * 8;
+    const size_t o10 = ((size_t)(n * OH + a1) * OW + b) * C + g * 8, o11 = ((size_t)(n * OH + a1) * OW + b1) * C + g * 8;
+    const uint2 i00 = *reinterpret_cast<const uint2*>(idx + o00), i01 = *reinterpret_cast<const uint2*>(idx + o01);
+    const uint2 i10 = *reinterpret_cast<const uint2*>(idx + o10), i11 = *reinterpret_cast<const uint2*>(idx + o11);
+    const uint4 r00 = *reinterpret_cast<const uint4*>(dp + o00), r01 = *reinterpret_cast<const uint4*>(dp + o01);
+    const uint4 r10 = *reinterpret_cast<const uint4*>(dp + o10), r11 = *reinterpret_cast<const uint4*>(dp + o11);
+    float d00[8], d01[8], d10[8], d11[8];
+    unpack8(r00, d00); unpack8(r01, d01); unpack8(r10, d10); unpack8(r11, d11);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int sh = (i & 3) * 8;
+        const unsigned t00 = ((i < 4 ? i00.x : i00.y) >> sh) & 0xffu;
+        const unsigned t01 = vb ? ((i < 4 ? i01.x : i01.y) >> sh) & 0xffu : POOL_DEAD;
+        const unsigned t10 = va ? ((i < 4 ? i10.x : i10.y) >> sh) & 0xffu : POOL_DEAD;
+        const unsigned t11 = (va && vb) ? ((i < 4 ? i11.x : i11.y) >> sh) & 0xffu : POOL_DEAD;
+        gq[0][i] = (t00 == 4u ? d00[i] : 0.f);
+        gq[1][i] = (t00 == 5u ? d00[i] : 0.f) + (t01 == 3u ? d01[i] : 0.f);
+        gq[2][i] = (t00 == 7u ? d00[i] : 0.f) + (t10 == 1u ? d10[i] : 0.f);
+        gq[3][i] = (t00 == 8u ? d00[i] : 0.f) + (t01 == 6u ? d01[i] : 0.f) + (t10 == 2u ? d10[i] : 0.f) +
+                   (t11 == 0u ? d11[i] : 0.f);
+    }
+}
+
+// PASS 0: sum_g += g, sum_gx += g * xhat.   PASS 1: dy = k * g + a0 + a1 * y (see bn_bwd_apply_kernel).
+template <int PASS>
+__global__ void __launch_bounds__(BN_THREADS, 2)
+bn_relu_pool_bwd_kernel(const bf16* __restrict__ dp, const uint8_t* __restrict__ idx, const bf16* __restrict__ y,
+                        const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                        float* __restrict__ sum_g, float* __restrict__ sum_gx, bf16* __restrict__ dy, int N, int H, int W,
+                        int C) {
+    const int cg = C >> 3;
+    const int g = threadIdx.x % cg;
+    const int OH = H >> 1, OW = W >> 1;
+    float c0[8], c1[8], c2[8];          // PASS 0: mu, sum, sumx.  PASS 1: k, a0, a1
+    const float inv_m = 1.f / ((float)N * H * W);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = g * 8 + i;
+        if (PASS == 0) {
+            c0[i] = mean[c]; c1[i] = 0.f; c2[i] = 0.f;
+        } else {
+            const float is = invstd[c], mu = mean[c];
+            c0[i] = gamma[c] * is;
+            const float t = c0[i] * sum_gx[c] * inv_m * is;
+            c2[i] = -t;
+            c1[i] = fmaf(t, mu, -c0[i] * sum_g[c] * inv_m);
+        }
+    }
+    const int blk_per_iter = BN_THREADS / cg;
+    const long long total = (long long)N * OH * OW;          // 2x2 blocks of BN-output pixels
+    for (long long blk = (long long)blockIdx.x * blk_per_iter + threadIdx.x / cg; blk < total;
+         blk += (long long)gridDim.x * blk_per_iter) {
+        const int b = (int)(blk % OW);
+        const long long t2 = blk / OW;
+        const int a = (int)(t2 % OH);
+        const long long n = t2 / OH;
+        size_t yo[4];
+        uint4 ry[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            yo[q] = ((size_t)(n * H + 2 * a + (q >> 1)) * W + 2 * b + (q & 1)) * C + g * 8;
+            ry[q] = *reinterpret_cast<const uint4*>(y + yo[q]);
+        }
+        float gq[4][8];
+        pool_block_grad(dp, idx, n, a, b, OH, OW, C, g, gq);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            float x[8];
+            unpack8(ry[q], x);
+            if (PASS == 0) {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    c1[i] += gq[q][i];
+                    c2[i] = fmaf(gq[q][i], x[i] - c0[i], c2[i]);
+                }
+            } else {
+                float o[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) o[i] = fmaf(c0[i], gq[q][i], fmaf(c2[i], x[i], c1[i]));
+                *reinterpret_cast<uint4*>(dy + yo[q]) = pack8(o);
+            }
+        }
+    }
+    if (PASS == 0) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) c2[i] *= invstd[g * 8 + i];
+        extern __shared__ float sh_red[];
+        block_channel_reduce(c1, c2, cg, g, sum_g, sum_gx, sh_red);
+    }
+}
+
 // `per_sm` = blocks of the kernel that are resident per SM (its launch bound): large tensors get exactly one wave
 // of grid-striding blocks.
 int bn_grid(long long M, int C, int per_sm = 8) {
@@ -416,6 +603,39 @@ extern "C" int ptd_bn_bwd_apply(const void* dz, const void* z, const void* y, co
     else if (g_out) PTD_BWD(0, true);
     else PTD_BWD(0, false);
 #undef PTD_BWD
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+// p[N,H/2,W/2,C] = maxpool3x3s2p1(relu(bn(y[N,H,W,C]))), idx = winning tap per element (u8, 15 = gradient blocked).
+extern "C" int ptd_bn_relu_maxpool_fwd(const void* y, void* p, void* idx, const float* sum, const float* sq,
+                                       const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                       float* save_mean, float* save_invstd, int N, int H, int W, int C, float eps,
+                                       float momentum, void* stream) {
+    PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
+    PTD_REQUIRE(H % 2 == 0 && W % 2 == 0, "bn_relu_maxpool: H (%d) and W (%d) must be even", H, W);
+    const int grid = bn_grid((long long)N * (H / 2) * (W / 2), C, 4);
+    bn_relu_pool_fwd_kernel<<<grid, BN_THREADS, 0, (cudaStream_t)stream>>>(
+        (const bf16*)y, (bf16*)p, (uint8_t*)idx, sum, sq, gamma, beta, running_mean, running_var, save_mean, save_invstd,
+        N, H, W, C, eps, momentum);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+// dy[N,H,W,C] = gradient w.r.t. the convolution output y, from dp[N,H/2,W/2,C]; sums (2*C floats, zeroed by the
+// caller) receive [dbeta | dgamma].
+extern "C" int ptd_bn_relu_maxpool_bwd(const void* dp, const void* idx, const void* y, const float* mean,
+                                       const float* invstd, const float* gamma, float* sums, void* dy, int N, int H,
+                                       int W, int C, void* stream) {
+    PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
+    PTD_REQUIRE(H % 2 == 0 && W % 2 == 0, "bn_relu_maxpool: H (%d) and W (%d) must be even", H, W);
+    const int grid = bn_grid((long long)N * (H / 2) * (W / 2), C, 2);
+    cudaStream_t st = (cudaStream_t)stream;
+    bn_relu_pool_bwd_kernel<0><<<grid, BN_THREADS, 2 * C * sizeof(float), st>>>(
+        (const bf16*)dp, (const uint8_t*)idx, (const bf16*)y, mean, invstd, gamma, sums, sums + C, nullptr, N, H, W, C);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    bn_relu_pool_bwd_kernel<1><<<grid, BN_THREADS, 0, st>>>(
+        (const bf16*)dp, (const uint8_t*)idx, (const bf16*)y, mean, invstd, gamma, sums, sums + C, (bf16*)dy, N, H, W, C);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }

@@ -116,6 +116,14 @@ int ptd_bn_bwd_reduce(const void* dz, const void* z, const void* y, const float*
 int ptd_bn_bwd_apply(const void* dz, const void* z, const void* y, const float* mean, const float* invstd,
                      const float* gamma, const float* sum_g, const float* sum_gx, void* dy, void* g_out, long long M,
                      int C, int relu, void* stream);
+/* BN + ReLU + 3x3/2 max-pool (pad 1) fused: the ResNet stem tail (bn1, relu, maxpool of torchvision ResNet).  H, W even.
+ * idx: u8 per pooled element, the winning tap 0..8 or 15 when the ReLU blocks the gradient.  The backward rebuilds the
+ * pooled gradient on the fly in both BN passes; sums = [dbeta | dgamma], 2*C floats zeroed by the caller. */
+int ptd_bn_relu_maxpool_fwd(const void* y, void* p, void* idx, const float* sum, const float* sq, const float* gamma,
+                            const float* beta, float* running_mean, float* running_var, float* save_mean,
+                            float* save_invstd, int N, int H, int W, int C, float eps, float momentum, void* stream);
+int ptd_bn_relu_maxpool_bwd(const void* dp, const void* idx, const void* y, const float* mean, const float* invstd,
+                            const float* gamma, float* sums, void* dy, int N, int H, int W, int C, void* stream);
 /* BatchNorm backward (both passes) for callers that must not allocate: the 2*C-float scratch lives in a fixed array
  * inside the library image instead of being passed in.  C <= 2048 (16 KiB per GPU), larger C is rejected.  The first
  * call on a device looks up the array's address - make it before any stream capture on that device.  All calls share

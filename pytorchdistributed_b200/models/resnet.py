@@ -14,6 +14,8 @@ from __future__ import annotations
 
 from typing import List, Optional, Sequence
 
+import os
+
 import torch
 from torch import nn
 
@@ -64,8 +66,24 @@ class Bottleneck(nn.Module):
         return conv_bn_act(out, self.conv3, self.bn3, relu=True, residual=identity)
 
 
+def stem_pool(conv: Conv2d, bn: BatchNorm2d, pool: nn.Module, x: torch.Tensor) -> torch.Tensor:
+    """conv1 -> bn1 -> relu -> maxpool.  Training on a GPU with a conv output of even height and width runs the
+    BN/ReLU/pool part as one fused kernel each way (``ops.functional.stem_bn_relu_pool``)."""
+    if x.is_cuda:
+        fuse = (bn.training and conv.is_stem and x.shape[2] % 4 == 0 and x.shape[3] % 4 == 0
+                and os.environ.get("PTDB200_STEM_POOL_FUSE", "1") != "0")
+        xin = F_.stem_input(x)
+        if fuse:
+            with torch.no_grad():
+                bn.num_batches_tracked += 1
+            return F_.stem_bn_relu_pool(xin, conv.weight, conv.shadow(), bn.weight, bn.bias, bn.running_mean,
+                                        bn.running_var, bn.eps, bn.momentum)
+        x = xin
+    return pool(conv_bn_act(x, conv, bn, relu=True))
+
+
 class Stem(nn.Module):
-    """conv1 + bn1 + relu as one fused node (used by ``stage_modules``; shares the parent's parameters)."""
+    """conv1 + bn1 + relu as one fused node (shares the parent's parameters)."""
 
     def __init__(self, conv: Conv2d, bn: BatchNorm2d) -> None:
         super().__init__()
@@ -75,6 +93,17 @@ class Stem(nn.Module):
         if x.is_cuda:
             x = F_.stem_input(x)
         return conv_bn_act(x, self.conv, self.bn, relu=True)
+
+
+class StemPool(nn.Module):
+    """conv1 + bn1 + relu + maxpool (used by ``stage_modules``; shares the parent's parameters)."""
+
+    def __init__(self, conv: Conv2d, bn: BatchNorm2d, pool: nn.Module) -> None:
+        super().__init__()
+        self.conv, self.bn, self.pool = conv, bn, pool
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return stem_pool(self.conv, self.bn, self.pool, x)
 
 
 class ResNet(nn.Module):
@@ -115,7 +144,7 @@ class ResNet(nn.Module):
         return conv_bn_act(x, self.conv1, self.bn1, relu=True)
 
     def features(self, x: torch.Tensor) -> torch.Tensor:
-        x = self.maxpool(self.stem(x))
+        x = stem_pool(self.conv1, self.bn1, self.maxpool, x)
         x = self.layer1(x)
         x = self.layer2(x)
         x = self.layer3(x)
@@ -129,7 +158,7 @@ class ResNet(nn.Module):
     def stage_modules(self):
         """The reference's 2-stage split (notebook 03 cell5): ``seq1`` = stem..layer2, ``seq2`` =
         layer3..avgpool; ``fc`` stays separate.  The Sequentials share this model's parameters."""
-        seq1 = nn.Sequential(Stem(self.conv1, self.bn1), self.maxpool, self.layer1, self.layer2)
+        seq1 = nn.Sequential(StemPool(self.conv1, self.bn1, self.maxpool), self.layer1, self.layer2)
         seq2 = nn.Sequential(self.layer3, self.layer4, self.avgpool)
         return seq1, seq2, self.fc
 

@@ -307,6 +307,41 @@ def stem_wgrad_raw(xin: torch.Tensor, dy: torch.Tensor, w_shape) -> torch.Tensor
     return dw
 
 
+class _StemBnReluPool(torch.autograd.Function):
+    """stem conv (7x7/2) -> BN (batch stats) -> ReLU -> maxpool 3x3/2 with the BN/ReLU/pool part in ONE kernel
+    forward (``ptd_bn_relu_maxpool_fwd``) and two backward (``ptd_bn_relu_maxpool_bwd``): the 112x112 post-BN
+    activation and its gradient are never materialised.  ``xin`` comes from :func:`stem_input`."""
+
+    @staticmethod
+    def forward(ctx, xin, weight, wp, gamma, beta, running_mean, running_var, eps, momentum):
+        y, stats = stem_fprop_raw(xin, wp)
+        n, c, h, w = y.shape
+        p = _empty_act(n, c, h // 2, w // 2, y.device)
+        idx = torch.empty((n, h // 2, w // 2, c), device=y.device, dtype=torch.uint8)
+        saved = torch.empty((2, c), device=y.device, dtype=torch.float32)
+        _lib.call("ptd_bn_relu_maxpool_fwd", y, p, idx, stats[0], stats[1], gamma, beta, running_mean, running_var,
+                  saved[0], saved[1], n, h, w, c, float(eps), float(momentum), _stream())
+        ctx.save_for_backward(xin, y, idx, saved, gamma)
+        ctx.w_shape = tuple(weight.shape)
+        return p
+
+    @staticmethod
+    def backward(ctx, dp):
+        xin, y, idx, saved, gamma = ctx.saved_tensors
+        dp = as_nhwc_bf16(dp)
+        n, c, h, w = y.shape
+        sums = torch.zeros((2, c), device=y.device, dtype=torch.float32)        # [dbeta | dgamma]
+        dy = torch.empty_like(y, memory_format=CL)
+        _lib.call("ptd_bn_relu_maxpool_bwd", dp, idx, y, saved[0], saved[1], gamma, sums, dy, n, h, w, c, _stream())
+        dw = stem_wgrad_raw(xin, dy, ctx.w_shape) if ctx.needs_input_grad[1] else None
+        return None, dw, None, sums[1], sums[0], None, None, None, None
+
+
+def stem_bn_relu_pool(xin, weight, wp, gamma, beta, running_mean, running_var, eps=1e-5, momentum=0.1):
+    """Training-mode stem + BN + ReLU + maxpool on a CUDA stem input whose conv output has even height and width."""
+    return _StemBnReluPool.apply(xin, weight, wp, gamma, beta, running_mean, running_var, eps, momentum)
+
+
 # ------------------------------------------------------------------------------------------------
 # pooling
 # ------------------------------------------------------------------------------------------------

@@ -141,6 +141,75 @@ def test_stem_space_to_depth(n, h, w):
     assert _rel(dw, refw) < 1e-2
 
 
+@pytest.mark.parametrize("n,c,h,w", [(3, 64, 16, 24), (2, 128, 8, 8)])
+def test_bn_relu_maxpool_fused_kernels(n, c, h, w):
+    """BN + ReLU + maxpool(3,2,1) in one kernel each way.  The forward is compared with torch; the backward with
+    torch's BN backward fed the pooled gradient routed through the kernel's OWN arg-max choice (a max-pool is
+    discontinuous: comparing two pipelines that round differently measures arg-max flips, not the kernel)."""
+    y = _act(n, c, h, w, scale=2.0)
+    gamma, beta = torch.rand(c, device=DEV) + 0.5, torch.randn(c, device=DEV) * 0.3
+    stats = K.bn_stats_raw(y)
+    pz = torch.empty(n, c, h // 2, w // 2, device=DEV, dtype=torch.bfloat16).contiguous(memory_format=CL)
+    idx = torch.empty(n, h // 2, w // 2, c, device=DEV, dtype=torch.uint8)
+    saved = torch.empty(2, c, device=DEV)
+    _lib.call("ptd_bn_relu_maxpool_fwd", y, pz, idx, stats[0], stats[1], gamma, beta, None, None, saved[0], saved[1],
+              n, h, w, c, 1e-5, 0.1, K._stream())
+    yf = y.float().requires_grad_()
+    g2, b2 = gamma.clone().requires_grad_(), beta.clone().requires_grad_()
+    ybn = F.batch_norm(yf, None, None, g2, b2, True, 0.1, 1e-5)
+    pr, ir = F.max_pool2d(F.relu(ybn), 3, 2, 1, return_indices=True)
+    assert _rel(pz, pr) < 1e-2
+    # arg-max: same input pixel as torch wherever the pooled value is clearly positive
+    oh = torch.arange(h // 2, device=DEV).view(1, -1, 1, 1)
+    ow = torch.arange(w // 2, device=DEV).view(1, 1, -1, 1)
+    tap = idx.long()
+    ih, iw = 2 * oh - 1 + tap // 3, 2 * ow - 1 + tap % 3
+    live = tap < 9
+    assert (tap[~live] == 15).all()
+    flat_ours = (ih * w + iw).permute(0, 3, 1, 2)
+    clear = (pr > 1e-2) & live.permute(0, 3, 1, 2)
+    assert (flat_ours[clear] == ir[clear]).float().mean() > 0.995
+    assert ((pr <= 0) == (~live).permute(0, 3, 1, 2))[(pr.abs() > 1e-2) | (pr == 0)].all()
+    # backward
+    dp = _act(n, c, h // 2, w // 2, seed=3)
+    sums = torch.zeros(2, c, device=DEV)
+    dy = torch.empty_like(y)
+    _lib.call("ptd_bn_relu_maxpool_bwd", dp, idx, y, saved[0], saved[1], gamma, sums, dy, n, h, w, c, K._stream())
+    g = torch.zeros(n, h, w, c, device=DEV)
+    nn_ = torch.arange(n, device=DEV).view(-1, 1, 1, 1).expand_as(tap)
+    cc = torch.arange(c, device=DEV).view(1, 1, 1, -1).expand_as(tap)
+    dpn = dp.float().permute(0, 2, 3, 1)
+    g.index_put_((nn_[live], ih.expand_as(tap)[live], iw.expand_as(tap)[live], cc[live]), dpn[live], accumulate=True)
+    ybn.backward(g.permute(0, 3, 1, 2))
+    assert _rel(dy, yf.grad) < 2e-2
+    assert _rel(sums[1], g2.grad) < 2e-2 and _rel(sums[0], b2.grad) < 2e-2
+
+
+def test_stem_bn_relu_maxpool_node_matches_unfused_nodes():
+    """The fused autograd node against conv+BN+ReLU node -> pooling node (same kernels around it)."""
+    n, h, w = 4, 64, 64
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(n, 3, h, w, generator=g).to(DEV)
+    wt = (torch.randn(64, 3, 7, 7, generator=g) * 0.1).to(DEV).contiguous(memory_format=CL).requires_grad_()
+    gamma = (torch.rand(64, device=DEV) + 0.5).requires_grad_()
+    beta = (torch.randn(64, device=DEV) * 0.3).requires_grad_()
+    rm, rv = torch.zeros(64, device=DEV), torch.ones(64, device=DEV)
+    rm2, rv2 = rm.clone(), rv.clone()
+    p = K.stem_bn_relu_pool(K.stem_input(x), wt, K.stem_pack(wt.detach()), gamma, beta, rm, rv, 1e-5, 0.1)
+    wt2 = wt.detach().clone().requires_grad_()
+    g3, b3 = gamma.detach().clone().requires_grad_(), beta.detach().clone().requires_grad_()
+    z = K.conv_bn_act(K.stem_input(x), wt2, K.stem_pack(wt2.detach()), g3, b3, rm2, rv2, None, 2, 3, 1e-5, 0.1, True, True)
+    p2 = K.max_pool_3x3_s2(z)
+    assert _rel(p, p2) < 5e-3
+    assert _rel(rm, rm2) < 1e-4 and _rel(rv, rv2) < 1e-4
+    dp = _act(n, 64, h // 4, w // 4, seed=3)
+    p.backward(dp)
+    p2.backward(dp)
+    # the unfused path pools bf16-rounded activations, so a few near-tie windows pick another tap
+    assert _rel(wt.grad, wt2.grad) < 0.2
+    assert _rel(gamma.grad, g3.grad) < 5e-2 and _rel(beta.grad, b3.grad) < 5e-2
+
+
 @pytest.mark.parametrize("m,n,k", [(256, 1000, 2048), (120, 1000, 2048), (7, 16, 64), (300, 72, 128)])
 def test_linear(m, n, k):
     g = torch.Generator().manual_seed(0)
