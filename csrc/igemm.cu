@@ -32,6 +32,9 @@ constexpr int BLOCK_K = 64;              // 64 bf16 = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
 constexpr int A_TILE_BYTES = BLOCK_M * BLOCK_K * 2;   // 16 KiB
 constexpr int SUB_TILE_BYTES = 64 * 64 * 2;           // 8 KiB : [64 rows][64 elems] swizzled image
+#ifndef PTD_EPI_WARPS_WIDE
+#define PTD_EPI_WARPS_WIDE 16
+#endif
 constexpr int NUM_EPI_WARPS = 8;
 constexpr int TMA_WARP = 8;
 constexpr int MMA_WARP = 9;
@@ -222,11 +225,20 @@ struct FCfg {
     static constexpr int B_TILE_BYTES = BLOCK_N * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
     static constexpr int STAGES = (BLOCK_N == 256) ? 4 : (BLOCK_N == 128 ? 6 : 8);
+    // Epilogue warps: a warp may only read TMEM lanes 32 * (warp % 4) .. + 31, so warps come in groups of four and
+    // each group takes a column range.  Wide tiles use four groups: the epilogue of a memory-bound layer is a chain
+    // of long-latency steps per warp (tcgen05.ld, staging, stores) and gains from more warps in flight.
+    static constexpr int EPI_WARPS = (BLOCK_N >= 128 && EPI == 0) ? PTD_EPI_WARPS_WIDE : 8;
+    static constexpr int EPI_GROUPS = EPI_WARPS / 4;
+    static constexpr int TMA_WARP = EPI_WARPS;
+    static constexpr int MMA_WARP = EPI_WARPS + 1;
+    static constexpr int GATHER_WARP0 = EPI_WARPS + 2;
     static constexpr int THREADS = A_MODE != AM_GATHER ? (MMA_WARP + 1) * 32 : (GATHER_WARP0 + 4) * 32;
     static constexpr int TMEM_COLS = 2 * BLOCK_N;
     static constexpr int STAGING_OFF = STAGES * STAGE_BYTES + 1024;        // barriers live in the 1 KiB before it
-    static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGING_OFF + NUM_EPI_WARPS * 2048;
-    static constexpr int CHUNKS_PER_WARP = BLOCK_N / 64;   // 32-column chunks per epilogue warp
+    static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGING_OFF + EPI_WARPS * 2048;
+    static constexpr int COLS_PER_GROUP = BLOCK_N / EPI_GROUPS;
+    static constexpr int CHUNKS_PER_WARP = COLS_PER_GROUP / 32;   // 32-column chunks per epilogue warp
 };
 
 // Gather-producer loop of igemm_f (128 threads).  conv: thread owns the 16-byte column (tid & 7) of rows
@@ -241,7 +253,7 @@ __device__ __forceinline__ void f_gather_loop(const FParams& p, Barriers<Cfg::ST
     constexpr int STAGES = Cfg::STAGES;
     constexpr int NR = STEM ? 16 : 8;
     constexpr int ROW_STEP = STEM ? 8 : 16;
-    const int tid = threadIdx.x - GATHER_WARP0 * 32;
+    const int tid = threadIdx.x - Cfg::GATHER_WARP0 * 32;
     const int chunk = tid & 7;
     const int sub = STEM ? (tid >> 4) : (tid >> 3);
     const uint32_t dst_off = STEM ? (uint32_t)(sub * 128 + ((((tid & 15) >> 1) ^ (sub & 7)) << 4) + (tid & 1) * 8)
@@ -291,7 +303,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
     const int n_blk = blockIdx.x % p.n_blocks;      // grid is a multiple of n_blocks: fixed per CTA
     const int n0 = n_blk * BLOCK_N;
 
-    if (warp == TMA_WARP && lane == 0) {
+    if (warp == Cfg::TMA_WARP && lane == 0) {
         if (A_TMA) tma_prefetch_desc(&p.tmA);
         tma_prefetch_desc(&p.tmB);
         for (int s = 0; s < STAGES; ++s) {
@@ -300,17 +312,17 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(&bars->tmem_full[a], 1);
-            mbar_init(&bars->tmem_empty[a], NUM_EPI_WARPS * 32);
+            mbar_init(&bars->tmem_empty[a], Cfg::EPI_WARPS * 32);
         }
         mbar_fence_init();
     }
-    if (warp == MMA_WARP) tmem_alloc<Cfg::TMEM_COLS>(&bars->tmem_base);
+    if (warp == Cfg::MMA_WARP) tmem_alloc<Cfg::TMEM_COLS>(&bars->tmem_base);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_base;
 
-    if (warp == TMA_WARP) {
+    if (warp == Cfg::TMA_WARP) {
         // ===================== TMA producer (one lane) =====================
         if (lane == 0) {
             int stage = 0;
@@ -364,7 +376,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                 }
             }
         }
-    } else if (warp == MMA_WARP) {
+    } else if (warp == Cfg::MMA_WARP) {
         // ===================== MMA issuer (one lane) =====================
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BLOCK_N, 0, B_MN ? 1 : 0);
@@ -395,10 +407,10 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                 umma_commit(&bars->tmem_full[acc]);
             }
         }
-    } else if (warp < NUM_EPI_WARPS) {
+    } else if (warp < Cfg::EPI_WARPS) {
         // ===================== Epilogue =====================
         const int q = warp & 3;
-        const int half = warp >> 2;
+        const int half = warp >> 2;       // column group of this warp
         // per-chunk BN partial sums, kept in four scalar pairs so the chunk loop need not be unrolled (the unrolled
         // butterfly made the epilogue stall on instruction fetch: ncu stall_no_inst 27 %)
         // BN partial sums: lane (cp = lane & 15, par = lane >> 4) accumulates columns 2cp, 2cp+1 of each of the warp's
@@ -421,7 +433,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
             tc_fence_after();
 #pragma unroll 1
             for (int c = 0; c < Cfg::CHUNKS_PER_WARP; ++c) {
-                const int col = half * (BLOCK_N / 2) + c * 32;
+                const int col = half * Cfg::COLS_PER_GROUP + c * 32;
                 uint32_t raw[32];
                 tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BLOCK_N + col, raw);
                 tmem_ld_wait();
@@ -533,7 +545,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
             const float4 fa[4] = {acc0, acc1, acc2, acc3};
 #pragma unroll
             for (int c = 0; c < Cfg::CHUNKS_PER_WARP; ++c) {
-                const int nb = n0 + half * (BLOCK_N / 2) + c * 32;
+                const int nb = n0 + half * Cfg::COLS_PER_GROUP + c * 32;
                 if (stats_smem) {
                     const int n = nb + 2 * (int)(lane & 15);
                     atomicAdd(p.stat_sum + n, fa[c].x);
@@ -554,7 +566,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
 
     tc_fence_before();
     __syncthreads();
-    if (warp == MMA_WARP) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+    if (warp == Cfg::MMA_WARP) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
 // ------------------------------------------------------------------------------------------
