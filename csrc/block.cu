@@ -140,7 +140,13 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
     } while (0)
 
     SideStream* side = overlap_enabled() ? side_stream() : nullptr;
-    BN_BWD(2, d->dz, 1, d->g_id);            // last BN: also emits the masked gradient of the identity branch
+    // The identity-branch gradient is dz behind the block's final ReLU.  With the forward's bit mask it is taken
+    // from dz where it is needed (gated addend of conv1's data gradient, or the shortcut BN's backward in mask
+    // mode); without it the last BN's backward writes it out as g_id.
+    static int gate_on = -1;
+    if (gate_on < 0) { const char* e = getenv("PTDB200_GATE_IDENTITY"); gate_on = e ? atoi(e) : 1; }
+    const bool gate = d->mask[2] != nullptr && gate_on;
+    BN_BWD(2, d->dz, 1, gate ? nullptr : d->g_id);
     DGRAD(2, d->dz2, nullptr);
     WGRAD(2, d->z[1]);
     BN_BWD(1, d->dz2, 1, nullptr);
@@ -148,12 +154,27 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
     WGRAD(1, d->z[0]);
     BN_BWD(0, d->dz1, 1, nullptr);
     if (d->has_ds) {
-        BN_BWD(3, d->g_id, 0, nullptr);
+        if (gate) {
+            float* sm = d->sums + off[3];
+            const float* sv = d->saved + off[3];
+            rc = ptd_bn_bwd_reduce(d->dz, d->mask[2], d->y[3], sv, sv + g[3].cout, sm, sm + g[3].cout, g[3].m_out,
+                                   g[3].cout, 2, stream);
+            if (rc) return rc;
+            rc = ptd_bn_bwd_apply(d->dz, d->mask[2], d->y[3], sv, sv + g[3].cout, d->gamma[3], sm, sm + g[3].cout,
+                                  d->dy[3], nullptr, g[3].m_out, g[3].cout, 2, stream);
+            if (rc) return rc;
+        } else {
+            BN_BWD(3, d->g_id, 0, nullptr);
+        }
         WGRAD(3, d->x);
         DGRAD(0, d->dx, nullptr);
         // the shortcut convolution adds into dx in place (stride 2 touches only the strided quarter)
         rc = ptd_conv_dgrad_accum(d->dy[3], d->w[3], d->dx, d->N, g[3].h_in, g[3].w_in, g[3].cin, g[3].cout, 1, 1,
                                   g[3].stride, 0, stream);
+        if (rc) return rc;
+    } else if (gate) {
+        rc = ptd_conv_dgrad_masked_addend(d->dy[0], d->w[0], d->dx, d->dz, d->mask[2], d->N, g[0].h_in, g[0].w_in, g[0].cin,
+                                          g[0].cout, stream);
         if (rc) return rc;
     } else {
         DGRAD(0, d->dx, d->g_id);

@@ -63,6 +63,7 @@ struct alignas(64) FParams {
     int b_cblocks;       // MN-major B: k-blocks per tap
     bf16* out;
     const bf16* addend;
+    const uint8_t* addend_mask;   // optional: bit (element & 7) of byte (element >> 3) gates the addend element
     float* stat_sum;
     float* stat_sq;
     float* out_f32;
@@ -482,7 +483,15 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                             const size_t off = (size_t)orow * p.ldo + n0 + col + pc * 8;
                             if (p.addend != nullptr) {
                                 const uint4 a4 = *reinterpret_cast<const uint4*>(p.addend + off);
-                                const uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+                                uint32_t aw[4] = {a4.x, a4.y, a4.z, a4.w};
+                                if (p.addend_mask != nullptr) {
+                                    // the addend is a gradient that still has to pass a ReLU: one mask bit per element
+                                    const uint32_t mb = p.addend_mask[off >> 3];
+#pragma unroll
+                                    for (int e = 0; e < 4; ++e)
+                                        aw[e] &= (((mb >> (2 * e)) & 1u) ? 0x0000ffffu : 0u) |
+                                                 (((mb >> (2 * e + 1)) & 1u) ? 0xffff0000u : 0u);
+                                }
                                 uint32_t ow[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
                                 for (int e = 0; e < 4; ++e) {
@@ -1087,6 +1096,26 @@ extern "C" int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const voi
         if (ok) return PTD_OK;
     }
     return dispatch_f<AM_GATHER, true, 0>(p, bn, stream);
+}
+
+// 1x1 stride-1 data gradient with a gated addend: dx = dy * W + (mask bit ? addend : 0).  `mask` is the ReLU bit
+// tensor of ptd_bn_apply_mask over dx's shape: the residual block's identity-branch gradient is the block-output
+// gradient behind the final ReLU, so it can be taken from dz directly instead of from a materialised copy.
+extern "C" int ptd_conv_dgrad_masked_addend(const void* dy, const void* w, void* dx, const void* addend,
+                                            const void* mask, int N, int H, int W, int Cin, int Cout, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    PTD_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "conv_dgrad: Cin (%d) and Cout (%d) must be multiples of 64", Cin, Cout);
+    PTD_REQUIRE(addend != nullptr && mask != nullptr, "conv_dgrad_masked_addend: addend and mask are required");
+    FParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = N * H * W; p.N = Cin; p.num_kb = Cout / 64;
+    p.out = (bf16*)dx; p.ldo = Cin; p.addend = (const bf16*)addend; p.addend_mask = (const uint8_t*)mask;
+    p.b_tap_cols = Cin; p.b_cblocks = Cout / 64;
+    int rc = ptd_make_tmap_2d_bf16(&p.tmB, w, (uint64_t)Cin, Cout, (uint64_t)Cin * 2, 64, 64);
+    if (rc) return rc;
+    rc = ptd_make_tmap_2d_bf16(&p.tmA, dy, Cout, p.M, (uint64_t)Cout * 2, 64, BLOCK_M);
+    if (rc) return rc;
+    return dispatch_f<AM_TILED, true, 0>(p, pick_block_n(Cin), stream);
 }
 
 // dx += conv_transpose(dy, w)  (in place).  For the 1x1 stride-2 shortcut convolution this touches only the

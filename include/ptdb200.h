@@ -29,6 +29,10 @@ int ptd_conv_fprop(const void* x, const void* w, void* y, float* stat_sum, float
 /* dx[N,H,W,Cin] = conv_transpose(dy[N,OH,OW,Cout], w) (+ addend[N,H,W,Cin] if not NULL). */
 int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const void* addend, int N, int H, int W, int Cin,
                    int Cout, int R, int S, int stride, int pad, void* stream);
+/* 1x1 stride-1 data gradient whose addend passes a ReLU first: dx = dy*W + (mask bit ? addend : 0), mask = the
+ * u8 bit tensor of ptd_bn_apply_mask over dx's shape (a residual block's identity-branch gradient, taken from dz) */
+int ptd_conv_dgrad_masked_addend(const void* dy, const void* w, void* dx, const void* addend, const void* mask, int N,
+                                 int H, int W, int Cin, int Cout, void* stream);
 /* dx += conv_transpose(dy, w), in place (the 1x1 stride-2 shortcut only touches the strided quarter of dx). */
 int ptd_conv_dgrad_accum(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int R, int S,
                          int stride, int pad, void* stream);
