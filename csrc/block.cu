@@ -55,6 +55,11 @@ SideStream* side_stream() {
     }
     return &s;
 }
+bool dual_bn_enabled() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("PTDB200_DUAL_BN"); v = e ? atoi(e) : 1; }
+    return v == 1;
+}
 bool overlap_enabled() {
     static int v = -1;
     if (v < 0) { const char* e = getenv("PTDB200_WGRAD_OVERLAP"); v = e ? atoi(e) : 1; }
@@ -82,6 +87,17 @@ extern "C" int ptd_bottleneck_fwd(const PtdBottleneckFwd* d, void* stream) {
         int rc = ptd_conv_fprop(in, d->w[i], d->y[i], st, st + g[i].cout, d->N, g[i].h_in, g[i].w_in, g[i].cin, g[i].cout,
                                 g[i].k, g[i].k, g[i].stride, g[i].pad, stream);
         if (rc) return rc;
+        if (i == 3 && dual_bn_enabled()) continue;          // the shortcut's BN is applied inside conv3's BN below
+        if (i == 2 && d->has_ds && dual_bn_enabled()) {
+            float* st3 = d->stats + off[3];
+            float* sv3 = d->saved + off[3];
+            rc = ptd_bn_apply_dual(d->y[2], d->y[3], d->z[2], d->mask[2], st, st + g[2].cout, d->gamma[2], d->beta[2],
+                                   d->running_mean[2], d->running_var[2], sv, sv + g[2].cout, st3, st3 + g[3].cout,
+                                   d->gamma[3], d->beta[3], d->running_mean[3], d->running_var[3], sv3, sv3 + g[3].cout,
+                                   g[2].m_out, g[2].cout, d->eps, d->momentum, stream);
+            if (rc) return rc;
+            continue;
+        }
         const void* residual = nullptr;
         int relu = 1;
         if (i == 2) residual = d->has_ds ? d->z[3] : d->x;

@@ -160,6 +160,82 @@ bn_apply_kernel(const bf16* __restrict__ y, const bf16* __restrict__ res, bf16* 
     }
 }
 
+// z = relu(bn(y) + bn2(y2)): the last BatchNorm of a residual block whose shortcut is itself conv + BN.  The
+// shortcut's normalised activation is never written: it is applied here, straight from the shortcut convolution's
+// output y2, with its own batch statistics (and its running statistics / saved mean, invstd are updated here too).
+__global__ void __launch_bounds__(BN_THREADS, 3)
+bn_apply_dual_kernel(const bf16* __restrict__ y, const bf16* __restrict__ y2, bf16* __restrict__ z,
+                     unsigned char* __restrict__ mask, const float* __restrict__ sum, const float* __restrict__ sq,
+                     const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ running_mean,
+                     float* __restrict__ running_var, float* __restrict__ save_mean, float* __restrict__ save_invstd,
+                     const float* __restrict__ sum2, const float* __restrict__ sq2, const float* __restrict__ gamma2,
+                     const float* __restrict__ beta2, float* __restrict__ running_mean2, float* __restrict__ running_var2,
+                     float* __restrict__ save_mean2, float* __restrict__ save_invstd2, long long M, int C, float eps,
+                     float momentum) {
+    const int cg = C >> 3;
+    const int rows_per_iter = BN_THREADS / cg;
+    const int g = threadIdx.x % cg;
+    float scale[8], scale2[8], shift[8];
+    const float inv_m = 1.f / (float)M;
+    const float unb = M > 1 ? (float)M / (float)(M - 1) : 1.f;
+    const bool writer = blockIdx.x == 0 && threadIdx.x < cg;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = g * 8 + i;
+        const float mean = sum[c] * inv_m, mean2 = sum2[c] * inv_m;
+        const float var = fmaxf(sq[c] * inv_m - mean * mean, 0.f), var2 = fmaxf(sq2[c] * inv_m - mean2 * mean2, 0.f);
+        const float invstd = rsqrtf(var + eps), invstd2 = rsqrtf(var2 + eps);
+        scale[i] = gamma[c] * invstd;
+        scale2[i] = gamma2[c] * invstd2;
+        shift[i] = (beta[c] - mean * scale[i]) + (beta2[c] - mean2 * scale2[i]);
+        if (writer) {
+            save_mean[c] = mean; save_invstd[c] = invstd;
+            save_mean2[c] = mean2; save_invstd2[c] = invstd2;
+            if (running_mean != nullptr) {
+                running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+                running_var[c] = (1.f - momentum) * running_var[c] + momentum * var * unb;
+            }
+            if (running_mean2 != nullptr) {
+                running_mean2[c] = (1.f - momentum) * running_mean2[c] + momentum * mean2;
+                running_var2[c] = (1.f - momentum) * running_var2[c] + momentum * var2 * unb;
+            }
+        }
+    }
+    long long row = (long long)blockIdx.x * rows_per_iter + threadIdx.x / cg;
+    const long long row_step = (long long)gridDim.x * rows_per_iter;
+    constexpr int U = 2;
+    for (; row < M; row += U * row_step) {
+        uint4 ry[U], rr[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long ru = row + u * row_step;
+            if (ru < M) {
+                const size_t off = (size_t)ru * C + g * 8;
+                ry[u] = *reinterpret_cast<const uint4*>(y + off);
+                rr[u] = *reinterpret_cast<const uint4*>(y2 + off);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long ru = row + u * row_step;
+            if (ru >= M) break;
+            const size_t off = (size_t)ru * C + g * 8;
+            float f[8], r[8];
+            unpack8(ry[u], f);
+            unpack8(rr[u], r);
+            unsigned bits = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                float v = fmaf(f[i], scale[i], fmaf(r[i], scale2[i], shift[i]));
+                if (v > 0.f) bits |= 1u << i;
+                f[i] = fmaxf(v, 0.f);
+            }
+            *reinterpret_cast<uint4*>(z + off) = pack8(f);
+            if (mask != nullptr) mask[(size_t)ru * cg + g] = (unsigned char)bits;
+        }
+    }
+}
+
 // z = act(y * scale[c] + shift[c] [+ residual])  (inference-mode BN, or any per-channel affine)
 template <bool RELU, bool RES>
 __global__ void __launch_bounds__(BN_THREADS)
@@ -551,6 +627,22 @@ extern "C" int ptd_bn_apply_mask(const void* y, const void* residual, void* z, v
     else if (residual) PTD_BN_APPLY(false, true);
     else PTD_BN_APPLY(false, false);
 #undef PTD_BN_APPLY
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+// z = relu(bn(y) + bn2(y2)) with both sets of batch statistics; see bn_apply_dual_kernel.
+extern "C" int ptd_bn_apply_dual(const void* y, const void* y2, void* z, void* mask, const float* sum, const float* sq,
+                                 const float* gamma, const float* beta, float* running_mean, float* running_var,
+                                 float* save_mean, float* save_invstd, const float* sum2, const float* sq2,
+                                 const float* gamma2, const float* beta2, float* running_mean2, float* running_var2,
+                                 float* save_mean2, float* save_invstd2, long long M, int C, float eps, float momentum,
+                                 void* stream) {
+    PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
+    bn_apply_dual_kernel<<<bn_grid(M, C, 3), BN_THREADS, 0, (cudaStream_t)stream>>>(
+        (const bf16*)y, (const bf16*)y2, (bf16*)z, (unsigned char*)mask, sum, sq, gamma, beta, running_mean, running_var,
+        save_mean, save_invstd, sum2, sq2, gamma2, beta2, running_mean2, running_var2, save_mean2, save_invstd2, M, C,
+        eps, momentum);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }

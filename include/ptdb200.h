@@ -109,6 +109,13 @@ int ptd_bn_apply(const void* y, const void* residual, void* z, const float* sum,
 int ptd_bn_apply_mask(const void* y, const void* residual, void* z, void* mask, const float* sum, const float* sq,
                       const float* gamma, const float* beta, float* running_mean, float* running_var, float* save_mean,
                       float* save_invstd, long long M, int C, float eps, float momentum, int relu, void* stream);
+/* z = relu(bn(y) + bn2(y2)): last BN of a residual block fused with the BN of its conv shortcut (y2 = the shortcut
+ * convolution's output); both sets of running statistics and saved mean / invstd are written */
+int ptd_bn_apply_dual(const void* y, const void* y2, void* z, void* mask, const float* sum, const float* sq,
+                      const float* gamma, const float* beta, float* running_mean, float* running_var, float* save_mean,
+                      float* save_invstd, const float* sum2, const float* sq2, const float* gamma2, const float* beta2,
+                      float* running_mean2, float* running_var2, float* save_mean2, float* save_invstd2, long long M,
+                      int C, float eps, float momentum, void* stream);
 /* z = act(y * scale[c] + shift[c] [+ residual])  (inference-mode BN) */
 int ptd_affine_act(const void* y, const void* residual, void* z, const float* scale, const float* shift, long long M,
                    int C, int relu, void* stream);
