@@ -162,7 +162,17 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
     static int gate_on = -1;
     if (gate_on < 0) { const char* e = getenv("PTDB200_GATE_IDENTITY"); gate_on = e ? atoi(e) : 1; }
     const bool gate = d->mask[2] != nullptr && gate_on;
-    BN_BWD(2, d->dz, 1, gate ? nullptr : d->g_id);
+    const bool dual = gate && d->has_ds && dual_bn_enabled();     // last BN and shortcut BN share g = dz * mask
+    if (dual) {
+        const float* sv2 = d->saved + off[2];
+        const float* sv3 = d->saved + off[3];
+        rc = ptd_bn_bwd_dual(d->dz, d->mask[2], d->y[2], d->y[3], sv2, sv2 + g[2].cout, d->gamma[2], sv3, sv3 + g[3].cout,
+                             d->gamma[3], d->sums + off[2], d->sums + off[3], d->dy[2], d->dy[3], g[2].m_out, g[2].cout,
+                             stream);
+        if (rc) return rc;
+    } else {
+        BN_BWD(2, d->dz, 1, gate ? nullptr : d->g_id);
+    }
     DGRAD(2, d->dz2, nullptr);
     WGRAD(2, d->z[1]);
     BN_BWD(1, d->dz2, 1, nullptr);
@@ -170,7 +180,9 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
     WGRAD(1, d->z[0]);
     BN_BWD(0, d->dz1, 1, nullptr);
     if (d->has_ds) {
-        if (gate) {
+        if (dual) {
+            /* the shortcut BN's backward ran together with the last BN's */
+        } else if (gate) {
             float* sm = d->sums + off[3];
             const float* sv = d->saved + off[3];
             rc = ptd_bn_bwd_reduce(d->dz, d->mask[2], d->y[3], sv, sv + g[3].cout, sm, sm + g[3].cout, g[3].m_out,

@@ -390,6 +390,135 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dz, const void* __restrict__ zm, co
 }
 
 // =================================================================================================
+// Backward of z = relu(bn(y) + bn2(y2)) (bn_apply_dual_kernel): both BatchNorms see the same gradient
+// g = dz * mask, so dz and the mask are read once per pass for the two of them.
+// =================================================================================================
+__global__ void __launch_bounds__(BN_THREADS, 2)
+bn_bwd_reduce_dual_kernel(const bf16* __restrict__ dz, const unsigned char* __restrict__ mask, const bf16* __restrict__ y,
+                          const bf16* __restrict__ y2, const float* __restrict__ mean, const float* __restrict__ invstd,
+                          const float* __restrict__ mean2, const float* __restrict__ invstd2, float* __restrict__ sum_g,
+                          float* __restrict__ sum_gx, float* __restrict__ sum_g2, float* __restrict__ sum_gx2, long long M,
+                          int C) {
+    const int cg = C >> 3;
+    const int rows_per_iter = BN_THREADS / cg;
+    const int g = threadIdx.x % cg;
+    float mu[8], mu2[8], s[8], q[8], q2[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { mu[i] = mean[g * 8 + i]; mu2[i] = mean2[g * 8 + i]; s[i] = q[i] = q2[i] = 0.f; }
+    long long row = (long long)blockIdx.x * rows_per_iter + threadIdx.x / cg;
+    const long long row_step = (long long)gridDim.x * rows_per_iter;
+    constexpr int U = 4;
+    for (; row < M; row += U * row_step) {
+        uint4 rd[U], rx[U], rx2[U];
+        unsigned rb[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long ru = row + u * row_step;
+            rb[u] = 0;                                  // rows past M: all elements dead
+            if (ru < M) {
+                const size_t off = (size_t)ru * C + g * 8;
+                rd[u] = *reinterpret_cast<const uint4*>(dz + off);
+                rx[u] = *reinterpret_cast<const uint4*>(y + off);
+                rx2[u] = *reinterpret_cast<const uint4*>(y2 + off);
+                rb[u] = mask[(size_t)ru * cg + g];
+            } else {
+                rd[u] = rx[u] = rx2[u] = make_uint4(0, 0, 0, 0);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float d[8], x[8], x2[8];
+            unpack8(rd[u], d);
+            unpack8(rx[u], x);
+            unpack8(rx2[u], x2);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float gi = ((rb[u] >> i) & 1u) ? d[i] : 0.f;
+                s[i] += gi;
+                q[i] = fmaf(gi, x[i] - mu[i], q[i]);
+                q2[i] = fmaf(gi, x2[i] - mu2[i], q2[i]);
+            }
+        }
+    }
+    float s2[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { q[i] *= invstd[g * 8 + i]; q2[i] *= invstd2[g * 8 + i]; s2[i] = s[i]; }
+    extern __shared__ float sh_red[];
+    block_channel_reduce(s, q, cg, g, sum_g, sum_gx, sh_red);
+    __syncthreads();
+    block_channel_reduce(s2, q2, cg, g, sum_g2, sum_gx2, sh_red);
+}
+
+__global__ void __launch_bounds__(BN_THREADS, 2)
+bn_bwd_apply_dual_kernel(const bf16* __restrict__ dz, const unsigned char* __restrict__ mask, const bf16* __restrict__ y,
+                         const bf16* __restrict__ y2, const float* __restrict__ mean, const float* __restrict__ invstd,
+                         const float* __restrict__ gamma, const float* __restrict__ mean2, const float* __restrict__ invstd2,
+                         const float* __restrict__ gamma2, const float* __restrict__ sum_g, const float* __restrict__ sum_gx,
+                         const float* __restrict__ sum_g2, const float* __restrict__ sum_gx2, bf16* __restrict__ dy,
+                         bf16* __restrict__ dy2, long long M, int C) {
+    const int cg = C >> 3;
+    const int rows_per_iter = BN_THREADS / cg;
+    const int g = threadIdx.x % cg;
+    float k[8], a0[8], a1[8], k2[8], b0[8], b1[8];      // dy = k*g + a0 + a1*y,  dy2 = k2*g + b0 + b1*y2
+    const float inv_m = 1.f / (float)M;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int c = g * 8 + i;
+        {
+            const float is = invstd[c], mu = mean[c];
+            k[i] = gamma[c] * is;
+            const float t = k[i] * sum_gx[c] * inv_m * is;
+            a1[i] = -t;
+            a0[i] = fmaf(t, mu, -k[i] * sum_g[c] * inv_m);
+        }
+        {
+            const float is = invstd2[c], mu = mean2[c];
+            k2[i] = gamma2[c] * is;
+            const float t = k2[i] * sum_gx2[c] * inv_m * is;
+            b1[i] = -t;
+            b0[i] = fmaf(t, mu, -k2[i] * sum_g2[c] * inv_m);
+        }
+    }
+    long long row = (long long)blockIdx.x * rows_per_iter + threadIdx.x / cg;
+    const long long row_step = (long long)gridDim.x * rows_per_iter;
+    constexpr int U = 2;
+    for (; row < M; row += U * row_step) {
+        uint4 rd[U], rx[U], rx2[U];
+        unsigned rb[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long ru = row + u * row_step;
+            rb[u] = 0;
+            if (ru < M) {
+                const size_t off = (size_t)ru * C + g * 8;
+                rd[u] = *reinterpret_cast<const uint4*>(dz + off);
+                rx[u] = *reinterpret_cast<const uint4*>(y + off);
+                rx2[u] = *reinterpret_cast<const uint4*>(y2 + off);
+                rb[u] = mask[(size_t)ru * cg + g];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long ru = row + u * row_step;
+            if (ru >= M) break;
+            const size_t off = (size_t)ru * C + g * 8;
+            float d[8], x[8], x2[8], o[8], o2[8];
+            unpack8(rd[u], d);
+            unpack8(rx[u], x);
+            unpack8(rx2[u], x2);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float gi = ((rb[u] >> i) & 1u) ? d[i] : 0.f;
+                o[i] = fmaf(k[i], gi, fmaf(a1[i], x[i], a0[i]));
+                o2[i] = fmaf(k2[i], gi, fmaf(b1[i], x2[i], b0[i]));
+            }
+            *reinterpret_cast<uint4*>(dy + off) = pack8(o);
+            *reinterpret_cast<uint4*>(dy2 + off) = pack8(o2);
+        }
+    }
+}
+
+// =================================================================================================
 // BatchNorm + ReLU + 3x3/2 max-pool in one pass each way (the ResNet stem's tail)
 // =================================================================================================
 // Forward: p = maxpool(relu(bn(y))) straight from the convolution output; the 112x112 activation between BN and
@@ -627,6 +756,27 @@ extern "C" int ptd_bn_apply_mask(const void* y, const void* residual, void* z, v
     else if (residual) PTD_BN_APPLY(false, true);
     else PTD_BN_APPLY(false, false);
 #undef PTD_BN_APPLY
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+// Backward of ptd_bn_apply_dual: dy / dy2 = gradients w.r.t. y / y2; sums / sums2 = [dbeta | dgamma] of the two
+// BatchNorms (2*C floats each, zeroed by the caller); mask = the bit tensor the forward wrote.
+extern "C" int ptd_bn_bwd_dual(const void* dz, const void* mask, const void* y, const void* y2, const float* mean,
+                               const float* invstd, const float* gamma, const float* mean2, const float* invstd2,
+                               const float* gamma2, float* sums, float* sums2, void* dy, void* dy2, long long M, int C,
+                               void* stream) {
+    PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
+    PTD_REQUIRE(mask != nullptr, "bn_bwd_dual: the forward's ReLU bit mask is required");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int grid = bn_grid(M, C, 2);
+    bn_bwd_reduce_dual_kernel<<<grid, BN_THREADS, 2 * C * sizeof(float), st>>>(
+        (const bf16*)dz, (const unsigned char*)mask, (const bf16*)y, (const bf16*)y2, mean, invstd, mean2, invstd2, sums,
+        sums + C, sums2, sums2 + C, M, C);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    bn_bwd_apply_dual_kernel<<<grid, BN_THREADS, 0, st>>>(
+        (const bf16*)dz, (const unsigned char*)mask, (const bf16*)y, (const bf16*)y2, mean, invstd, gamma, mean2, invstd2,
+        gamma2, sums, sums + C, sums2, sums2 + C, (bf16*)dy, (bf16*)dy2, M, C);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }

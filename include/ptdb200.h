@@ -116,6 +116,10 @@ int ptd_bn_apply_dual(const void* y, const void* y2, void* z, void* mask, const 
                       float* save_invstd, const float* sum2, const float* sq2, const float* gamma2, const float* beta2,
                       float* running_mean2, float* running_var2, float* save_mean2, float* save_invstd2, long long M,
                       int C, float eps, float momentum, void* stream);
+/* backward of ptd_bn_apply_dual (both passes, dz and the mask read once for the two BatchNorms) */
+int ptd_bn_bwd_dual(const void* dz, const void* mask, const void* y, const void* y2, const float* mean,
+                    const float* invstd, const float* gamma, const float* mean2, const float* invstd2,
+                    const float* gamma2, float* sums, float* sums2, void* dy, void* dy2, long long M, int C, void* stream);
 /* z = act(y * scale[c] + shift[c] [+ residual])  (inference-mode BN) */
 int ptd_affine_act(const void* y, const void* residual, void* z, const float* scale, const float* shift, long long M,
                    int C, int relu, void* stream);
