@@ -157,6 +157,23 @@ __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* m, 
         : "memory");
 }
 
+// Tiled store shared -> global (bulk async-group completion): the issuing thread must have ordered the generic-proxy
+// writes of the tile before it (fence.proxy.async by the writers, then a barrier).
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, uint32_t src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(m)), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all but the N most recent bulk groups have finished READING their shared-memory source
+template <int N>
+__device__ __forceinline__ void bulk_wait_group_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait_group() {
+    asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+
 // im2col-mode load: (c, w, h, n) is the input-space position of the first pixel's top-left tap, (off_w, off_h) the
 // filter tap; the box is [pixels][64 channels].
 __device__ __forceinline__ void tma_load_im2col(uint32_t dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h,

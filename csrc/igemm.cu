@@ -56,7 +56,9 @@ struct ConvGeom {
 struct alignas(64) FParams {
     CUtensorMap tmA;
     CUtensorMap tmB;
+    CUtensorMap tmO;     // output [M][ldo] bf16, box 32 x 32 with the 64-byte swizzle (valid when tma_store != 0)
     ConvGeom g;
+    int tma_store;       // epilogue hands each staged 32 x 32 tile to the TMA store engine instead of LDS + STG
     int M, N, num_kb;
     int n_blocks, m_blocks;
     int b_tap_cols;      // MN-major B: column offset per filter tap (= N of the full weight slice)
@@ -307,6 +309,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
     if (warp == Cfg::TMA_WARP && lane == 0) {
         if (A_TMA) tma_prefetch_desc(&p.tmA);
         tma_prefetch_desc(&p.tmB);
+        if (EPI == 0 && p.tma_store != 0) tma_prefetch_desc(&p.tmO);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&bars->full[s], A_TMA ? 1 : 1 + ((p.dbg & 4) ? 4 : NUM_GATHER_THREADS));
             mbar_init(&bars->empty[s], 1);
@@ -446,6 +449,11 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                     // contiguous: 4 lanes cover one row's 64 B (two full sectors) instead of every lane
                     // writing 16 B of a different row.  XOR on the 16-byte slot keeps both phases conflict-free.
                     const uint32_t stg = smem_base + Cfg::STAGING_OFF + warp * 2048;
+                    const bool tma_out = p.tma_store != 0;
+                    if (tma_out) {              // the previous tile of this warp has been read out of the buffer
+                        if (lane == 0) bulk_wait_group_read<0>();
+                        __syncwarp();
+                    }
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const uint32_t a = stg + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4);
@@ -454,8 +462,20 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                                      "r"(pack_bf16x2(v[j * 8 + 4], v[j * 8 + 5])), "r"(pack_bf16x2(v[j * 8 + 6], v[j * 8 + 7]))
                                      : "memory");
                     }
-                    __syncwarp();
                     const long long m_base = (long long)(t / p.n_blocks) * BLOCK_M + q * 32;
+                    if (tma_out) {
+                        // The staging tile already is the 64-byte-swizzle image of a [32 rows][32 channels] box: one
+                        // lane hands it to the TMA store engine (rows past M are clipped), which takes the LDS + STG
+                        // wavefronts of the copy-out off the load/store pipe - ncu had that pipe 72 % busy and the
+                        // copy-out was 51 of its 83 wavefronts per tile (profiles/README.md).
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0) {
+                            tma_store_2d(&p.tmO, stg, n0 + col, (int)m_base);
+                            bulk_commit_group();
+                        }
+                    } else {
+                    __syncwarp();
 #pragma unroll
                     for (int i = 0; i < 4; ++i) {
                         const int piece = (int)lane + 32 * i;
@@ -503,6 +523,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                             *reinterpret_cast<uint4*>(p.out + off) = o;
                         }
                     }
+                    }       // !tma_out
                     if (do_stats && !stats_smem) {
                         float sq[32];
 #pragma unroll
@@ -550,6 +571,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
             tc_fence_before();
             mbar_arrive(&bars->tmem_empty[acc]);
         }
+        if (EPI == 0 && p.tma_store != 0 && lane == 0) bulk_wait_group<0>();      // this warp's stores are complete
         if (do_stats) {
             const float4 fa[4] = {acc0, acc1, acc2, acc3};
 #pragma unroll
@@ -956,6 +978,18 @@ int pick_nsub(int ksub) {   // ksub = Kw / 64
     return 1;
 }
 
+// Output through the TMA store engine: possible when GEMM row m is output row m (no row map) and nothing is added
+// to the tile on its way out.
+int enable_tma_store(FParams& p) {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("PTD_TMA_STORE"); on = e ? atoi(e) : 1; }
+    if (!on || p.addend != nullptr || p.map_mul != 0 || p.out == nullptr) return PTD_OK;
+    int rc = ptd_make_tmap_2d_bf16_store64(&p.tmO, p.out, (uint64_t)p.ldo, (uint64_t)p.M, (uint64_t)p.ldo * 2, 32);
+    if (rc) return rc;
+    p.tma_store = 1;
+    return PTD_OK;
+}
+
 bool force_gather() {
     static int v = -1;
     if (v < 0) { const char* e = getenv("PTD_IGEMM_FORCE_GATHER"); v = (e && atoi(e)) ? 1 : 0; }
@@ -998,6 +1032,8 @@ extern "C" int ptd_conv_fprop(const void* x, const void* w, void* y, float* stat
     const int bn = pick_block_n(Cout);
     int rc = ptd_make_tmap_2d_bf16(&p.tmB, w, (uint64_t)R * S * Cin, Cout, (uint64_t)R * S * Cin * 2, 64, bn);
     if (rc) return rc;
+    rc = enable_tma_store(p);
+    if (rc) return rc;
     const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
     if (plain) {
         rc = ptd_make_tmap_2d_bf16(&p.tmA, x, Cin, p.M, (uint64_t)Cin * 2, 64, BLOCK_M);
@@ -1034,6 +1070,8 @@ extern "C" int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const voi
     if (plain) {
         rc = ptd_make_tmap_2d_bf16(&p.tmA, dy, Cout, p.M, (uint64_t)Cout * 2, 64, BLOCK_M);
         if (rc) return rc;
+        rc = enable_tma_store(p);
+        if (rc) return rc;
         return dispatch_f<AM_TILED, true, 0>(p, bn, stream);
     }
     fill_geom(p.g, (const bf16*)dy, OH, OW, Cout, H, W, R, S, stride, pad, GM_DGRAD);
@@ -1045,6 +1083,8 @@ extern "C" int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const voi
         if (rc) return rc;
         fill_taps(p, R, S, true);
         p.g.pad = (S - 1) - pad;          // tile origin = (w - ((S-1) - pad), h - ...)
+        rc = enable_tma_store(p);
+        if (rc) return rc;
         return dispatch_f<AM_IM2COL, true, 0>(p, bn, stream);
     }
     if (stride == 2 && (H % 2 == 0) && (W % 2 == 0) && OH == H / 2 && OW == W / 2) {

@@ -138,6 +138,32 @@ int ptd_make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dim
     return PTD_OK;
 }
 
+int ptd_make_tmap_2d_bf16_store64(CUtensorMap* out, const void* base, uint64_t inner, uint64_t rows,
+                                  uint64_t row_pitch_bytes, uint32_t box_rows) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) {
+        ptd_set_error("cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
+        return PTD_ERR_CUDA;
+    }
+    if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || (row_pitch_bytes & 15) != 0) {
+        ptd_set_error("TMA needs a 16-byte aligned base (%p) and row pitch (%llu)", base, (unsigned long long)row_pitch_bytes);
+        return PTD_ERR_ARG;
+    }
+    cuuint64_t dims[2] = {inner, rows};
+    cuuint64_t strides[1] = {row_pitch_bytes};
+    cuuint32_t box[2] = {32, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        ptd_set_error("cuTensorMapEncodeTiled (store) failed: %d (inner=%llu rows=%llu pitch=%llu box=32x%u)", (int)r,
+                      (unsigned long long)inner, (unsigned long long)rows, (unsigned long long)row_pitch_bytes, box_rows);
+        return PTD_ERR_CUDA;
+    }
+    return PTD_OK;
+}
+
 int ptd_make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t rows, uint64_t row_pitch_bytes,
                           uint32_t box_inner, uint32_t box_rows) {
     EncodeTiledFn enc = get_encode();

@@ -17,3 +17,8 @@ int ptd_make_tmap_im2col_bf16(CUtensorMap* out, const void* base, int C, int W, 
 // byte stride of dimension i+1.  Strides may be smaller than the extent below them (overlapping windows).
 int ptd_make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint64_t strides_bytes[3],
                           const uint32_t box[4]);
+
+// 2-D descriptor for STORING [box_rows][32 bf16] tiles held in shared memory with the 64-byte swizzle (16-byte chunk
+// index ^= (row >> 1) & 3).  Rows past `rows` are clipped by the hardware.
+int ptd_make_tmap_2d_bf16_store64(CUtensorMap* out, const void* base, uint64_t inner, uint64_t rows,
+                                  uint64_t row_pitch_bytes, uint32_t box_rows);
