@@ -223,11 +223,14 @@ __device__ __forceinline__ float transpose_reduce32(float (&v)[32], uint32_t lan
 // (oh, ow) for k-block r' is the 128-byte window at pixel (oh + r', ow) of the input.
 enum { AM_GATHER = 0, AM_TILED = 1, AM_IM2COL = 2, AM_PATCH = 3 };
 
-template <int BLOCK_N, int A_MODE, bool B_MN, int EPI /*0 = bf16 (+stats/+addend), 1 = fp32 + bias*/>
+// PAIR: two CTAs of a cluster share one 256 x BLOCK_N tile (tcgen05 cta_group::2): each loads its own 128 rows of A
+// and HALF of B, the leader issues M = 256 MMAs that read B from both shared memories.  Per SM that is a third fewer
+// operand bytes per MMA - what the K-heavy layers are bound by (L2 -> SM ingress, ~40 B/clk/SM measured).
+template <int BLOCK_N, int A_MODE, bool B_MN, int EPI /*0 = bf16 (+stats/+addend), 1 = fp32 + bias*/, bool PAIR = false>
 struct FCfg {
-    static constexpr int B_TILE_BYTES = BLOCK_N * BLOCK_K * 2;
+    static constexpr int B_TILE_BYTES = BLOCK_N * BLOCK_K * 2 / (PAIR ? 2 : 1);      // bytes this CTA loads
     static constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
-    static constexpr int STAGES = (BLOCK_N == 256) ? 4 : (BLOCK_N == 128 ? 6 : 8);
+    static constexpr int STAGES = PAIR ? (BLOCK_N == 256 ? 6 : 8) : ((BLOCK_N == 256) ? 4 : (BLOCK_N == 128 ? 6 : 8));
     // Epilogue warps: a warp may only read TMEM lanes 32 * (warp % 4) .. + 31, so warps come in groups of four and
     // each group takes a column range.  Wide tiles use four groups: the epilogue of a memory-bound layer is a chain
     // of long-latency steps per warp (tcgen05.ld, staging, stores) and gains from more warps in flight.
@@ -289,10 +292,11 @@ __device__ __forceinline__ void f_gather_loop(const FParams& p, Barriers<Cfg::ST
     }
 }
 
-template <int BLOCK_N, int A_MODE, bool B_MN, int EPI>
-__global__ void __launch_bounds__(FCfg<BLOCK_N, A_MODE, B_MN, EPI>::THREADS, 1)
+template <int BLOCK_N, int A_MODE, bool B_MN, int EPI, bool PAIR = false>
+__global__ void __launch_bounds__(FCfg<BLOCK_N, A_MODE, B_MN, EPI, PAIR>::THREADS, 1)
 igemm_f_kernel(const __grid_constant__ FParams p) {
-    using Cfg = FCfg<BLOCK_N, A_MODE, B_MN, EPI>;
+    using Cfg = FCfg<BLOCK_N, A_MODE, B_MN, EPI, PAIR>;
+    static_assert(!PAIR || (A_MODE == AM_TILED && EPI == 0 && BLOCK_N >= 128), "CTA pairs: tiled 1x1 path only");
     constexpr bool A_TMA = A_MODE != AM_GATHER;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
@@ -302,8 +306,13 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
 
     const int warp = threadIdx.x >> 5;
     const uint32_t lane = lane_id();
+    // PAIR: the two CTAs of a cluster are one worker; m_blocks then counts 256-row tiles
+    const uint32_t crank = PAIR ? cluster_ctarank() : 0u;
+    const int worker = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int n_workers = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    constexpr int TILE_M = PAIR ? 2 * BLOCK_M : BLOCK_M;
     const int num_tiles = p.m_blocks * p.n_blocks;
-    const int n_blk = blockIdx.x % p.n_blocks;      // grid is a multiple of n_blocks: fixed per CTA
+    const int n_blk = worker % p.n_blocks;          // workers are a multiple of n_blocks: fixed per CTA
     const int n0 = n_blk * BLOCK_N;
 
     if (warp == Cfg::TMA_WARP && lane == 0) {
@@ -316,13 +325,17 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(&bars->tmem_full[a], 1);
-            mbar_init(&bars->tmem_empty[a], Cfg::EPI_WARPS * 32);
+            mbar_init(&bars->tmem_empty[a], Cfg::EPI_WARPS * 32 * (PAIR ? 2 : 1));   // PAIR: both CTAs' epilogues
         }
         mbar_fence_init();
     }
-    if (warp == Cfg::MMA_WARP) tmem_alloc<Cfg::TMEM_COLS>(&bars->tmem_base);
+    if (warp == Cfg::MMA_WARP) {
+        if (PAIR) tmem_alloc_2sm<Cfg::TMEM_COLS>(&bars->tmem_base);
+        else tmem_alloc<Cfg::TMEM_COLS>(&bars->tmem_base);
+    }
     tc_fence_before();
     __syncthreads();
+    if (PAIR) cluster_sync_all();         // the peer's barriers exist before anything signals them
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_base;
 
@@ -331,8 +344,8 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const int m0 = (t / p.n_blocks) * BLOCK_M;
+            for (int t = worker; t < num_tiles; t += n_workers) {
+                const int m0 = (t / p.n_blocks) * TILE_M + (int)crank * BLOCK_M;
                 int iw0 = 0, ih0 = 0, in0 = 0;          // im2col: input-space position of the tile's first row
                 if (A_MODE == AM_IM2COL) {
                     const int hw = p.g.OH * p.g.OW;
@@ -356,6 +369,23 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                     mbar_wait(&bars->empty[stage], phase ^ 1);
                     const uint32_t a_dst = smem_base + stage * Cfg::STAGE_BYTES;
                     const uint32_t b_dst = a_dst + A_TILE_BYTES;
+                    if (PAIR) {
+                        // both CTAs' bytes are counted on the leader's barrier, which the leader arms for the pair
+                        if (crank == 0) mbar_arrive_expect_tx(&bars->full[stage], 2 * Cfg::STAGE_BYTES);
+                        tma_load_2d_2sm(a_dst, &p.tmA, &bars->full[stage], kb * BLOCK_K, m0);
+                        if (!B_MN) {
+                            tma_load_2d_2sm(b_dst, &p.tmB, &bars->full[stage], kb * BLOCK_K, n0 + (int)crank * (BLOCK_N / 2));
+                        } else {
+                            const int te = kb / p.b_cblocks;
+                            const int cb = kb - te * p.b_cblocks;
+#pragma unroll
+                            for (int j = 0; j < BLOCK_N / 128; ++j)
+                                tma_load_2d_2sm(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage],
+                                                te * p.b_tap_cols + n0 + (int)crank * (BLOCK_N / 2) + j * 64, cb * 64);
+                        }
+                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
                     mbar_arrive_expect_tx(&bars->full[stage], Cfg::B_TILE_BYTES + (A_TMA ? A_TILE_BYTES : 0));
                     if (A_MODE == AM_TILED) tma_load_2d(a_dst, &p.tmA, &bars->full[stage], kb * BLOCK_K, m0);
                     if (A_MODE == AM_PATCH) tma_load_4d(a_dst, &p.tmA, &bars->full[stage], 0, px0, py0 + kb, pn);
@@ -382,12 +412,12 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
         }
     } else if (warp == Cfg::MMA_WARP) {
         // ===================== MMA issuer (one lane) =====================
-        if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BLOCK_N, 0, B_MN ? 1 : 0);
+        if (lane == 0 && (!PAIR || crank == 0)) {
+            constexpr uint32_t idesc = umma_idesc_bf16(TILE_M, BLOCK_N, 0, B_MN ? 1 : 0);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+            for (int t = worker; t < num_tiles; t += n_workers, ++it) {
                 const int acc = it & 1;
                 const uint32_t acc_phase = (it >> 1) & 1;
                 mbar_wait(&bars->tmem_empty[acc], acc_phase ^ 1);
@@ -403,12 +433,15 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                         const uint64_t adesc = umma_smem_desc(a_addr + kk * 32, 16, 1024);
                         const uint64_t bdesc = B_MN ? umma_smem_desc(b_addr + kk * 2048, SUB_TILE_BYTES, 1024)
                                                     : umma_smem_desc(b_addr + kk * 32, 16, 1024);
-                        umma_f16(d_tmem, adesc, bdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
+                        if (PAIR) umma_f16_2sm(d_tmem, adesc, bdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
+                        else umma_f16(d_tmem, adesc, bdesc, idesc, (kb | kk) != 0 ? 1u : 0u);
                     }
-                    umma_commit(&bars->empty[stage]);
+                    if (PAIR) umma_commit_2sm(&bars->empty[stage]);       // frees the stage in both CTAs
+                    else umma_commit(&bars->empty[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(&bars->tmem_full[acc]);
+                if (PAIR) umma_commit_2sm(&bars->tmem_full[acc]);
+                else umma_commit(&bars->tmem_full[acc]);
             }
         }
     } else if (warp < Cfg::EPI_WARPS) {
@@ -428,10 +461,10 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
         const bool do_stats = (EPI == 0) && p.stat_sum != nullptr;
         const bool stats_smem = p.stats_smem != 0;
         int it = 0;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+        for (int t = worker; t < num_tiles; t += n_workers, ++it) {
             const int acc = it & 1;
             const uint32_t acc_phase = (it >> 1) & 1;
-            const long long m = (long long)(t / p.n_blocks) * BLOCK_M + q * 32 + lane;
+            const long long m = (long long)(t / p.n_blocks) * TILE_M + crank * BLOCK_M + q * 32 + lane;
             const bool row_ok = m < p.M;      // fp32 epilogue: one row per lane
             mbar_wait(&bars->tmem_full[acc], acc_phase);
             tc_fence_after();
@@ -462,7 +495,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                                      "r"(pack_bf16x2(v[j * 8 + 4], v[j * 8 + 5])), "r"(pack_bf16x2(v[j * 8 + 6], v[j * 8 + 7]))
                                      : "memory");
                     }
-                    const long long m_base = (long long)(t / p.n_blocks) * BLOCK_M + q * 32;
+                    const long long m_base = (long long)(t / p.n_blocks) * TILE_M + crank * BLOCK_M + q * 32;
                     if (tma_out) {
                         // The staging tile already is the 64-byte-swizzle image of a [32 rows][32 channels] box: one
                         // lane hands it to the TMA store engine (rows past M are clipped), which takes the LDS + STG
@@ -569,7 +602,8 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                 }
             }
             tc_fence_before();
-            mbar_arrive(&bars->tmem_empty[acc]);
+            if (PAIR) mbar_arrive_leader(&bars->tmem_empty[acc]);     // the leader's MMA thread waits for both CTAs
+            else mbar_arrive(&bars->tmem_empty[acc]);
         }
         if (EPI == 0 && p.tma_store != 0 && lane == 0) bulk_wait_group<0>();      // this warp's stores are complete
         if (do_stats) {
@@ -597,7 +631,11 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
 
     tc_fence_before();
     __syncthreads();
-    if (warp == Cfg::MMA_WARP) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+    if (PAIR) cluster_sync_all();          // neither CTA frees TMEM or exits while its partner may still use it
+    if (warp == Cfg::MMA_WARP) {
+        if (PAIR) tmem_dealloc_2sm<Cfg::TMEM_COLS>(tmem_base);
+        else tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -873,6 +911,61 @@ int launch_f(FParams& p, cudaStream_t stream) {
     return PTD_OK;
 }
 
+// CTA-pair launch (cluster of 2, tcgen05 cta_group::2): 256 x BLOCK_N tiles, tiled 1x1 path.
+template <int BLOCK_N, bool B_MN>
+int launch_f_pair(FParams& p, cudaStream_t stream) {
+    using Cfg = FCfg<BLOCK_N, AM_TILED, B_MN, 0, true>;
+    auto kern = igemm_f_kernel<BLOCK_N, AM_TILED, B_MN, 0, true>;
+    static bool configured[64] = {false};
+    int dev = 0;
+    PTD_CUDA_CHECK(cudaGetDevice(&dev));
+    if (!configured[dev & 63]) {
+        PTD_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
+        configured[dev & 63] = true;
+    }
+    p.m_blocks = ceil_div_i(p.M, 2 * BLOCK_M);
+    p.n_blocks = ceil_div_i(p.N, BLOCK_N);
+    { const char* e = getenv("PTD_IGEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
+    p.stats_smem = 0;
+    const int tiles = p.m_blocks * p.n_blocks;
+    int workers = ptd_num_sms() / 2;
+    workers = (workers / p.n_blocks) * p.n_blocks;      // fixed n block per worker
+    if (workers < p.n_blocks) workers = p.n_blocks;
+    if (workers > tiles) workers = tiles;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(2 * workers);
+    cfg.blockDim = dim3(Cfg::THREADS);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    PTD_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p));
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+// K loop length (k-blocks) from which a 1x1 layer runs on CTA pairs; 0 = never.
+int pair_min_kb() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("PTD_PAIR_MIN_KB"); v = e ? atoi(e) : 8; }
+    return v;
+}
+bool use_pair(const FParams& p, int block_n) {
+    const int mk = pair_min_kb();
+    return mk > 0 && block_n >= 128 && p.num_kb >= mk && p.addend == nullptr && p.map_mul == 0;
+}
+template <bool B_MN>
+int dispatch_f_pair(FParams& p, int block_n, cudaStream_t stream) {
+    if (block_n == 256) return launch_f_pair<256, B_MN>(p, stream);
+    return launch_f_pair<128, B_MN>(p, stream);
+}
+
 template <int A_MODE, bool B_MN, int EPI>
 int dispatch_f(FParams& p, int block_n, cudaStream_t stream) {
     switch (block_n) {
@@ -1030,14 +1123,17 @@ extern "C" int ptd_conv_fprop(const void* x, const void* w, void* y, float* stat
     p.M = N * OH * OW; p.N = Cout; p.num_kb = R * S * Cin / 64;
     p.out = (bf16*)y; p.ldo = Cout; p.stat_sum = stat_sum; p.stat_sq = stat_sq;
     const int bn = pick_block_n(Cout);
-    int rc = ptd_make_tmap_2d_bf16(&p.tmB, w, (uint64_t)R * S * Cin, Cout, (uint64_t)R * S * Cin * 2, 64, bn);
+    const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
+    const bool pair = plain && use_pair(p, bn);
+    // a CTA of a pair loads half of the weight rows of the tile
+    int rc = ptd_make_tmap_2d_bf16(&p.tmB, w, (uint64_t)R * S * Cin, Cout, (uint64_t)R * S * Cin * 2, 64, pair ? bn / 2 : bn);
     if (rc) return rc;
     rc = enable_tma_store(p);
     if (rc) return rc;
-    const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
     if (plain) {
         rc = ptd_make_tmap_2d_bf16(&p.tmA, x, Cin, p.M, (uint64_t)Cin * 2, 64, BLOCK_M);
         if (rc) return rc;
+        if (pair) return dispatch_f_pair<false>(p, bn, stream);
         return dispatch_f<AM_TILED, false, 0>(p, bn, stream);
     }
     fill_geom(p.g, (const bf16*)x, H, W, Cin, OH, OW, R, S, stride, pad, GM_FPROP);
@@ -1072,6 +1168,7 @@ extern "C" int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const voi
         if (rc) return rc;
         rc = enable_tma_store(p);
         if (rc) return rc;
+        if (use_pair(p, bn)) return dispatch_f_pair<true>(p, bn, stream);
         return dispatch_f<AM_TILED, true, 0>(p, bn, stream);
     }
     fill_geom(p.g, (const bf16*)dy, OH, OW, Cout, H, W, R, S, stride, pad, GM_DGRAD);
