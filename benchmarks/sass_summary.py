@@ -16,7 +16,7 @@ KEEP = re.compile(r"^(UTC|UTMA|LDTM|STTM|SYNCS|LDGSTS|RED|REDG|UBLKCP|UBLKPF|UCG
 
 def main():
     sass = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True, check=True).stdout
-    names = subprocess.run(["c++filt"], input=sass, capture_output=True, text=True).stdout if False else sass
+    names = sass
     per = collections.OrderedDict()
     cur = None
     for line in names.splitlines():
@@ -37,7 +37,10 @@ def main():
     for (mangled, cnt), name in zip(per.items(), demangled):
         if not cnt:
             continue
-        short = re.sub(r"\(anonymous namespace\)::", "", name.split("(")[0]).replace("void ", "")
+        short = name.replace("(anonymous namespace)::", "").replace("void ", "")
+        cut = short.find(">(")
+        short = short[:cut + 1] if cut >= 0 else short.split("(")[0]
+        short = re.sub(r"\((?:int|bool|unsigned int)\)", "", short)
         rows.append((short, ", ".join(f"{k} x{v}" for k, v in sorted(cnt.items()))))
     for short, body in sorted(rows):
         print(short)
