@@ -118,12 +118,69 @@ class ModelParallelResNet50(ResNet):
         return sd
 
 
-class PipelineParallelResNet50(ModelParallelResNet50):
-    def __init__(self, split_size: int = 20, *args, **kwargs) -> None:
-        super().__init__(*args, **kwargs)
-        self.split_size = split_size
+class _Stage2(nn.Module):
+    """layer3..avgpool + fc as one module (the second pipeline stage)."""
+
+    def __init__(self, seq2: nn.Module, fc: nn.Module) -> None:
+        super().__init__()
+        self.seq2, self.fc = seq2, fc
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        x = self.seq2(x)
+        return self.fc(x.view(x.size(0), -1))
+
+
+class PipelineParallelResNet50(ModelParallelResNet50):
+    """``cuda_graph=True``: in training mode every full-size micro-batch of either stage replays a captured
+    (forward, backward) graph pair (``parallel/graphed.py``) instead of issuing its kernels from Python; graphs are
+    built on the first call for that batch size, an uneven last split runs eagerly."""
+
+    def __init__(self, split_size: int = 20, *args, cuda_graph: bool = False, **kwargs) -> None:
+        super().__init__(*args, **kwargs)
+        self.split_size = split_size
+        self.cuda_graph = cuda_graph and self._on_gpu
+        self._graphs = None          # (n_full, stage-1 GraphedStage, stage-2 GraphedStage)
+
+    def _graphed(self, x: torch.Tensor):
+        from .graphed import GraphedStage
+        n_full = x.size(0) // self.split_size
+        if self._graphs is None or self._graphs[0] != n_full or self._graphs[1].static_in[0].shape[1:] != x.shape[1:]:
+            if n_full == 0:
+                return None
+            sample = x[:self.split_size].detach().to(self.devices[0])
+            g1 = GraphedStage(self.seq1, self.devices[0], sample, n_full, input_requires_grad=False)
+            o = g1.static_out[0]                 # shape / strides of the activation that crosses the boundary
+            act = torch.empty_strided(o.shape, o.stride(), dtype=o.dtype, device=self.devices[1]).normal_()
+            stage2 = _Stage2(self.seq2, self.fc)
+            g2 = GraphedStage(stage2, self.devices[1], act, n_full, input_requires_grad=True)
+            self._graphs = (n_full, g1, g2)
+        return self._graphs
+
+    def _forward_graphed(self, x: torch.Tensor) -> torch.Tensor:
+        n_full, g1, g2 = self._graphs
+        splits = list(x.split(self.split_size, dim=0))
+
+        def stage1(i):
+            s = splits[i]
+            return g1(s, i) if i < n_full else self.seq1(s)
+
+        def stage2(a, i):
+            if i < n_full:
+                return g2(a, i)
+            a = self.seq2(a)
+            return self.fc(a.view(a.size(0), -1))
+
+        ret: List[torch.Tensor] = []
+        prev = self._boundary(stage1(0))
+        for i in range(1, len(splits)):
+            ret.append(stage2(prev, i - 1))
+            prev = self._boundary(stage1(i))
+        ret.append(stage2(prev, len(splits) - 1))
+        return torch.cat(ret)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.cuda_graph and self.training and torch.is_grad_enabled() and self._graphed(x) is not None:
+            return self._forward_graphed(x)
         splits = iter(x.split(self.split_size, dim=0))
         s_next = next(splits)
         s_prev = self._boundary(self.seq1(s_next))

@@ -189,6 +189,53 @@ def test_ddp_p2p_replicas_identical_and_match_nccl_path(world):
     assert p2p[0][2]["iterations"] == 3 and p2p[0][2]["allreduce_launches"] >= 3
 
 
+def test_pipeline_cuda_graph_matches_eager_pipeline():
+    """Graph-replayed pipeline stages (both stages on one GPU here: the graph logic does not care) behave like the
+    eager pipeline, step after step, uneven last split included.
+
+    Deep in a randomly initialised ResNet with 4-image micro-batches the gradients are chaotic: two EAGER runs of
+    the same model on the same batch differ by O(1) there (fp32 atomics land in a different order and 50
+    BatchNorms over 16-element statistics amplify it).  So a second eager model measures that noise per parameter
+    and the graphed model has to stay within a small multiple of it; on top: every gradient present, finite and of
+    the same magnitude - what a missing or doubled accumulation would break."""
+    from pytorchdistributed_b200.ops import functional as K
+    from pytorchdistributed_b200.parallel import PipelineParallelResNet50
+    torch.manual_seed(0)
+    dev = ("cuda:0", "cuda:0")
+    mk = lambda **kw: PipelineParallelResNet50(split_size=4, num_classes=32, devices=dev, transfer="p2p", **kw).train()
+    eager, eager2, graph = mk(), mk(), mk(cuda_graph=True)
+    eager2.load_state_dict(eager.state_dict())
+    graph.load_state_dict(eager.state_dict())
+    models = (eager, eager2, graph)
+    opts = [torch.optim.SGD(m.parameters(), lr=1e-3) for m in models]
+    g = torch.Generator().manual_seed(1)
+    rel = lambda a, b: float((a - b).norm() / (a.norm() + 1e-6))
+    for step in range(3):
+        x = torch.randn(10, 3, 64, 64, generator=g).cuda()            # 4 + 4 + 2: the tail runs eagerly
+        y = torch.randint(0, 32, (10,), generator=g).cuda()
+        losses = []
+        for model, opt in zip(models, opts):
+            opt.zero_grad()
+            loss = K.cross_entropy(model(x), y)
+            loss.backward()
+            losses.append(float(loss.detach()))
+        assert abs(losses[0] - losses[2]) < 3 * abs(losses[0] - losses[1]) + 2e-2 * max(1.0, abs(losses[0])), (step, losses)
+        for (k, pe), p2, pg in zip(eager.named_parameters(), eager2.parameters(), graph.parameters()):
+            assert pg.grad is not None and torch.isfinite(pg.grad).all(), k
+            ne, ng = float(pe.grad.norm()), float(pg.grad.norm())
+            assert 0.4 * ne <= ng <= 2.5 * ne + 1e-6, (step, k, ne, ng)
+            noise = rel(pe.grad, p2.grad)
+            assert rel(pe.grad, pg.grad) < 3 * noise + 0.05, (step, k, noise, rel(pe.grad, pg.grad))
+        for opt in opts:
+            opt.step()
+    assert graph._graphs is not None and graph._graphs[0] == 2
+    sd_e, sd_2, sd_g = eager.state_dict(), eager2.state_dict(), graph.state_dict()
+    for k in sd_e:
+        if "running" in k or "num_batches" in k:        # BatchNorm buffers are updated by the replayed graphs too
+            noise = rel(sd_e[k].float(), sd_2[k].float())
+            assert rel(sd_e[k].float(), sd_g[k].float()) < 3 * noise + 0.05, (k, noise)
+
+
 def test_data_parallel_forward_backward_matches_single_device():
     _need(2)
     from pytorchdistributed_b200.models import MLP
