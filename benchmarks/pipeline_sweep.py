@@ -51,6 +51,10 @@ def main():
     ap.add_argument("--repeat", type=int, default=5)
     ap.add_argument("--splits", default=",".join(map(str, SPLITS)))
     ap.add_argument("--out", default=None)
+    ap.add_argument("--graph", action="store_true", help="ours: pipeline stages replayed from CUDA graphs")
+    ap.add_argument("--prewarm", action="store_true",
+                    help="build each model once and run one untimed train() before the timed repetitions (steady "
+                         "state: allocator warm, graphs captured) instead of the notebook's fresh model per repetition")
     args = ap.parse_args()
     assert torch.cuda.device_count() >= 2, "needs 2 GPUs"
     splits = [int(s) for s in args.splits.split(",") if s]
@@ -80,13 +84,21 @@ def main():
 
         builders = {"single": lambda: resnet50(num_classes=NUM_CLASSES).to("cuda:0"),
                     "model_parallel": lambda: ModelParallelResNet50(),
-                    **{f"pipeline_{k}": (lambda k=k: PipelineParallelResNet50(split_size=k)) for k in splits}}
+                    **{f"pipeline_{k}": (lambda k=k: PipelineParallelResNet50(split_size=k, cuda_graph=args.graph))
+                       for k in splits}}
 
     results = {}
     for name, build in builders.items():
         wall, synced = [], []
+        kept = None
         for rep in range(args.repeat + 1):
-            model = build()
+            if args.prewarm:
+                if kept is None:
+                    kept = build()
+                    train(kept)              # untimed: allocator, kernel attributes, graph capture
+                model = kept
+            else:
+                model = build()
             torch.cuda.synchronize("cuda:0"); torch.cuda.synchronize("cuda:1")
             t0 = time.perf_counter()
             train(model)
@@ -97,13 +109,15 @@ def main():
                 wall.append(t1 - t0)
                 synced.append(t2 - t0)
             del model
+        kept = None
         results[name] = {"wall_s_mean": statistics.mean(wall), "wall_s_std": statistics.pstdev(wall),
                          "synced_s_mean": statistics.mean(synced), "synced_s_std": statistics.pstdev(synced)}
         print(f"{args.impl:9s} {name:16s} train() = {results[name]['synced_s_mean']:.4f} s synced "
               f"(+-{results[name]['synced_s_std']:.4f}), {results[name]['wall_s_mean']:.4f} s host wall  "
               f"[{results[name]['synced_s_mean'] / NUM_EPOCH * 1e3:.1f} ms/iter]", flush=True)
     if args.out:
-        json.dump({"impl": args.impl, "batch": BATCH, "img": IMG, "iters_per_train": NUM_EPOCH, "results": results},
+        json.dump({"impl": args.impl, "graph": args.graph, "prewarm": args.prewarm, "batch": BATCH, "img": IMG,
+                   "iters_per_train": NUM_EPOCH, "results": results},
                   open(args.out, "w"), indent=1)
 
 
