@@ -37,6 +37,9 @@ _SIGS: dict[str, list] = {
     "ptd_bn_stats": [P, P, P, L, I, P],
     "ptd_bn_apply": [P, P, P, P, P, P, P, P, P, P, P, L, I, F, F, I, P],
     "ptd_bn_apply_mask": [P, P, P, P, P, P, P, P, P, P, P, P, L, I, F, F, I, P],
+    "ptd_bn_apply_dual": [P] * 20 + [L, I, F, F, P],
+    "ptd_bn_bwd_dual": [P] * 14 + [L, I, P],
+    "ptd_conv_dgrad_masked_addend": [P, P, P, P, P, I, I, I, I, I, P],
     "ptd_bn_relu_maxpool_fwd": [P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, F, F, P],
     "ptd_bn_relu_maxpool_bwd": [P, P, P, P, P, P, P, P, I, I, I, I, P],
     "ptd_affine_act": [P, P, P, P, P, L, I, I, P],

@@ -279,6 +279,55 @@ def test_bn_relu_bit_mask_equals_mask_from_z(c, res):
             assert _rel(ta, tb) < 1e-4
 
 
+def test_dual_bn_forward_backward():
+    """z = relu(bn(y) + bn2(y2)) in one kernel, and the joint backward of both BatchNorms, against torch fp32."""
+    n, c, h = 4, 256, 7
+    y, y2, dz = _act(n, c, h, h, scale=2.0), _act(n, c, h, h, scale=1.5, seed=4), _act(n, c, h, h, seed=6)
+    gam = [torch.rand(c, device=DEV) + 0.5 for _ in range(2)]
+    bet = [torch.randn(c, device=DEV) * 0.2 for _ in range(2)]
+    rm = [torch.zeros(c, device=DEV) for _ in range(2)]
+    rv = [torch.ones(c, device=DEV) for _ in range(2)]
+    st, st2 = K.bn_stats_raw(y), K.bn_stats_raw(y2)
+    z = torch.empty_like(y)
+    mask = torch.empty(n * h * h, c // 8, device=DEV, dtype=torch.uint8)
+    sv, sv2 = torch.empty(2, c, device=DEV), torch.empty(2, c, device=DEV)
+    m = n * h * h
+    _lib.call("ptd_bn_apply_dual", y, y2, z, mask, st[0], st[1], gam[0], bet[0], rm[0], rv[0], sv[0], sv[1],
+              st2[0], st2[1], gam[1], bet[1], rm[1], rv[1], sv2[0], sv2[1], m, c, 1e-5, 0.1, K._stream())
+    yf, y2f = y.float().requires_grad_(), y2.float().requires_grad_()
+    g = [t.clone().requires_grad_() for t in gam]
+    b = [t.clone().requires_grad_() for t in bet]
+    rmr, rvr = [torch.zeros(c, device=DEV) for _ in range(2)], [torch.ones(c, device=DEV) for _ in range(2)]
+    zr = F.relu(F.batch_norm(yf, rmr[0], rvr[0], g[0], b[0], True, 0.1, 1e-5) +
+                F.batch_norm(y2f, rmr[1], rvr[1], g[1], b[1], True, 0.1, 1e-5))
+    assert _rel(z, zr) < 1e-2
+    for i in range(2):
+        assert _rel(rm[i], rmr[i]) < 1e-3 and _rel(rv[i], rvr[i]) < 1e-3
+    sums, sums2 = torch.zeros(2, c, device=DEV), torch.zeros(2, c, device=DEV)
+    dy, dy2 = torch.empty_like(y), torch.empty_like(y)
+    _lib.call("ptd_bn_bwd_dual", dz, mask, y, y2, sv[0], sv[1], gam[0], sv2[0], sv2[1], gam[1], sums, sums2, dy, dy2,
+              m, c, K._stream())
+    zr.backward(dz.float())
+    assert _rel(dy, yf.grad) < 2e-2 and _rel(dy2, y2f.grad) < 2e-2
+    assert _rel(sums[1], g[0].grad) < 2e-2 and _rel(sums[0], b[0].grad) < 2e-2
+    assert _rel(sums2[1], g[1].grad) < 2e-2 and _rel(sums2[0], b[1].grad) < 2e-2
+
+
+def test_dgrad_with_gated_addend():
+    """dx = dy * W + (mask bit ? addend : 0) for a 1x1 convolution (identity-branch gradient behind a ReLU)."""
+    n, cin, cout, h = 3, 256, 64, 14
+    w = _wt(cout, cin, 1)
+    dy, addend = _act(n, cout, h, h, seed=3), _act(n, cin, h, h, seed=5)
+    keep = torch.rand(n, h, h, cin, device=DEV) > 0.4
+    bits = (keep.reshape(-1, cin // 8, 8).to(torch.int32) << torch.arange(8, device=DEV, dtype=torch.int32)).sum(-1)
+    mask = bits.to(torch.uint8).contiguous()
+    dx = torch.empty_like(addend)
+    _lib.call("ptd_conv_dgrad_masked_addend", dy, w, dx, addend, mask, n, h, h, cin, cout, K._stream())
+    ref = torch.nn.grad.conv2d_input((n, cin, h, h), w.float(), dy.float()) + \
+        addend.float() * keep.permute(0, 3, 1, 2).float()
+    assert _rel(dx, ref) < 1e-2
+
+
 def test_conv_bn_act_fused_matches_unfused():
     x, c = _act(4, 64, 16, 16), 128
     w = _wt(c, 64, 3).float().contiguous(memory_format=CL).requires_grad_()
