@@ -48,6 +48,23 @@ def main(path, title=""):
         for n, s, dd in sorted(lines, key=lambda x: -x[0])[:8]:
             top = max(dd.items(), key=lambda kv: kv[1])
             print(f"  {n:6d}  {s[:78]:78s} {top[0][6:]}")
+    if len(rows) > 3:
+        print("all kernels in this report (us, DRAM % of peak, tensor pipe % active, L1/LSU % of peak):")
+        ix = {n: i for i, n in enumerate(hdr)}
+        cols = ["gpu__time_duration.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+                "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+                "l1tex__throughput.avg.pct_of_peak_sustained_elapsed"]
+        for r in rows[2:]:
+            if len(r) < len(hdr):
+                continue
+            name = r[ix["Kernel Name"]].replace("void <unnamed>::", "").split("(")[0]
+            nums = []
+            for c in cols:
+                try:
+                    nums.append(f"{float(r[ix[c]].replace(',', '')):8.1f}")
+                except (KeyError, ValueError):
+                    nums.append("       -")
+            print(f"  {name:44s} " + " ".join(nums))
     print()
 
 
