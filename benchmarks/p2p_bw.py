@@ -43,8 +43,8 @@ def main():
                       f"all-reduce {t_a:8.1f} us = {mb * 1.048576 * (world - 1) / world / t_a * 1e3:7.1f} GB/s per direction per GPU", flush=True)
         # one-directional pushes / pulls between rank 0 and rank 1 (every rank does the same towards its neighbour)
         from pytorchdistributed_b200 import _lib
-        sb = be._sym(buf)
-        peer = sb.ptrs[(rank + 1) % world]
+        reg, off = be._loc(buf)
+        peer = reg.ptrs[(rank + 1) % world] + off
         local2 = torch.empty(n, dtype=torch.float32, device=dev)
         st = torch.cuda.current_stream(dev).cuda_stream
         nbytes = n * 4

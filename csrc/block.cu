@@ -66,6 +66,22 @@ bool overlap_enabled() {
     return v == 1;
 }
 
+// dst[k][i] += src[off_k + i]: adds the per-unit [dbeta | dgamma] sums of one block into up to 8 gradient tensors
+// (DDP bucket views) with one launch.
+struct ScatterAdd {
+    const float* src;
+    float* dst[8];
+    int off[8];
+    int n[8];
+};
+__global__ void __launch_bounds__(256) scatter_add_kernel(ScatterAdd s) {
+    const int k = blockIdx.y;
+    float* dst = s.dst[k];
+    if (dst == nullptr) return;
+    const float* src = s.src + s.off[k];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < s.n[k]; i += gridDim.x * blockDim.x) dst[i] += src[i];
+}
+
 }  // namespace
 
 extern "C" int ptd_bottleneck_fwd(const PtdBottleneckFwd* d, void* stream) {
@@ -119,7 +135,7 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
     for (int i = 0; i < nu; ++i) off[i + 1] = off[i] + 2 * g[i].cout;
     cudaStream_t st = (cudaStream_t)stream;
     PTD_CUDA_CHECK(cudaMemsetAsync(d->sums, 0, (size_t)off[nu] * sizeof(float), st));
-    PTD_CUDA_CHECK(cudaMemsetAsync(d->dw_all, 0, (size_t)d->dw_all_bytes, st));
+    if (d->dw_all_bytes > 0) PTD_CUDA_CHECK(cudaMemsetAsync(d->dw_all, 0, (size_t)d->dw_all_bytes, st));
     int rc;
 #define BN_BWD(i, dz_, relu_, gout_)                                                                                   \
     do {                                                                                                               \
@@ -208,6 +224,23 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
         DGRAD(0, d->dx, d->g_id);
     }
     WGRAD(0, d->x);
+    {   // every BN backward of the block has run: hand dbeta / dgamma to their gradient tensors
+        ScatterAdd sa;
+        bool any = false;
+        sa.src = d->sums;
+        for (int i = 0; i < 4; ++i)
+            for (int j = 0; j < 2; ++j) {
+                const int k = 2 * i + j;
+                sa.dst[k] = i < nu ? d->gdst[k] : nullptr;
+                sa.off[k] = i < nu ? off[i] + j * g[i].cout : 0;
+                sa.n[k] = i < nu ? g[i].cout : 0;
+                any = any || sa.dst[k] != nullptr;
+            }
+        if (any) {
+            scatter_add_kernel<<<dim3(2, 8), 256, 0, st>>>(sa);
+            PTD_CUDA_CHECK(cudaGetLastError());
+        }
+    }
     if (side != nullptr) {          // join: the caller's stream continues only after the last weight gradient
         cudaEvent_t e = side->ev[side->next++ & 15];
         PTD_CUDA_CHECK(cudaEventRecord(e, side->stream));

@@ -894,7 +894,8 @@ extern "C" int ptd_bn_relu_maxpool_bwd(const void* dp, const void* idx, const vo
 // routine it calls (cudaGetSymbolAddress, cudaMemsetAsync, cudaMemcpyAsync and kernel launches only).
 //
 // Limit: 2048 channels (2 * 2048 floats = 16 KiB, held by every GPU that loads the library until it exits).
-// A wider layer is refused with an error instead of silently overrunning the array.
+// A wider layer is refused with an error instead of silently overrunning the array.  Like every BN kernel of this
+// library the channel count must also be a power of two, 64 at least (64, 128, ..., 2048).
 //
 // In host code the array's name is only a host-side handle, not a device address - a kernel handed the name
 // would fault (or quietly touch the wrong memory on a system where the GPU can reach host memory).  The real
@@ -942,6 +943,13 @@ extern "C" int ptd_bn_backward_static(const void* dz, const void* z, const void*
                 "ptd_bn_bwd_apply with your own 2*C-float scratch instead", C, BN_STATIC_MAX_C);
     PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
     PTD_REQUIRE(dgamma != nullptr && dbeta != nullptr && dy != nullptr, "bn_backward_static: dy, dgamma and dbeta are required");
+    PTD_REQUIRE(relu == 0 || relu == 1,
+                "bn_backward_static: relu must be 0 or 1 (got %d); the bit-mask mode (2) of ptd_bn_bwd_reduce/apply is not "
+                "offered here", relu);
+    PTD_REQUIRE(M > 0, "bn_backward_static: M (%lld rows) must be positive", M);
+    PTD_REQUIRE(dz != nullptr && y != nullptr && mean != nullptr && invstd != nullptr && gamma != nullptr,
+                "bn_backward_static: dz, y, mean, invstd and gamma are required");
+    PTD_REQUIRE(!relu || z != nullptr, "bn_backward_static: relu = 1 needs z (the activation the ReLU mask is taken from)");
     float* sums = nullptr;
     int rc = bn_static_sums_ptr(&sums);
     if (rc) return rc;

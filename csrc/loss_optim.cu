@@ -95,9 +95,12 @@ struct TensorEntry {
 };
 constexpr int OPT_CHUNK = 8192;   // elements per block
 
+// lr_dev (optional): the learning rate read from device memory instead of the launch argument, so that a step that
+// was captured into a CUDA graph follows a schedule (the host rewrites one float between replays).
 __global__ void __launch_bounds__(256)
 multi_sgd_kernel(const TensorEntry* __restrict__ tab, const int2* __restrict__ blockmap, float lr, float momentum,
-                 float weight_decay, float grad_scale, int first_step) {
+                 float weight_decay, float grad_scale, int first_step, const float* __restrict__ lr_dev) {
+    if (lr_dev != nullptr) lr = *lr_dev;
     const int2 bm = blockmap[blockIdx.x];
     const TensorEntry e = tab[bm.x];
     const long long base = (long long)bm.y * OPT_CHUNK;
@@ -116,9 +119,21 @@ multi_sgd_kernel(const TensorEntry* __restrict__ tab, const int2* __restrict__ b
     }
 }
 
+// Adam's step count lives on the device when step_dev is given: adam_advance_kernel increments it (one thread, before
+// the update kernel on the same stream) and every block derives the bias corrections from it.  A host-side count would
+// be frozen at capture time inside a CUDA graph - the corrections would never decay (torch: capturable=True).
+__global__ void adam_advance_kernel(int* step_dev) { *step_dev += 1; }
+
 __global__ void __launch_bounds__(256)
 multi_adam_kernel(const TensorEntry* __restrict__ tab, const int2* __restrict__ blockmap, float lr, float beta1,
-                  float beta2, float eps, float weight_decay, float bias1, float bias2_sqrt, float grad_scale) {
+                  float beta2, float eps, float weight_decay, float bias1, float bias2_sqrt, float grad_scale,
+                  const int* __restrict__ step_dev, const float* __restrict__ lr_dev) {
+    if (lr_dev != nullptr) lr = *lr_dev;
+    if (step_dev != nullptr) {
+        const float t = (float)*step_dev;
+        bias1 = 1.f - powf(beta1, t);
+        bias2_sqrt = sqrtf(1.f - powf(beta2, t));
+    }
     const int2 bm = blockmap[blockIdx.x];
     const TensorEntry e = tab[bm.x];
     const long long base = (long long)bm.y * OPT_CHUNK;
@@ -185,7 +200,17 @@ extern "C" int ptd_multi_sgd(const void* table, const void* blockmap, int n_bloc
                              float weight_decay, float grad_scale, int first_step, void* stream) {
     if (n_blocks <= 0) return PTD_OK;
     multi_sgd_kernel<<<n_blocks, 256, 0, (cudaStream_t)stream>>>((const TensorEntry*)table, (const int2*)blockmap, lr,
-                                                                 momentum, weight_decay, grad_scale, first_step);
+                                                                 momentum, weight_decay, grad_scale, first_step, nullptr);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+// Same, with the learning rate in device memory (lr_dev: one float) - what a CUDA-graph-captured step uses.
+extern "C" int ptd_multi_sgd_dev(const void* table, const void* blockmap, int n_blocks, const float* lr_dev,
+                                 float momentum, float weight_decay, float grad_scale, int first_step, void* stream) {
+    if (n_blocks <= 0) return PTD_OK;
+    PTD_REQUIRE(lr_dev != nullptr, "multi_sgd_dev: lr_dev is required");
+    multi_sgd_kernel<<<n_blocks, 256, 0, (cudaStream_t)stream>>>((const TensorEntry*)table, (const int2*)blockmap, 0.f,
+                                                                 momentum, weight_decay, grad_scale, first_step, lr_dev);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }
@@ -196,7 +221,22 @@ extern "C" int ptd_multi_adam(const void* table, const void* blockmap, int n_blo
     const float bias2_sqrt = sqrtf(1.f - powf(beta2, (float)step));
     multi_adam_kernel<<<n_blocks, 256, 0, (cudaStream_t)stream>>>((const TensorEntry*)table, (const int2*)blockmap, lr,
                                                                   beta1, beta2, eps, weight_decay, bias1, bias2_sqrt,
-                                                                  grad_scale);
+                                                                  grad_scale, nullptr, nullptr);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+// Adam with its step count (step_dev: one int, incremented here before the update) and learning rate (lr_dev: one
+// float) in device memory: replaying a captured step advances the bias corrections like an eager step does.
+extern "C" int ptd_multi_adam_dev(const void* table, const void* blockmap, int n_blocks, const float* lr_dev, float beta1,
+                                  float beta2, float eps, float weight_decay, int* step_dev, float grad_scale,
+                                  void* stream) {
+    PTD_REQUIRE(lr_dev != nullptr && step_dev != nullptr, "multi_adam_dev: lr_dev and step_dev are required");
+    adam_advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_dev);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    if (n_blocks <= 0) return PTD_OK;
+    multi_adam_kernel<<<n_blocks, 256, 0, (cudaStream_t)stream>>>((const TensorEntry*)table, (const int2*)blockmap, 0.f,
+                                                                  beta1, beta2, eps, weight_decay, 1.f, 1.f, grad_scale,
+                                                                  step_dev, lr_dev);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }

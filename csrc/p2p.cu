@@ -11,6 +11,12 @@
 //   in each direction (its own reads and writes plus serving its peers') - the minimum for an all-reduce
 //   without in-switch reduction - and the kernel needs two flag barriers (inputs ready / outputs complete).  The flatten step of DDP is free (gradients already live in the buffer), the averaging
 //   and the optional bf16 storage format are fused into the same pass.
+//   all-reduce through the switch (NVLS): when the buffer also has a multicast mapping (csrc/vmm.cu), rank r runs
+//   `multimem.ld_reduce` over slice r - the NVSwitch fetches the element from all N copies and returns the fp32 sum -
+//   and `multimem.st`s the scaled result to all N copies.  Each port then carries ~(1 + 1/N) of the buffer per
+//   direction instead of 2(N-1)/N, and the SMs issue one load and one store per 16 bytes instead of N of each.
+//   bf16 wire format: fp32 gradients are cast (pre-scaled by 1/N) into a bf16 staging buffer, reduced there by
+//   either path (fp32 accumulation), and cast back - all three phases in ONE kernel, half the NVLink bytes.
 //   broadcast: non-root ranks pull the root's buffer.    reduce-to-root / peer copy: used by the
 //   single-process DataParallel wrapper (replicate, gather, gradient reduction).
 //
@@ -28,9 +34,21 @@ constexpr int MAX_WORLD = 8;
 constexpr int MAX_BLOCKS = 128;
 constexpr int AR_THREADS = 512;
 
+// Signal pad layout (uint32 words), one pad per rank and channel:
+//   [0 ..)            MAX_BLOCKS x MAX_WORLD arrival flags written by the peers (flag barrier)
+//   [PAD_SEQ ..)      MAX_BLOCKS local sequence counters of the flag barrier
+//   [PAD_MC_CNT ..)   MAX_BLOCKS arrival counters incremented by every rank with ONE multimem.red (switch barrier)
+//   [PAD_MC_EPOCH ..) MAX_BLOCKS local counts of switch barriers passed
+constexpr int PAD_SEQ = MAX_BLOCKS * MAX_WORLD;
+constexpr int PAD_MC_CNT = PAD_SEQ + MAX_BLOCKS;
+constexpr int PAD_MC_EPOCH = PAD_MC_CNT + MAX_BLOCKS;
+constexpr int PAD_WORDS = PAD_MC_EPOCH + MAX_BLOCKS;
+
 struct PeerPtrs {
     void* buf[MAX_WORLD];
     uint32_t* pad[MAX_WORLD];
+    uint32_t* mc_pad;                 // multicast mapping of the pads (nullptr: flag barrier over the unicast mappings)
+    unsigned long long timeout_ns;    // a barrier that waits longer than this reports the missing peer and traps
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -54,12 +72,12 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 // replayable from a CUDA graph (a host-side sequence argument would be frozen at capture time).
 __device__ __forceinline__ uint32_t seq_begin(const PeerPtrs& pp, int rank) {
     __shared__ uint32_t s_seq;
-    if (threadIdx.x == 0) s_seq = pp.pad[rank][MAX_BLOCKS * MAX_WORLD + blockIdx.x];
+    if (threadIdx.x == 0) s_seq = pp.pad[rank][PAD_SEQ + blockIdx.x];
     __syncthreads();
     return s_seq + 1;
 }
 __device__ __forceinline__ void seq_end(const PeerPtrs& pp, int rank, uint32_t last_used) {
-    if (threadIdx.x == 0) pp.pad[rank][MAX_BLOCKS * MAX_WORLD + blockIdx.x] = last_used;
+    if (threadIdx.x == 0) pp.pad[rank][PAD_SEQ + blockIdx.x] = last_used;
 }
 
 // Block-level barrier across ranks: block b of every rank meets block b of every other rank.
@@ -73,13 +91,67 @@ __device__ __forceinline__ void rank_barrier(const PeerPtrs& pp, int rank, int w
         const uint32_t* mine = pp.pad[rank] + blockIdx.x * MAX_WORLD + peer;
         const unsigned long long t0 = global_timer_ns();
         while ((int32_t)(ld_acquire_sys(mine) - seq) < 0) {
-            if (global_timer_ns() - t0 > 20ull * 1000 * 1000 * 1000) {      // 20 s: a peer died; do not hang the GPU
+            if (global_timer_ns() - t0 > pp.timeout_ns) {      // a peer died or never launched: do not hang the GPU
                 printf("ptd: rank %d block %d timed out waiting for rank %d (seq %u)\n", rank, blockIdx.x, peer, seq);
                 __trap();
             }
         }
     }
     __syncthreads();
+}
+
+// ---- multimem (NVLS) primitives: the address is a multicast mapping, the NVSwitch does the fan-out / reduction ----
+__device__ __forceinline__ float4 mm_ld_reduce_f32x4(const void* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mm_st_f32x4(void* mc, const float4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// 8 bf16 per access, summed in fp32 inside the switch, rounded once on the way back
+__device__ __forceinline__ uint4 mm_ld_reduce_bf16x8(const void* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mm_st_b32x4(void* mc, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 ::"l"(mc), "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)),
+                   "f"(__uint_as_float(v.w)) : "memory");
+}
+
+// Switch barrier: every rank adds 1 to the same counter word of ALL pads with one multimem.red (release), then
+// waits until its own copy has seen `world` arrivals for this epoch.  One store through the switch instead of N
+// remote stores; the epoch count lives next to the counter so a captured graph can replay it.
+__device__ __forceinline__ void rank_barrier_mc(const PeerPtrs& pp, int rank, int world) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t* local = pp.pad[rank];
+        const uint32_t epoch = local[PAD_MC_EPOCH + blockIdx.x] + 1;
+        local[PAD_MC_EPOCH + blockIdx.x] = epoch;
+        __threadfence_system();
+        asm volatile("multimem.red.release.sys.global.add.u32 [%0], %1;" ::"l"(pp.mc_pad + PAD_MC_CNT + blockIdx.x), "r"(1u)
+                     : "memory");
+        const uint32_t target = epoch * (uint32_t)world;
+        const unsigned long long t0 = global_timer_ns();
+        while ((int32_t)(ld_acquire_sys(local + PAD_MC_CNT + blockIdx.x) - target) < 0) {
+            if (global_timer_ns() - t0 > pp.timeout_ns) {
+                printf("ptd: rank %d block %d timed out in the switch barrier (epoch %u)\n", rank, blockIdx.x, epoch);
+                __trap();
+            }
+        }
+    }
+    __syncthreads();
+}
+
+// Either barrier, chosen per launch.  `seq` is only consumed by the flag barrier.
+__device__ __forceinline__ void rank_sync(const PeerPtrs& pp, int rank, int world, uint32_t seq) {
+    if (pp.mc_pad != nullptr) rank_barrier_mc(pp, rank, world);
+    else rank_barrier(pp, rank, world, seq);
 }
 
 __device__ __forceinline__ float4 ld_f4(const float4* p) {
@@ -197,6 +269,145 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_bf16_kernel(PeerPtrs pp,
     seq_end(pp, rank, seq + 1);
 }
 
+// ---- all-reduce through the switch (NVLS), in place, fp32 or bf16 storage --------------------------------------
+// mc = multicast mapping of the buffer; nvec = 16-byte vectors.  Rank r reduces slice r: one multimem.ld_reduce (the
+// switch sums the N copies in fp32) and one multimem.st (the switch writes all N copies) per vector.
+template <bool BF16>
+__global__ void __launch_bounds__(AR_THREADS) allreduce_mc_kernel(PeerPtrs pp, uint4* mc, int rank, int world,
+                                                                  long long nvec, float scale) {
+    const uint32_t seq = seq_begin(pp, rank);
+    rank_sync(pp, rank, world, seq);                    // every rank's contribution is final
+    const long long per = (nvec + world - 1) / world;
+    const long long begin = min(nvec, per * rank), end = min(nvec, begin + per);
+    const long long stride = (long long)gridDim.x * AR_THREADS;
+    constexpr int UNROLL = 4;
+    const bool rescale = scale != 1.f;
+    long long i = begin + (long long)blockIdx.x * AR_THREADS + threadIdx.x;
+    for (; i + (UNROLL - 1) * stride < end; i += UNROLL * stride) {
+        if (BF16) {
+            uint4 v[UNROLL];
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) v[u] = mm_ld_reduce_bf16x8(mc + i + u * stride);
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+                if (rescale) {
+                    uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) { const float2 f = unpack_bf16x2(w[k]); w[k] = pack_bf16x2(f.x * scale, f.y * scale); }
+                    v[u] = make_uint4(w[0], w[1], w[2], w[3]);
+                }
+                mm_st_b32x4(mc + i + u * stride, v[u]);
+            }
+        } else {
+            float4 v[UNROLL];
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) v[u] = mm_ld_reduce_f32x4(mc + i + u * stride);
+#pragma unroll
+            for (int u = 0; u < UNROLL; ++u) {
+                v[u].x *= scale; v[u].y *= scale; v[u].z *= scale; v[u].w *= scale;
+                mm_st_f32x4(mc + i + u * stride, v[u]);
+            }
+        }
+    }
+    for (; i < end; i += stride) {
+        if (BF16) {
+            uint4 v = mm_ld_reduce_bf16x8(mc + i);
+            if (rescale) {
+                uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { const float2 f = unpack_bf16x2(w[k]); w[k] = pack_bf16x2(f.x * scale, f.y * scale); }
+                v = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            mm_st_b32x4(mc + i, v);
+        } else {
+            float4 v = mm_ld_reduce_f32x4(mc + i);
+            v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
+            mm_st_f32x4(mc + i, v);
+        }
+    }
+    rank_sync(pp, rank, world, seq + 1);                // every rank's stores have landed everywhere
+    seq_end(pp, rank, seq + 1);
+}
+
+// ---- all-reduce of an fp32 buffer with a bf16 wire format, one kernel, three phases ----------------------------
+//   A  every rank casts scale * grad (fp32, local) into its bf16 staging buffer (symmetric);
+//   B  rank r reduces slice r of the staging buffers - through the switch (MC) or by loading it from all N copies -
+//      with fp32 accumulation, rounds once, and stores the bf16 result into all N staging buffers;
+//   C  every rank casts its (now complete) staging buffer back into the fp32 buffer.
+// Only block-level rank barriers are needed although A and C run inside the kernel: block b of every rank handles
+// the SAME vector indices of every slice in all three phases, so what block b of rank r reads in B was written in A
+// by block b of the peers (and likewise for C).  pp.buf = the staging buffers; n8 = vectors of 8 elements.
+// Half the NVLink bytes of the fp32 kernels; results are identical on every rank (the slice owner rounds).
+template <int WORLD, bool MC>
+__global__ void __launch_bounds__(AR_THREADS) allreduce_wire_bf16_kernel(PeerPtrs pp, uint4* mc_stage, float4* grad,
+                                                                         int rank, long long n8, float scale) {
+    const uint32_t seq = seq_begin(pp, rank);
+    const long long per = (n8 + WORLD - 1) / WORLD;
+    const long long stride = (long long)gridDim.x * AR_THREADS;
+    const long long t0 = (long long)blockIdx.x * AR_THREADS + threadIdx.x;
+    uint4* stage = reinterpret_cast<uint4*>(pp.buf[rank]);
+    // A: (the previous collective on this pad ended with a barrier, so no peer still reads our staging buffer)
+    for (int s = 0; s < WORLD; ++s) {
+        const long long b = min(n8, per * s), e = min(n8, b + per);
+        for (long long i = b + t0; i < e; i += stride) {
+            const float4 lo = grad[2 * i], hi = grad[2 * i + 1];
+            uint4 o;
+            o.x = pack_bf16x2(lo.x * scale, lo.y * scale); o.y = pack_bf16x2(lo.z * scale, lo.w * scale);
+            o.z = pack_bf16x2(hi.x * scale, hi.y * scale); o.w = pack_bf16x2(hi.z * scale, hi.w * scale);
+            stage[i] = o;
+        }
+    }
+    rank_sync(pp, rank, WORLD, seq);
+    // B
+    {
+        const long long b = min(n8, per * rank), e = min(n8, b + per);
+        if (MC) {
+            long long i = b + t0;
+            for (; i + 3 * stride < e; i += 4 * stride) {
+                uint4 v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = mm_ld_reduce_bf16x8(mc_stage + i + u * stride);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) mm_st_b32x4(mc_stage + i + u * stride, v[u]);
+            }
+            for (; i < e; i += stride) mm_st_b32x4(mc_stage + i, mm_ld_reduce_bf16x8(mc_stage + i));
+        } else {
+            for (long long i = b + t0; i < e; i += stride) {
+                uint4 v[WORLD];
+#pragma unroll
+                for (int r = 0; r < WORLD; ++r) v[r] = ld_u4(reinterpret_cast<const uint4*>(pp.buf[(rank + r) % WORLD]) + i);
+                float acc[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+#pragma unroll
+                for (int r = 0; r < WORLD; ++r) {
+                    const uint32_t w[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) { const float2 f = unpack_bf16x2(w[k]); acc[2 * k] += f.x; acc[2 * k + 1] += f.y; }
+                }
+                const uint4 o = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]),
+                                           pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7]));
+#pragma unroll
+                for (int r = 0; r < WORLD; ++r) st_u4(reinterpret_cast<uint4*>(pp.buf[(rank + r) % WORLD]) + i, o);
+            }
+        }
+    }
+    rank_sync(pp, rank, WORLD, seq + 1);
+    // C: system-scope loads - the lines were written by peers (or the switch) while this SM may hold stale copies
+    for (int s = 0; s < WORLD; ++s) {
+        const long long b = min(n8, per * s), e = min(n8, b + per);
+        for (long long i = b + t0; i < e; i += stride) {
+            const uint4 v = ld_u4(stage + i);
+            const float2 a = unpack_bf16x2(v.x), bq = unpack_bf16x2(v.y), c = unpack_bf16x2(v.z), d = unpack_bf16x2(v.w);
+            grad[2 * i] = make_float4(a.x, a.y, bq.x, bq.y);
+            grad[2 * i + 1] = make_float4(c.x, c.y, d.x, d.y);
+        }
+    }
+    // The next collective on this pad starts with phase A writing the staging buffer that peers read in B: it may not
+    // begin before every peer is past B.  They are: barrier seq + 1 above is only passed once all ranks finished B.
+    seq_end(pp, rank, seq + 1);
+}
+
 // ---- broadcast: every non-root rank pulls the root's buffer ----------------------------------------------
 __global__ void __launch_bounds__(AR_THREADS) broadcast_pull_kernel(PeerPtrs pp, int rank, int world, int root,
                                                                     long long n16) {
@@ -214,6 +425,27 @@ __global__ void __launch_bounds__(AR_THREADS) broadcast_pull_kernel(PeerPtrs pp,
         for (; i < n16; i += stride) dst[i] = ld_u4(src + i);
     }
     rank_barrier(pp, rank, world, seq + 1);             // root may overwrite its buffer again
+    seq_end(pp, rank, seq + 1);
+}
+
+// ---- broadcast through the switch: the root stores every vector ONCE with multimem.st, the NVSwitch writes all N copies
+// (the root's port carries the message once instead of N-1 times as with the pull kernel above) ---------------------
+__global__ void __launch_bounds__(AR_THREADS) broadcast_mc_kernel(PeerPtrs pp, uint4* mc, int rank, int world, int root,
+                                                                  long long n16) {
+    const uint32_t seq = seq_begin(pp, rank);
+    rank_sync(pp, rank, world, seq);                    // nobody still reads the previous contents of its copy
+    if (rank == root) {
+        const uint4* src = reinterpret_cast<const uint4*>(pp.buf[rank]);
+        const long long stride = (long long)gridDim.x * AR_THREADS;
+        long long i = (long long)blockIdx.x * AR_THREADS + threadIdx.x;
+        for (; i + 3 * stride < n16; i += 4 * stride) {
+            const uint4 v0 = src[i], v1 = src[i + stride], v2 = src[i + 2 * stride], v3 = src[i + 3 * stride];
+            mm_st_b32x4(mc + i, v0); mm_st_b32x4(mc + i + stride, v1);
+            mm_st_b32x4(mc + i + 2 * stride, v2); mm_st_b32x4(mc + i + 3 * stride, v3);
+        }
+        for (; i < n16; i += stride) mm_st_b32x4(mc + i, src[i]);
+    }
+    rank_sync(pp, rank, world, seq + 1);                // the root's stores have landed everywhere
     seq_end(pp, rank, seq + 1);
 }
 
@@ -362,37 +594,103 @@ __global__ void __launch_bounds__(32) bulk_copy_kernel(uint8_t* __restrict__ dst
 struct SrcList {
     const float* p[MAX_WORLD];
 };
-// dst[i] = scale * (beta*dst[i] + sum_k src_k[i])
-__global__ void __launch_bounds__(256) reduce_sum_kernel(float* __restrict__ dst, SrcList srcs, int n_src, long long n,
-                                                         float scale, int accumulate) {
+// dst[i] = scale * (accumulate * dst[i] + sum_k src_k[i]).  16-byte accesses, every source's load of a vector issued
+// before the first add (the sources are peer GPUs: what limits the kernel is bytes in flight over NVLink), two
+// vectors per thread and iteration.  Scalar tail for n % 4 and for unaligned pointers.
+template <int NSRC>
+__global__ void __launch_bounds__(256) reduce_sum_kernel(float* __restrict__ dst, SrcList srcs, long long n,
+                                                         float scale, int accumulate, int vec_ok) {
     const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        float acc = accumulate ? dst[i] : 0.f;
-        for (int k = 0; k < n_src; ++k) acc += srcs.p[k][i];
-        dst[i] = acc * scale;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long n4 = vec_ok ? n / 4 : 0;
+    float4* d4 = reinterpret_cast<float4*>(dst);
+    long long i = tid;
+    for (; i + stride < n4; i += 2 * stride) {
+        float4 v[NSRC > 0 ? NSRC : 1][2];
+#pragma unroll
+        for (int k = 0; k < NSRC; ++k) {
+            v[k][0] = ld_f4_weak(reinterpret_cast<const float4*>(srcs.p[k]) + i);
+            v[k][1] = ld_f4_weak(reinterpret_cast<const float4*>(srcs.p[k]) + i + stride);
+        }
+        float4 a0 = accumulate ? d4[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 a1 = accumulate ? d4[i + stride] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < NSRC; ++k) {
+            a0.x += v[k][0].x; a0.y += v[k][0].y; a0.z += v[k][0].z; a0.w += v[k][0].w;
+            a1.x += v[k][1].x; a1.y += v[k][1].y; a1.z += v[k][1].z; a1.w += v[k][1].w;
+        }
+        d4[i] = make_float4(a0.x * scale, a0.y * scale, a0.z * scale, a0.w * scale);
+        d4[i + stride] = make_float4(a1.x * scale, a1.y * scale, a1.z * scale, a1.w * scale);
     }
+    for (; i < n4; i += stride) {
+        float4 a = accumulate ? d4[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int k = 0; k < NSRC; ++k) {
+            const float4 v = ld_f4_weak(reinterpret_cast<const float4*>(srcs.p[k]) + i);
+            a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+        }
+        d4[i] = make_float4(a.x * scale, a.y * scale, a.z * scale, a.w * scale);
+    }
+    for (long long j = n4 * 4 + tid; j < n; j += stride) {
+        float acc = accumulate ? dst[j] : 0.f;
+#pragma unroll
+        for (int k = 0; k < NSRC; ++k) acc += srcs.p[k][j];
+        dst[j] = acc * scale;
+    }
+}
+
+int env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
 }
 
 int pick_blocks(long long work_items, int requested) {
     if (requested > 0) return requested > MAX_BLOCKS ? MAX_BLOCKS : requested;
     long long b = (work_items + AR_THREADS * 4 - 1) / (AR_THREADS * 4);
     if (b < 1) b = 1;
-    // enough loads in flight to fill NVLink (measured: 32 CTAs 455 GB/s, 64 CTAs 700, 128 CTAs 715 on a pull);
-    // bucket-sized messages leave more SMs to the overlapping backward kernels
-    const long long cap = work_items >= (1ll << 20) ? 128 : 96;
+    // enough loads in flight to fill NVLink (measured: 32 CTAs 455 GB/s, 64 CTAs 700, 128 CTAs 715 on a pull)
+    static int cap = -1;
+    if (cap < 0) cap = env_int("PTDB200_AR_MAX_BLOCKS", 128);
     if (b > cap) b = cap;
     return (int)b;
 }
 
-int fill_peers(PeerPtrs& pp, const void* const* bufs, const void* const* pads, int world) {
+// Through the switch the SMs issue one load and one store per vector (not N of each): fewer CTAs saturate the
+// port, and every CTA not taken is an SM left to the backward kernels the all-reduce overlaps with.
+int pick_blocks_mc(long long work_items, int requested) {
+    if (requested > 0) return requested > MAX_BLOCKS ? MAX_BLOCKS : requested;
+    long long b = (work_items + AR_THREADS * 4 - 1) / (AR_THREADS * 4);
+    if (b < 1) b = 1;
+    static int cap = -1;
+    if (cap < 0) cap = env_int("PTDB200_MC_MAX_BLOCKS", 48);
+    if (b > cap) b = cap;
+    return (int)b;
+}
+
+unsigned long long barrier_timeout_ns() {
+    static unsigned long long v = 0;
+    if (v == 0) {
+        // Long enough for a peer that is still capturing a graph, loading data or writing a checkpoint; a dead peer
+        // is reported after this time instead of hanging the GPU forever.
+        const char* e = getenv("PTDB200_P2P_TIMEOUT_S");
+        double sec = e ? atof(e) : 600.0;
+        if (sec < 0.001) sec = 0.001;
+        v = (unsigned long long)(sec * 1e9);
+    }
+    return v;
+}
+
+int fill_peers(PeerPtrs& pp, const void* const* bufs, const void* const* pads, int world, const void* mc_pad = nullptr) {
     if (world < 1 || world > MAX_WORLD) {
         ptd_set_error("p2p: world size %d outside [1,%d]", world, MAX_WORLD);
         return PTD_ERR_ARG;
     }
     for (int r = 0; r < MAX_WORLD; ++r) {
-        pp.buf[r] = r < world ? const_cast<void*>(bufs[r]) : nullptr;
+        pp.buf[r] = (r < world && bufs != nullptr) ? const_cast<void*>(bufs[r]) : nullptr;
         pp.pad[r] = r < world ? (uint32_t*)const_cast<void*>(pads[r]) : nullptr;
     }
+    pp.mc_pad = (uint32_t*)const_cast<void*>(mc_pad);
+    pp.timeout_ns = barrier_timeout_ns();
     return PTD_OK;
 }
 
@@ -439,7 +737,7 @@ extern "C" int ptd_p2p_enable_peer_access(int dev, int peer) {
     PTD_CUDA_CHECK(e);
     return PTD_OK;
 }
-extern "C" int ptd_p2p_pad_bytes() { return (MAX_BLOCKS * MAX_WORLD + MAX_BLOCKS) * (int)sizeof(uint32_t); }
+extern "C" int ptd_p2p_pad_bytes() { return PAD_WORDS * (int)sizeof(uint32_t); }
 extern "C" int ptd_p2p_max_blocks() { return MAX_BLOCKS; }
 
 // ---- collectives --------------------------------------------------------------------------------------------
@@ -483,6 +781,20 @@ extern "C" int ptd_broadcast_inplace(const void* const* bufs, const void* const*
     return PTD_OK;
 }
 
+// Broadcast through the switch; bufs = unicast mappings (only the root's own is read), mc_buf = multicast mapping.
+extern "C" int ptd_broadcast_mc(const void* const* bufs, void* mc_buf, const void* const* pads, const void* mc_pad,
+                                int rank, int world, int root, long long nbytes, int blocks, void* stream) {
+    PeerPtrs pp;
+    int rc = fill_peers(pp, bufs, pads, world, mc_pad);
+    if (rc) return rc;
+    PTD_REQUIRE(nbytes % 16 == 0 && mc_buf != nullptr, "broadcast_mc: nbytes (%lld) must be a multiple of 16, mc_buf set", nbytes);
+    PTD_REQUIRE(root >= 0 && root < world, "broadcast_mc: root %d outside the group", root);
+    const int grid = pick_blocks_mc(nbytes / 16, blocks);
+    broadcast_mc_kernel<<<grid, AR_THREADS, 0, (cudaStream_t)stream>>>(pp, (uint4*)mc_buf, rank, world, root, nbytes / 16);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
 // op: 0 all-gather, 1 gather (to root), 2 scatter (from root), 3 reduce-scatter, 4 reduce (to root), 5 one-shot
 // all-reduce (ops 3-5: fp32 data, `scale` applied to the sum).  nbytes a multiple of 16; shard s of the buffer
 // (ceil(nbytes/16/world) vectors) belongs to rank s.  See shard_collective_kernel.
@@ -509,8 +821,7 @@ extern "C" int ptd_shard_collective(const void* const* bufs, const void* const* 
 
 extern "C" int ptd_p2p_barrier(const void* const* pads, int rank, int world, void* stream) {
     PeerPtrs pp;
-    const void* none[MAX_WORLD] = {nullptr};
-    int rc = fill_peers(pp, none, pads, world);
+    int rc = fill_peers(pp, nullptr, pads, world);
     if (rc) return rc;
     barrier_only_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pp, rank, world);
     PTD_CUDA_CHECK(cudaGetLastError());
@@ -553,11 +864,66 @@ extern "C" int ptd_reduce_sum_f32(float* dst, const void* const* srcs, int n_src
                                   int accumulate, void* stream) {
     PTD_REQUIRE(n_src >= 0 && n_src <= MAX_WORLD, "reduce_sum: %d sources (max %d)", n_src, MAX_WORLD);
     SrcList sl;
-    for (int k = 0; k < MAX_WORLD; ++k) sl.p[k] = k < n_src ? (const float*)srcs[k] : nullptr;
-    long long blocks = (numel + 255) / 256;
+    int vec_ok = ((uintptr_t)dst & 15) == 0;
+    for (int k = 0; k < MAX_WORLD; ++k) {
+        sl.p[k] = k < n_src ? (const float*)srcs[k] : nullptr;
+        if (k < n_src && ((uintptr_t)srcs[k] & 15) != 0) vec_ok = 0;
+    }
+    long long blocks = (numel / 4 + 2 * 256 - 1) / (2 * 256);
     if (blocks < 1) blocks = 1;
-    if (blocks > 4LL * ptd_num_sms()) blocks = 4LL * ptd_num_sms();
-    reduce_sum_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(dst, sl, n_src, numel, scale, accumulate);
+    if (blocks > 2LL * ptd_num_sms()) blocks = 2LL * ptd_num_sms();
+    cudaStream_t st = (cudaStream_t)stream;
+#define PTD_RS(K) case K: reduce_sum_kernel<K><<<(int)blocks, 256, 0, st>>>(dst, sl, numel, scale, accumulate, vec_ok); break;
+    switch (n_src) {
+        PTD_RS(0) PTD_RS(1) PTD_RS(2) PTD_RS(3) PTD_RS(4) PTD_RS(5) PTD_RS(6) PTD_RS(7) PTD_RS(8)
+    }
+#undef PTD_RS
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+// ---- NVLS / bf16-wire entry points --------------------------------------------------------------------------
+// In-place all-reduce through the switch.  mc_buf: multicast mapping of the symmetric buffer (csrc/vmm.cu); pads:
+// unicast pads; mc_pad: multicast mapping of the pads (NULL = flag barrier).  scale as in ptd_allreduce_inplace.
+extern "C" int ptd_allreduce_mc(void* mc_buf, const void* const* pads, const void* mc_pad, int rank, int world,
+                                long long numel, int is_bf16, float scale, int blocks, void* stream) {
+    PeerPtrs pp;
+    int rc = fill_peers(pp, nullptr, pads, world, mc_pad);
+    if (rc) return rc;
+    PTD_REQUIRE(mc_buf != nullptr && ((uintptr_t)mc_buf & 15) == 0, "allreduce_mc: needs a 16-byte aligned multicast address");
+    const int per_vec = is_bf16 ? 8 : 4;
+    PTD_REQUIRE(numel % per_vec == 0, "allreduce_mc: numel (%lld) must be a multiple of %d", numel, per_vec);
+    const long long nvec = numel / per_vec;
+    const int grid = pick_blocks_mc((nvec + world - 1) / world, blocks);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (is_bf16) allreduce_mc_kernel<true><<<grid, AR_THREADS, 0, st>>>(pp, (uint4*)mc_buf, rank, world, nvec, scale);
+    else allreduce_mc_kernel<false><<<grid, AR_THREADS, 0, st>>>(pp, (uint4*)mc_buf, rank, world, nvec, scale);
+    PTD_CUDA_CHECK(cudaGetLastError());
+    return PTD_OK;
+}
+
+// All-reduce of the LOCAL fp32 buffer `grad` (numel a multiple of 8) with bf16 on the wire: `stages` are the unicast
+// mappings of a symmetric bf16 staging buffer of at least numel elements, `mc_stage` its multicast mapping (NULL =
+// peers' staging buffers are loaded one by one).  grad <- scale * sum over ranks, rounded to bf16 once per phase.
+extern "C" int ptd_allreduce_wire_bf16(float* grad, const void* const* stages, void* mc_stage, const void* const* pads,
+                                       const void* mc_pad, int rank, int world, long long numel, float scale, int blocks,
+                                       void* stream) {
+    PeerPtrs pp;
+    int rc = fill_peers(pp, stages, pads, world, mc_pad);
+    if (rc) return rc;
+    PTD_REQUIRE(numel % 8 == 0 && ((uintptr_t)grad & 15) == 0, "allreduce_wire_bf16: numel (%lld) %% 8 and a 16-byte aligned buffer", numel);
+    const long long n8 = numel / 8;
+    const int grid = mc_stage ? pick_blocks_mc((n8 + world - 1) / world, blocks) : pick_blocks((n8 + world - 1) / world, blocks);
+    cudaStream_t st = (cudaStream_t)stream;
+#define PTD_WIRE(W)                                                                                                      \
+    case W:                                                                                                              \
+        if (mc_stage) allreduce_wire_bf16_kernel<W, true><<<grid, AR_THREADS, 0, st>>>(pp, (uint4*)mc_stage, (float4*)grad, rank, n8, scale); \
+        else allreduce_wire_bf16_kernel<W, false><<<grid, AR_THREADS, 0, st>>>(pp, nullptr, (float4*)grad, rank, n8, scale);         \
+        break;
+    switch (world) {
+        PTD_WIRE(1) PTD_WIRE(2) PTD_WIRE(3) PTD_WIRE(4) PTD_WIRE(5) PTD_WIRE(6) PTD_WIRE(7) PTD_WIRE(8)
+    }
+#undef PTD_WIRE
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }

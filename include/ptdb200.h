@@ -87,6 +87,10 @@ typedef struct {
     void* dz1;                     /* scratch: gradient w.r.t. z[0] */
     void* dx;                      /* out: gradient w.r.t. x */
     const void* mask[4];           /* the forward's ReLU bit masks; a NULL entry recomputes the mask from z[i] */
+    float* gdst[8];                /* optional: where unit i's dbeta (gdst[2i]) and dgamma (gdst[2i+1]) are ADDED at the end
+                                      of the call (DDP gradient-bucket views); NULL entries are skipped.  With dw[] pointing
+                                      into the buckets as well and dw_all_bytes == 0 the weight-gradient kernels accumulate
+                                      straight into the buckets: no temporary, no AccumulateGrad pass (ddp_gpus.py:41). */
 } PtdBottleneckBwd;
 int ptd_bottleneck_fwd(const PtdBottleneckFwd* d, void* stream);
 int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream);
@@ -140,7 +144,8 @@ int ptd_bn_relu_maxpool_fwd(const void* y, void* p, void* idx, const float* sum,
 int ptd_bn_relu_maxpool_bwd(const void* dp, const void* idx, const void* y, const float* mean, const float* invstd,
                             const float* gamma, float* sums, void* dy, int N, int H, int W, int C, void* stream);
 /* BatchNorm backward (both passes) for callers that must not allocate: the 2*C-float scratch lives in a fixed array
- * inside the library image instead of being passed in.  C <= 2048 (16 KiB per GPU), larger C is rejected.  The first
+ * inside the library image instead of being passed in.  C must be a power of two in [64, 2048] (the cap is what the
+ * 16 KiB-per-GPU array holds), anything else is rejected; relu is 0 or 1 (z = the activation; no bit-mask mode).  The first
  * call on a device looks up the array's address - make it before any stream capture on that device.  All calls share
  * the array: overlapping calls on one device race, order them.  No counterpart in the reference (it has no native
  * code and never manages device memory itself). */
@@ -176,6 +181,13 @@ int ptd_multi_sgd(const void* table, const void* blockmap, int n_blocks, float l
                   float grad_scale, int first_step, void* stream);
 int ptd_multi_adam(const void* table, const void* blockmap, int n_blocks, float lr, float beta1, float beta2, float eps,
                    float weight_decay, int step, float grad_scale, void* stream);
+/* The same with the learning rate (lr_dev: one float) and Adam's step count (step_dev: one int, incremented by the call)
+ * in device memory, so that a training step captured into a CUDA graph keeps following the schedule and the bias
+ * corrections keep decaying on replay (torch.optim.Adam(capturable=True); notebook 03 cell 7 builds an Adam per call). */
+int ptd_multi_sgd_dev(const void* table, const void* blockmap, int n_blocks, const float* lr_dev, float momentum,
+                      float weight_decay, float grad_scale, int first_step, void* stream);
+int ptd_multi_adam_dev(const void* table, const void* blockmap, int n_blocks, const float* lr_dev, float beta1,
+                       float beta2, float eps, float weight_decay, int* step_dev, float grad_scale, void* stream);
 int ptd_multi_cast_bf16(const void* table, const void* blockmap, int n_blocks, void* stream);
 int ptd_multi_zero_grad(const void* table, const void* blockmap, int n_blocks, void* stream);
 int ptd_opt_chunk_elems(void);
@@ -218,6 +230,32 @@ int ptd_peer_copy(void* dst, const void* src, long long nbytes, void* stream);
 int ptd_peer_copy_bulk(void* dst, const void* src, long long nbytes, int blocks, void* stream);
 int ptd_reduce_sum_f32(float* dst, const void* const* srcs, int n_src, long long numel, float scale, int accumulate,
                        void* stream);
+
+/* ---- symmetric memory on the VMM API + NVSwitch multicast (NVLS) mapping (csrc/vmm.cu).  What NCCL sets up for itself
+ *      behind init_process_group("nccl") (ddp_gpus.py:22): registered peer buffers and a multicast object. ---- */
+int ptd_vmm_caps(void);                                   /* bit 0: VMM + POSIX-fd export, bit 1: multicast */
+int ptd_vmm_create(long long bytes, int rank, int world, long long* padded_out, int* fd_out);   /* -> block id > 0 */
+int ptd_vmm_import_peer(int id, int peer, int fd);
+int ptd_vmm_mc_create(int id, int* fd_out);               /* rank 0 */
+int ptd_vmm_mc_import(int id, int fd);                    /* other ranks */
+int ptd_vmm_mc_add_device(int id);                        /* all ranks, then a group barrier */
+int ptd_vmm_mc_bind(int id);                              /* all ranks: bind local memory, map the multicast range */
+int ptd_vmm_mc_drop(int id);
+int ptd_vmm_ptrs(int id, void** uc_out, void** mc_out, long long* bytes_out);
+int ptd_vmm_destroy(int id);
+/* In-place all-reduce through the switch: multimem.ld_reduce + multimem.st on the multicast mapping `mc_buf`; `mc_pad`
+ * (multicast mapping of the pads, may be NULL) selects the one-store switch barrier.  DDP's bucket all-reduce,
+ * ddp_gpus.py:41 (loss.backward() under DDP). */
+int ptd_allreduce_mc(void* mc_buf, const void* const* pads, const void* mc_pad, int rank, int world, long long numel,
+                     int is_bf16, float scale, int blocks, void* stream);
+/* Broadcast through the switch: the root stores each vector once (multimem.st), the NVSwitch writes every copy.  DDP's
+ * construction-time parameter broadcast and per-forward buffer broadcast (ddp_gpus.py:35). */
+int ptd_broadcast_mc(const void* const* bufs, void* mc_buf, const void* const* pads, const void* mc_pad, int rank,
+                     int world, int root, long long nbytes, int blocks, void* stream);
+/* fp32 gradients, bf16 on the wire: cast + reduce (switch or peer loads, fp32 accumulation) + cast back in one kernel. */
+int ptd_allreduce_wire_bf16(float* grad, const void* const* stages, void* mc_stage, const void* const* pads,
+                            const void* mc_pad, int rank, int world, long long numel, float scale, int blocks,
+                            void* stream);
 
 /* ---- gradient bucket planner / ready-tracking reducer (torch's C++ Reducer behind DDP) ---- */
 int ptd_plan_buckets(const long long* sizes_bytes, int n, long long first_cap, long long cap, int* bucket_of);

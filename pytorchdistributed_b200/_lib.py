@@ -62,6 +62,8 @@ _SIGS: dict[str, list] = {
     "ptd_softmax_ce": [P, P, P, P, P, I, I, I, I, F, P],
     "ptd_multi_sgd": [P, P, I, F, F, F, F, I, P],
     "ptd_multi_adam": [P, P, I, F, F, F, F, F, I, F, P],
+    "ptd_multi_sgd_dev": [P, P, I, P, F, F, F, I, P],
+    "ptd_multi_adam_dev": [P, P, I, P, F, F, F, F, P, F, P],
     "ptd_multi_cast_bf16": [P, P, I, P],
     "ptd_multi_zero_grad": [P, P, I, P],
     "ptd_opt_chunk_elems": [],
@@ -84,7 +86,7 @@ class BottleneckBwd(ctypes.Structure):
     _fields_ = [("N", I), ("H", I), ("W", I), ("inplanes", I), ("planes", I), ("stride", I), ("has_ds", I),
                 ("x", P), ("dz", P), ("w", P * 4), ("gamma", P * 4), ("y", P * 4), ("z", P * 4), ("saved", P),
                 ("sums", P), ("dw_all", P), ("dw_all_bytes", L), ("dw", P * 4), ("dy", P * 4), ("g_id", P), ("dz2", P),
-                ("dz1", P), ("dx", P), ("mask", P * 4)]
+                ("dz1", P), ("dx", P), ("mask", P * 4), ("gdst", P * 8)]
 
 
 _LIB: Optional[ctypes.CDLL] = None

@@ -16,9 +16,9 @@ Reference call sites: every layer of torchvision ``ResNet(Bottleneck,[3,4,6,3])`
 from __future__ import annotations
 
 import ctypes
-from typing import Optional, Tuple
-
 import os
+import weakref
+from typing import Optional, Tuple
 
 import torch
 
@@ -30,6 +30,27 @@ CL = torch.channels_last
 
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
+
+
+# ------------------------------------------------------------------------------------------------
+# gradient sink: lets a data-parallel wrapper receive parameter gradients where it wants them
+# ------------------------------------------------------------------------------------------------
+# A sink has two methods:
+#   targets(params) -> list of fp32 tensors (same element order as each parameter) that the kernels may
+#                      ACCUMULATE into directly, or None to decline (then autograd's AccumulateGrad runs as usual);
+#   done(params)    -> called once the kernels writing those targets have been issued on the current stream.
+# ``DistributedDataParallel`` installs itself: weight gradients are then reduced (red.global.add) straight into
+# the gradient-bucket views, no temporary and no per-parameter add kernel.
+_GRAD_SINK = None      # weak reference: the sink's lifetime stays with whoever built it
+
+
+def set_grad_sink(sink) -> None:
+    global _GRAD_SINK
+    _GRAD_SINK = weakref.ref(sink) if sink is not None else None
+
+
+def grad_sink():
+    return _GRAD_SINK() if _GRAD_SINK is not None else None
 
 
 def _empty_act(n: int, c: int, h: int, w: int, device, dtype=torch.bfloat16) -> torch.Tensor:
@@ -573,6 +594,8 @@ class _Bottleneck(torch.autograd.Function):
         ctx.cfg = cfg
         ctx.geom = (n, h, w, inplanes, planes, shapes)
         ctx.w_shapes = [tuple(u[0].shape) for u in units]
+        # the parameter objects themselves (weight, gamma, beta per unit): what a gradient sink is asked about
+        ctx.params = [t for u in units for t in (u[0], u[2], u[3])]
         ctx.save_for_backward(x, ybuf, zbuf, saved, mbuf, *[u[1] for u in units], *[u[2] for u in units])
         return zs[2]
 
@@ -606,15 +629,24 @@ class _Bottleneck(torch.autograd.Function):
             o += sz
         base = abuf.data_ptr()
         w_numels = [s_[0] * s_[1] * s_[2] * s_[3] for s_ in w_shapes]
-        gbuf = torch.empty(2 * sum(couts) + sum(w_numels), device=dev, dtype=torch.float32)   # [sums | dw_all]
-        sums = gbuf[:2 * sum(couts)]
-        dw_all = gbuf[2 * sum(couts):]
-        dws, o = [], 0
-        for shp, nel in zip(w_shapes, w_numels):
-            co, ci, r, s_ = shp
-            # as_strided offsets are absolute in the storage: dw_all starts after the sums
-            dws.append(torch.as_strided(gbuf, shp, (ci * r * s_, 1, s_ * ci, ci), 2 * sum(couts) + o))   # channels_last view
-            o += nel
+        # A gradient sink (DDP) may take every parameter gradient of the block where it lives: the weight-gradient
+        # kernels then accumulate into its tensors and dbeta / dgamma are added there by the same native call.
+        sink = grad_sink()
+        direct = sink.targets(ctx.params) if sink is not None else None
+        if direct is not None:
+            gbuf = torch.empty(2 * sum(couts), device=dev, dtype=torch.float32)
+            sums, dw_all = gbuf, None
+            dws = [direct[3 * i] for i in range(nu)]
+        else:
+            gbuf = torch.empty(2 * sum(couts) + sum(w_numels), device=dev, dtype=torch.float32)   # [sums | dw_all]
+            sums = gbuf[:2 * sum(couts)]
+            dw_all = gbuf[2 * sum(couts):]
+            dws, o = [], 0
+            for shp, nel in zip(w_shapes, w_numels):
+                co, ci, r, s_ = shp
+                # as_strided offsets are absolute in the storage: dw_all starts after the sums
+                dws.append(torch.as_strided(gbuf, shp, (ci * r * s_, 1, s_ * ci, ci), 2 * sum(couts) + o))   # channels_last view
+                o += nel
         d = _lib.BottleneckBwd()
         d.N, d.H, d.W, d.inplanes, d.planes, d.stride, d.has_ds = n, h, w, inplanes, planes, stride, int(has_ds)
         d.x, d.dz = x.data_ptr(), dz.data_ptr()
@@ -629,7 +661,15 @@ class _Bottleneck(torch.autograd.Function):
             o += numels[i] // 8
         d.mask = ma
         d.saved, d.sums = saved.data_ptr(), sums.data_ptr()
-        d.dw_all, d.dw_all_bytes = dw_all.data_ptr(), dw_all.numel() * 4
+        if direct is not None:
+            d.dw_all, d.dw_all_bytes = None, 0
+            gd = (ctypes.c_void_p * 8)()
+            for i in range(nu):
+                gd[2 * i] = direct[3 * i + 2].data_ptr()        # dbeta -> bias.grad
+                gd[2 * i + 1] = direct[3 * i + 1].data_ptr()    # dgamma -> weight.grad of the BatchNorm
+            d.gdst = gd
+        else:
+            d.dw_all, d.dw_all_bytes = dw_all.data_ptr(), dw_all.numel() * 4
         d.dw = _ptr4(dws)
         dya = (ctypes.c_void_p * 4)()
         for i in range(nu):
@@ -642,6 +682,9 @@ class _Bottleneck(torch.autograd.Function):
         _lib.call("ptd_bottleneck_bwd", d, _stream())
         xs = x.shape
         dx = torch.as_strided(abuf, xs, (xs[2] * xs[3] * xs[1], 1, xs[3] * xs[1], xs[1]), offs[nu + 3])
+        if direct is not None:
+            sink.done(ctx.params)
+            return (dx, None) + (None,) * (6 * nu)
         so, grads = 0, [dx, None]
         for i in range(nu):
             c = couts[i]

@@ -61,6 +61,29 @@ class _FusedBase(Optimizer):
         super().__init__(params, defaults)
         self._shadow_mods = _shadow_modules(model)
         self._tables: Dict[tuple, _DeviceTable] = {}
+        # Hyper-parameters the kernels read from DEVICE memory, per (param group, device): [lr] as one float and, for
+        # Adam, the step count as one int.  A step captured into a CUDA graph replays kernels, not this Python code:
+        # with host scalars the learning rate and Adam's bias corrections would be frozen at their capture-time values.
+        self._lr_dev: Dict[tuple, torch.Tensor] = {}
+        self._lr_host: Dict[tuple, float] = {}
+        self._step_dev: Dict[tuple, torch.Tensor] = {}
+
+    def _lr_tensor(self, gi: int, dev: torch.device, lr: float) -> torch.Tensor:
+        key = (gi, dev)
+        t = self._lr_dev.get(key)
+        if t is None:
+            t = self._lr_dev[key] = torch.full((1,), float(lr), device=dev, dtype=torch.float32)
+            self._lr_host[key] = float(lr)
+        elif self._lr_host[key] != float(lr):
+            t.fill_(float(lr))
+            self._lr_host[key] = float(lr)
+        return t
+
+    def sync_hyper(self) -> None:
+        """Push ``param_groups[i]["lr"]`` to the device copies the kernels read.  ``step()`` does this itself; call it
+        before replaying a CUDA graph that contains ``step()`` (``Trainer`` does) so an LR schedule takes effect."""
+        for (gi, dev), _ in list(self._lr_dev.items()):
+            self._lr_tensor(gi, dev, self.param_groups[gi]["lr"])
 
     def attach_model(self, model: torch.nn.Module) -> "_FusedBase":
         """Let ``step()`` refresh the bf16 shadow weights of ``model`` in the same kernel."""
@@ -123,8 +146,8 @@ class SGD(_FusedBase):
             if cuda:
                 by_dev, plist = self._rows(gi, cuda, 1 if mom != 0.0 else 0, ["momentum_buffer"] if mom != 0.0 else [])
                 self._launch(gi, by_dev, plist, lambda tab, st: _lib.call(
-                    "ptd_multi_sgd", tab.table, tab.blockmap, tab.n_blocks, float(lr), float(mom), float(wd),
-                    float(grad_scale), int(first), st))
+                    "ptd_multi_sgd_dev", tab.table, tab.blockmap, tab.n_blocks, self._lr_tensor(gi, tab.device, lr),
+                    float(mom), float(wd), float(grad_scale), int(first), st))
             for p in cpu:
                 g = p.grad * grad_scale
                 if wd != 0.0:
@@ -165,9 +188,13 @@ class Adam(_FusedBase):
             cpu = [p for p in ps if not p.is_cuda]
             if cuda:
                 by_dev, plist = self._rows(gi, cuda, 2, ["exp_avg", "exp_avg_sq"])
+                for dev in by_dev:
+                    if (gi, dev) not in self._step_dev:      # the kernel increments before it reads: start one behind
+                        self._step_dev[(gi, dev)] = torch.full((1,), int(t) - 1, device=dev, dtype=torch.int32)
                 self._launch(gi, by_dev, plist, lambda tab, st: _lib.call(
-                    "ptd_multi_adam", tab.table, tab.blockmap, tab.n_blocks, float(lr), float(b1), float(b2),
-                    float(eps), float(wd), int(t), float(grad_scale), st))
+                    "ptd_multi_adam_dev", tab.table, tab.blockmap, tab.n_blocks, self._lr_tensor(gi, tab.device, lr),
+                    float(b1), float(b2), float(eps), float(wd), self._step_dev[(gi, tab.device)], float(grad_scale),
+                    st))
             for p in cpu:
                 st = self.state[p]
                 g = p.grad * grad_scale
@@ -179,3 +206,23 @@ class Adam(_FusedBase):
                 denom = (st["exp_avg_sq"].sqrt() / bias2 ** 0.5).add_(eps)
                 p.addcdiv_(st["exp_avg"], denom, value=-lr / bias1)
         return loss
+
+    def step_count(self) -> int:
+        """Steps taken so far.  On CUDA the authoritative count lives on the device (it also advances when a captured
+        step is replayed, which never runs ``step()``'s Python); reading it synchronises."""
+        if self._step_dev:
+            return max(int(t.item()) for t in self._step_dev.values())
+        steps = [st["step"] for st in self.state.values() if "step" in st]
+        return int(max(steps)) if steps else 0
+
+    def state_dict(self):
+        if self._step_dev:                       # bring the host mirrors in line with the device count first
+            n = self.step_count()
+            for st in self.state.values():
+                if "step" in st:
+                    st["step"] = n
+        return super().state_dict()
+
+    def load_state_dict(self, state_dict) -> None:
+        super().load_state_dict(state_dict)
+        self._step_dev.clear()                   # re-created from the loaded host count at the next step()

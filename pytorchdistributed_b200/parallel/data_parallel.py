@@ -145,6 +145,9 @@ class DataParallel(nn.Module):
                 st.wait_event(ev)
                 if need_params:
                     _peer_copy(rep.pblock.flat, root.pblock.flat, root.pblock.total * 4, rep.device)
+                    # the raw kernel does not touch version counters: bump them so that everything cached on
+                    # (data_ptr, version) - the bf16 weight shadows of Conv2d / Linear - is rebuilt from the new values
+                    torch.autograd.graph.increment_version(rep.params)
                     self.stats["replicate_copies"] += 1
                 if rep.bblock is not None:
                     _peer_copy(rep.bblock.flat, root.bblock.flat, root.bblock.total * 4, rep.device)

@@ -13,10 +13,15 @@ Surface and semantics follow what the reference uses (``DDP(model, device_ids=[g
 * ``no_sync()`` skips the reduction (local accumulation); buffers (BatchNorm statistics) are
   re-broadcast from rank 0 before every forward, as one flat message.
 
-What changes underneath: on CUDA with >1 rank the averaging is our own peer-to-peer kernel over
-NVLink (``comm/p2p.py``: one-shot / two-shot / multimem, fused with the 1/world scale and the
-optional bf16 wire format); no NCCL call on that path.  ``comm="nccl"``/``"gloo"`` selects the
-``torch.distributed`` collective instead (baseline, and the CPU plumbing path).
+What changes underneath: on CUDA with >1 rank the averaging is our own kernel over NVLink (``comm/p2p.py``):
+through the NVSwitch (``multimem.ld_reduce`` / ``multimem.st``) where the box exposes multicast objects, a two-shot
+peer-to-peer reduction otherwise - the 1/world scale fused in, and with ``wire_dtype=torch.bfloat16`` the fp32
+buckets travel as bf16 (cast, reduction and cast back in the same kernel).  No NCCL call on that path;
+``comm="nccl"``/``"gloo"`` selects the ``torch.distributed`` collective instead (baseline, and the CPU plumbing path).
+
+Gradients reach the buckets without an extra pass where the producing kernel allows it: the module registers as the
+*gradient sink* of ``ops.functional`` and the residual blocks' weight-gradient kernels reduce straight into the bucket
+views (``_Bottleneck.backward``), then report their parameters ready themselves (``mark_ready``).
 """
 from __future__ import annotations
 
@@ -30,6 +35,7 @@ import torch.distributed as dist
 from torch import nn
 
 from .. import _lib
+from ..ops import functional as _F
 from ..utils.nvtx import nvtx_range
 
 _MiB = 1024 * 1024
@@ -103,7 +109,7 @@ class DistributedDataParallel(nn.Module):
                  broadcast_buffers: bool = True, process_group=None, bucket_cap_mb: float = 25,
                  first_bucket_mb: float = 1, find_unused_parameters: bool = False,
                  gradient_as_bucket_view: bool = True, comm: str = "auto", wire_dtype: Optional[torch.dtype] = None,
-                 rebuild_buckets: bool = True) -> None:
+                 rebuild_buckets: bool = True, direct_grads: bool = True) -> None:
         super().__init__()
         if not dist.is_initialized():
             raise RuntimeError("DistributedDataParallel needs an initialised process group (comm.ddp_setup)")
@@ -135,10 +141,14 @@ class DistributedDataParallel(nn.Module):
         self._index_of: Dict[int, int] = {id(p): i for i, p in enumerate(self._params)}
         self._reducer_id = 0
         self._buckets: List[_Bucket] = []
+        self._grad_region: Optional[torch.Tensor] = None      # one symmetric allocation all buckets are carved from
         self._build_buckets(list(reversed(range(len(self._params)))))
         self._callback_queued = False
         self._hooks = [p.register_post_accumulate_grad_hook(self._grad_ready) for p in self._params]
-        self.stats = {"allreduce_launches": 0, "bytes_reduced": 0, "iterations": 0}
+        self.stats = {"allreduce_launches": 0, "bytes_reduced": 0, "iterations": 0, "direct_grads": 0}
+        self.direct_grads = direct_grads and os.environ.get("PTDB200_DDP_DIRECT", "1") != "0"
+        if self.direct_grads and self.device.type == "cuda":
+            _F.set_grad_sink(self)            # the most recently built wrapper receives gradients directly
 
     # ------------------------------------------------------------------ construction helpers
     def _make_backend(self, comm: str, wire_dtype):
@@ -208,24 +218,40 @@ class DistributedDataParallel(nn.Module):
         sizes = [self._params[i].numel() * self._params[i].element_size() for i in order]
         assign = plan_buckets(sizes, self.first_cap, self.bucket_cap)
         n_buckets = max(assign) + 1
-        old_grads = {id(p): p.grad for p in self._params}
+        # a rebuild re-carves the region the old views live in: keep what they hold (accumulated gradients) aside
+        old_grads = {id(p): (p.grad.clone() if (p.grad is not None and self._grad_region is not None) else p.grad)
+                     for p in self._params}
         buckets = [_Bucket() for _ in range(n_buckets)]
         bucket_of = [0] * len(self._params)
         for pos, pi in enumerate(order):
             buckets[assign[pos]].params.append(self._params[pi])
             bucket_of[pi] = assign[pos]
+        totals = []
         for b in buckets:
             total, offs = 0, []
             for p in b.params:
                 total = (total + 3) // 4 * 4          # 16-byte alignment of every fp32 view
                 offs.append(total)
                 total += p.numel()
-            total = (total + 31) // 32 * 32
-            dtype = b.params[0].dtype
-            b.flat = self.backend.alloc(total, dtype, self.device)
+            total = (total + 63) // 64 * 64           # buckets start 256-byte aligned inside the region
             b.offsets = offs
-            for p, off in zip(b.params, offs):
-                view = torch.as_strided(b.flat, p.shape, p.stride(), off)
+            totals.append(total)
+        dtype = self._params[0].dtype
+        if any(p.dtype != dtype for p in self._params):
+            raise RuntimeError("DistributedDataParallel: parameters must share one dtype")
+        need = sum(totals)
+        if self._grad_region is None or self._grad_region.numel() < need:
+            # slack: a rebuild in ready order changes the per-bucket padding a little and must fit the same region
+            # (a second region would double the symmetric memory held until shutdown)
+            self._grad_region = self.backend.alloc(need + 64 * (len(self._params) + 64), dtype, self.device)
+        else:
+            self._grad_region.zero_()
+        start = 0
+        for b, total in zip(buckets, totals):
+            b.flat = self._grad_region[start:start + total]
+            start += total
+            for p, off in zip(b.params, b.offsets):
+                view = torch.as_strided(b.flat, p.shape, p.stride(), b.flat.storage_offset() + off)
                 g = old_grads[id(p)]
                 if g is not None:
                     view.copy_(g)
@@ -234,6 +260,8 @@ class DistributedDataParallel(nn.Module):
             if self.device.type == "cuda":
                 b.ready_event = torch.cuda.Event()
                 b.done_event = torch.cuda.Event()
+        if hasattr(self.backend, "reserve_wire"):
+            self.backend.reserve_wire(max(totals))
         self._buckets = buckets
         self._bucket_of = bucket_of
         arr = (ctypes.c_int * len(bucket_of))(*bucket_of)
@@ -275,12 +303,17 @@ class DistributedDataParallel(nn.Module):
                     torch.cuda.current_stream(self.device).synchronize()
                 self._build_buckets(order)
             self._rebuilt = True
-        # gradients dropped by optimizer.zero_grad(set_to_none=True): zero the flat buffers, re-attach views
-        if any(p.grad is None for p in self._params):
-            for b in self._buckets:
-                b.flat.zero_()
-                for p, v in zip(b.params, b.views):
-                    p.grad = v
+        # gradients dropped by optimizer.zero_grad(set_to_none=True): zero their bucket views and re-attach them
+        # (kernels accumulate into the views); gradients that are still set keep their contents
+        dropped = [p for p in self._params if p.grad is None]
+        if dropped:
+            if len(dropped) == len(self._params):
+                self._grad_region.zero_()                # one fill for all buckets
+            else:
+                for p in dropped:
+                    self._view_of[id(p)].zero_()
+            for p in dropped:
+                p.grad = self._view_of[id(p)]
         if self.broadcast_buffers and self.world_size > 1 and self.require_backward_grad_sync:
             with torch.no_grad():
                 for bf in self._buf_flats:
@@ -300,8 +333,32 @@ class DistributedDataParallel(nn.Module):
             p.grad = view
         self.mark_ready(p)
 
+    # -- gradient sink protocol (ops.functional.set_grad_sink) --------------------------------------------------
+    def targets(self, params) -> Optional[List[torch.Tensor]]:
+        """Bucket views the kernels may accumulate the gradients of ``params`` into, or ``None`` to decline (a
+        parameter of another module, a gradient that is not attached to its view, direct gradients switched off)."""
+        if not self.direct_grads:
+            return None
+        out = []
+        for p in params:
+            v = self._view_of.get(id(p))
+            g = p.grad
+            if v is None or g is None or not p.requires_grad:
+                return None
+            if g is not v and (g.data_ptr() != v.data_ptr() or g.stride() != v.stride()):
+                return None
+            out.append(v)
+        self.stats["direct_grads"] += len(out)
+        return out
+
+    def done(self, params) -> None:
+        for p in params:
+            self.mark_ready(p)
+
     def mark_ready(self, p: nn.Parameter) -> None:
         """Tell the reducer that ``p``'s gradient (already in its bucket view) is final for this backward."""
+        if not self.require_backward_grad_sync:
+            return
         if not self._callback_queued:
             torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
             self._callback_queued = True
@@ -352,6 +409,8 @@ class DistributedDataParallel(nn.Module):
 
     def __del__(self):
         try:
+            if _F.grad_sink() is self:
+                _F.set_grad_sink(None)
             if getattr(self, "_reducer_id", 0):
                 _lib.call_ret("ptd_reducer_destroy", self._reducer_id)
         except Exception:  # noqa: BLE001 - interpreter shutdown

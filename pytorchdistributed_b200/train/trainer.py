@@ -76,6 +76,8 @@ class Trainer:
             if g is not None and g["x"].shape == xs.shape and g["y"].shape == ys.shape and g["x"].dtype == xs.dtype:
                 g["x"].copy_(xs, non_blocking=True)
                 g["y"].copy_(ys, non_blocking=True)
+                if hasattr(self.optimizer, "sync_hyper"):
+                    self.optimizer.sync_hyper()          # an LR schedule reaches the replayed kernels through device memory
                 g["graph"].replay()
                 self.last_loss = g["loss"]
                 return self.last_loss
@@ -105,8 +107,8 @@ class Trainer:
             self._graph_failed = True
             self._graph = None
             torch.cuda.synchronize(self.device)
-            if not self.quiet:
-                print(f"[GPU: {self.gpu_id}] CUDA-graph capture failed, staying eager: {e}", flush=True)
+            # always said, also when `quiet`: a silent fall-back to eager would hide a 2x slower training loop
+            print(f"[GPU: {self.gpu_id}] CUDA-graph capture failed, staying eager: {type(e).__name__}: {e}", flush=True)
 
     def _run_epoch(self, epoch: int):
         batch_size = len(next(iter(self.train_dataloader))[0])

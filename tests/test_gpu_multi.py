@@ -12,13 +12,16 @@ def _need(n):
         pytest.skip(f"needs {n} GPUs")
 
 
-def _collectives(rank, world):
+def _collectives(rank, world, mode):
+    import os
+    os.environ["PTDB200_P2P_MODE"] = mode
+    os.environ["PTDB200_QUIET"] = "1"
     import torch
     import torch.distributed as dist
     from pytorchdistributed_b200.comm.p2p import P2PCollectives
     dev = torch.device("cuda", rank)
     be = P2PCollectives(None, dev)
-    out = {}
+    out = {"mode": be.mode, "mode_note": be.mode_note}
     for n in (4, 21, 1000, 262144 + 12, 4 * 1024 * 1024 + 4):
         for dtype in (torch.float32, torch.bfloat16):
             flat = be.alloc(n, dtype, dev)
@@ -35,29 +38,61 @@ def _collectives(rank, world):
             be.all_reduce_avg(flat)
             torch.cuda.synchronize()
             out[(n, str(dtype), "avg")] = bool(torch.allclose(flat.float(), ref / world, rtol=1e-2, atol=1e-2))
-    # back-to-back calls with no host sync in between
+            if dtype == torch.float32:
+                # bf16 on the wire: small integers (and their sums, and the power-of-two average) are exact in bf16
+                flat.copy_(vals)
+                be.all_reduce_avg(flat, scale=1.0, wire=True)
+                torch.cuda.synchronize()
+                out[(n, "wire_bf16", "sum_exact")] = bool(torch.equal(flat, ref))
+                # random data: every rank ends with the same values, close to the fp32 sum
+                r = torch.randn(n, generator=g).to(dev)
+                flat.copy_(r)
+                exact = r.clone()
+                dist.all_reduce(exact)
+                be.all_reduce_avg(flat, wire=True)
+                torch.cuda.synchronize()
+                out[(n, "wire_bf16", "close")] = bool(torch.allclose(flat, exact / world, rtol=2e-2, atol=2e-2))
+                lo, hi = flat.clone(), flat.clone()
+                dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+                dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+                out[(n, "wire_bf16", "identical_on_all_ranks")] = bool(torch.equal(lo, hi))
+    # back-to-back calls of every kind with no host sync in between
     flat = be.alloc(1 << 20, torch.float32, dev)
     flat.fill_(float(rank + 1))
-    for _ in range(20):
-        be.all_reduce_avg(flat)
+    for i in range(20):
+        be.all_reduce_avg(flat, wire=(i % 5 == 4))
     torch.cuda.synchronize()
     exp = sum(range(1, world + 1)) / world
-    out["repeat"] = bool(torch.allclose(flat, torch.full_like(flat, exp)))
+    out["repeat"] = bool(torch.allclose(flat, torch.full_like(flat, exp), rtol=1e-2))
     b = be.alloc(100003, torch.float32, dev)
     b.fill_(float(rank))
     be.broadcast(b, src=world - 1)
     torch.cuda.synchronize()
     out["bcast"] = bool((b == world - 1).all())
+    tmp = torch.full((777,), float(rank), device=dev)          # not symmetric memory: staged
+    be.broadcast(tmp, src=0)
+    torch.cuda.synchronize()
+    out["bcast_staged"] = bool((tmp == 0).all())
+    out["stats"] = dict(be.stats)
     be.close()
     return out
 
 
+@pytest.mark.parametrize("mode", ["nvls", "vmm", "ipc"])
 @pytest.mark.parametrize("world", [2, 4, 8])
-def test_p2p_collectives_match_nccl(world):
+def test_p2p_collectives_match_nccl(world, mode):
     _need(world)
-    for res in run_ranks(_collectives, world, backend="nccl"):
-        bad = [k for k, v in res.items() if not v]
-        assert not bad, bad
+    if mode == "vmm" and world != 2:
+        pytest.skip("the unicast-VMM provider runs the same kernels as ipc: covered once, at 2 ranks")
+    results = run_ranks(_collectives, world, (mode,), backend="nccl")
+    for res in results:
+        bad = [k for k, v in res.items() if isinstance(k, tuple) and not v] + [k for k in ("repeat", "bcast", "bcast_staged") if not res[k]]
+        assert not bad, (res["mode"], bad)
+    got = results[0]["mode"]
+    if got != mode:
+        pytest.skip(f"asked for {mode}, the box granted {got} ({results[0]['mode_note']}); that path passed")
+    if mode == "nvls":
+        assert results[0]["stats"]["nvls"] > 0 and results[0]["stats"]["two_shot"] == 0
 
 
 def _sharded(rank, world):
@@ -189,6 +224,111 @@ def test_ddp_p2p_replicas_identical_and_match_nccl_path(world):
     assert p2p[0][2]["iterations"] == 3 and p2p[0][2]["allreduce_launches"] >= 3
 
 
+def _ddp_mlp(rank, world, comm, wire):
+    """Deterministic little model (fp32 CUDA-core kernels, MSE): p2p and NCCL gradient averaging must agree tightly."""
+    import os
+    os.environ["PTDB200_QUIET"] = "1"
+    import torch
+    from pytorchdistributed_b200.models import MLP
+    from pytorchdistributed_b200.optim import SGD
+    from pytorchdistributed_b200.parallel import DistributedDataParallel as DDP
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(100 + rank)                     # different init per rank: rank 0's must win
+    model = MLP().to(dev).train()
+    ddp = DDP(model, device_ids=[rank], comm=comm, wire_dtype=torch.bfloat16 if wire else None)
+    opt = SGD(model.parameters(), lr=0.05, momentum=0.9)
+    g = torch.Generator().manual_seed(5)
+    xs = torch.randn(10, 16 * world, 10, generator=g)
+    ts = torch.randn(10, 16 * world, 5, generator=g)
+    losses = []
+    for s in range(10):
+        opt.zero_grad()
+        x = xs[s, rank * 16:(rank + 1) * 16].to(dev)
+        t = ts[s, rank * 16:(rank + 1) * 16].to(dev)
+        loss = torch.nn.functional.mse_loss(ddp(x), t)
+        loss.backward()
+        opt.step()
+        losses.append(float(loss))
+    torch.cuda.synchronize()
+    return losses, [p.detach().cpu() for p in model.parameters()], getattr(ddp.backend, "mode", "torch"), \
+        dict(getattr(ddp.backend, "stats", {}))
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_ddp_p2p_matches_nccl_on_deterministic_model(world):
+    _need(world)
+    p2p = run_ranks(_ddp_mlp, world, ("p2p", False), backend="nccl")
+    nccl = run_ranks(_ddp_mlp, world, ("torch", False), backend="nccl")
+    wire = run_ranks(_ddp_mlp, world, ("p2p", True), backend="nccl")
+    for r in range(1, world):
+        for a, b in zip(p2p[0][1], p2p[r][1]):
+            assert torch.equal(a, b)                         # replicas bit-identical
+        for a, b in zip(wire[0][1], wire[r][1]):
+            assert torch.equal(a, b)                         # also with bf16 on the wire (the slice owner rounds once)
+    for a, b in zip(p2p[0][1], nccl[0][1]):
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-5), float((a - b).abs().max())
+    for a, b in zip(wire[0][1], nccl[0][1]):
+        assert torch.allclose(a, b, rtol=5e-2, atol=5e-3), float((a - b).abs().max())     # bf16 gradients: ~3 digits
+    assert wire[0][3].get("wire_bf16", 0) > 0 and p2p[0][3].get("wire_bf16", 0) == 0
+    assert max(abs(x - y) for x, y in zip(p2p[0][0], nccl[0][0])) < 1e-4
+
+
+def _loss_curve(rank, world, impl):
+    """20 steps of ResNet-50 on a fixed batch (so the loss must fall), ours vs torchvision + torch DDP + bf16 autocast."""
+    import os
+    os.environ["PTDB200_QUIET"] = "1"
+    import torch
+    dev = torch.device("cuda", rank)
+    torch.manual_seed(0)
+    from pytorchdistributed_b200.models import resnet50
+    ours = resnet50(num_classes=16)
+    init = {k: v.clone() for k, v in ours.state_dict().items()}
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(8 * world, 3, 64, 64, generator=g)[rank * 8:(rank + 1) * 8].to(dev)
+    y = torch.randint(0, 16, (8 * world,), generator=g)[rank * 8:(rank + 1) * 8].to(dev)
+    if impl == "ours":
+        from pytorchdistributed_b200.ops import functional as K
+        from pytorchdistributed_b200.optim import SGD
+        from pytorchdistributed_b200.parallel import DistributedDataParallel as DDP
+        model = ours.to(dev).train()
+        ddp = DDP(model, device_ids=[rank])
+        opt = SGD(model.parameters(), lr=0.02, momentum=0.9)
+        fwd, loss_fn = ddp, K.cross_entropy
+    else:
+        import torchvision
+        model = torchvision.models.resnet50(num_classes=16)
+        model.load_state_dict(init)                                   # same initial weights: the layouts are compatible
+        model = model.to(dev).to(memory_format=torch.channels_last).train()
+        ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[rank])
+        opt = torch.optim.SGD(model.parameters(), lr=0.02, momentum=0.9)
+
+        def fwd(inp):
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                return ddp(inp.contiguous(memory_format=torch.channels_last)).float()
+        loss_fn = torch.nn.functional.cross_entropy
+    losses = []
+    for _ in range(20):
+        opt.zero_grad()
+        loss = loss_fn(fwd(x), y)
+        loss.backward()
+        opt.step()
+        losses.append(float(loss))
+    torch.cuda.synchronize()
+    return losses
+
+
+def test_ddp_resnet_loss_curve_tracks_torch_ddp():
+    _need(2)
+    ours = run_ranks(_loss_curve, 2, ("ours",), backend="nccl")[0]
+    ref = run_ranks(_loss_curve, 2, ("torch",), backend="nccl")[0]
+    print("ours :", [round(v, 3) for v in ours])
+    print("torch:", [round(v, 3) for v in ref])
+    assert abs(ours[0] - ref[0]) < 0.05                               # same weights, same batch: same first loss
+    assert ours[-1] < ours[0] - 0.5 and ref[-1] < ref[0] - 0.5        # both learn the fixed batch
+    diff = [abs(a - b) for a, b in zip(ours, ref)]
+    assert sum(diff) / len(diff) < 0.35, diff                         # two bf16 runs of a BN network drift, not diverge
+
+
 def test_pipeline_cuda_graph_matches_eager_pipeline():
     """Graph-replayed pipeline stages (both stages on one GPU here: the graph logic does not care) behave like the
     eager pipeline, step after step, uneven last split included.
@@ -266,6 +406,62 @@ def test_data_parallel_forward_backward_matches_single_device():
             p.add_(1.0)
     assert torch.allclose(dp(x), ref(x), atol=1e-4)
     assert dp.stats["replicate_copies"] > c0
+
+
+def test_data_parallel_resnet_gradients_and_second_step_match_single_device():
+    """Gradient parity (not just "finite") and the step after an optimizer update: replicas must run on the UPDATED
+    weights (their bf16 shadows are rebuilt after the raw peer copy), else the second loss comes out different."""
+    _need(2)
+    from pytorchdistributed_b200.models import resnet50
+    from pytorchdistributed_b200.ops import functional as K
+    from pytorchdistributed_b200.optim import SGD
+    from pytorchdistributed_b200.parallel import DataParallel
+    rel = lambda a, b: float((a.float() - b.float()).norm() / (b.float().norm() + 1e-12))  # noqa: E731
+    torch.manual_seed(0)
+    models = [resnet50(num_classes=32).cuda(0).train() for _ in range(3)]       # dp, single, single again (noise)
+    for m in models[1:]:
+        m.load_state_dict(models[0].state_dict())
+    dp = DataParallel(models[0], device_ids=[0, 1], criterion=K.cross_entropy)
+    opts = [SGD(m.parameters(), lr=0.1) for m in models]
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(8, 3, 64, 64, generator=g).cuda(0)
+    y = torch.randint(0, 32, (8,), generator=g).cuda(0)
+
+    def single(m):
+        # what two replicas compute: each half on its own (its own BatchNorm statistics), losses weighted by share
+        total = 0.0
+        for lo in (0, 4):
+            l = K.cross_entropy(m(x[lo:lo + 4]), y[lo:lo + 4]) * 0.5
+            l.backward()
+            total += float(l)
+        return total
+
+    losses = []
+    for step in range(2):
+        for o in opts:
+            o.zero_grad()
+        l_dp = dp(x, y)
+        l_dp.backward()
+        l_s, l_n = single(models[1]), single(models[2])
+        losses.append((float(l_dp), l_s, l_n))
+        if step == 0:
+            for (k, p), q, r in zip(models[0].named_parameters(), models[1].parameters(), models[2].parameters()):
+                noise = rel(q.grad, r.grad)
+                assert rel(p.grad, q.grad) < 3 * noise + 2e-2, (k, noise, rel(p.grad, q.grad))
+        for o in opts:
+            o.step()
+    assert abs(losses[0][0] - losses[0][1]) < 2e-2, losses
+    # the regression itself: after the update the replica's bf16 weight copy is the cast of the NEW root weights
+    root_w = models[0].layer1[0].conv1.weight.detach()
+    rep_mod = dp.replicas[1].module.layer1[0].conv1
+    dp(x, y)                                            # replicate + forward on the updated weights
+    torch.cuda.synchronize(1)
+    assert torch.equal(rep_mod.weight.detach().cpu(), root_w.cpu())
+    assert rep_mod._shadow is not None
+    assert torch.equal(rep_mod._shadow.float().cpu(), root_w.to(torch.bfloat16).float().cpu())
+    # and the loss of the second step follows the single-device run
+    assert abs(losses[1][0] - losses[1][1]) < 3 * abs(losses[1][1] - losses[1][2]) + 0.05 * max(1.0, abs(losses[1][1])), losses
+    assert dp.stats["replicate_copies"] >= 2
 
 
 def test_data_parallel_fused_loss_resnet():

@@ -71,6 +71,68 @@ def test_static_scratch_entry_point_matches_regular_path_twice():
         assert _rel(dgamma, rdgamma) < 1e-2 and _rel(dbeta, rdbeta) < 1e-2, f"call {call}"
 
 
+def _torch_fp32_bn_backward(y, z, dz, mean, invstd, gamma, relu):
+    """The same backward written in plain fp32 PyTorch: the oracle that does not share a line with the library."""
+    yf, dzf = y.float(), dz.float()
+    g = dzf * (z.float() > 0) if relu else dzf
+    cshape = (1, -1, 1, 1)
+    xhat = (yf - mean.view(cshape)) * invstd.view(cshape)
+    dbeta = g.sum((0, 2, 3))
+    dgamma = (g * xhat).sum((0, 2, 3))
+    m = yf.numel() // yf.shape[1]
+    dy = (gamma * invstd).view(cshape) * (g - dbeta.view(cshape) / m - xhat * dgamma.view(cshape) / m)
+    return dy, g, dgamma, dbeta
+
+
+@pytest.mark.parametrize("dev_index", [0, 1])
+def test_static_scratch_entry_point_matches_fp32_pytorch(dev_index):
+    """Against plain PyTorch, and once on a second GPU: the array's address is looked up per device, so the first
+    call there takes the branch that the calls on device 0 no longer do."""
+    if torch.cuda.device_count() <= dev_index:
+        pytest.skip(f"needs {dev_index + 1} GPUs")
+    lib = _lib.require()
+    fn = lib.ptd_bn_backward_static
+    fn.restype = I
+    fn.argtypes = [P, P, P, P, P, P, P, P, P, P, L, I, I, P]
+    dev = torch.device("cuda", dev_index)
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        for c, relu, seed in [(128, 1, 21), (512, 0, 22)]:           # two calls in a row on this device
+            y, z, dz, mean, invstd, gamma, m = _case(c, relu, seed, dev)
+            dy, gout = torch.empty_like(y), torch.empty_like(y)
+            dgamma, dbeta = torch.empty(c, device=dev), torch.empty(c, device=dev)
+            rc = fn(dz.data_ptr(), z.data_ptr(), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(), gamma.data_ptr(),
+                    dy.data_ptr(), gout.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), m, c, relu, stream)
+            assert rc == 0, lib.ptd_last_error()
+            tdy, tg, tdgamma, tdbeta = _torch_fp32_bn_backward(y, z, dz, mean, invstd, gamma, bool(relu))
+            torch.cuda.synchronize(dev)
+            assert _rel(dy, tdy) < 1e-2 and _rel(gout, tg) < 1e-2, (c, relu)
+            assert _rel(dgamma, tdgamma) < 1e-2 and _rel(dbeta, tdbeta) < 1e-2, (c, relu)
+
+
+def test_static_scratch_entry_point_rejects_bad_arguments():
+    """Nothing may launch on arguments the kernels cannot honour: the bit-mask mode of the two-call path, a missing z
+    with the ReLU on, an empty tensor, a channel count that is not a power of two."""
+    lib = _lib.require()
+    fn = lib.ptd_bn_backward_static
+    fn.restype = I
+    fn.argtypes = [P, P, P, P, P, P, P, P, P, P, L, I, I, P]
+    dev = torch.device("cuda:0")
+    c = 64
+    t = torch.zeros(1, c, 2, 2, device=dev, dtype=torch.bfloat16).contiguous(memory_format=CL)
+    v = torch.ones(c, device=dev)
+    out = torch.empty(c, device=dev)
+    st = torch.cuda.current_stream(dev).cuda_stream
+    call = lambda z, m, ch, relu: fn(t.data_ptr(), z, t.data_ptr(), v.data_ptr(), v.data_ptr(), v.data_ptr(),  # noqa: E731
+                                     t.data_ptr(), None, out.data_ptr(), out.data_ptr(), m, ch, relu, st)
+    assert call(t.data_ptr(), 4, c, 2) != 0 and b"relu" in lib.ptd_last_error()
+    assert call(None, 4, c, 1) != 0 and b"z" in lib.ptd_last_error()
+    assert call(t.data_ptr(), 0, c, 0) != 0
+    assert call(t.data_ptr(), 4, 96, 0) != 0 and b"power of two" in lib.ptd_last_error()
+    assert call(t.data_ptr(), 4, c, 1) == 0, lib.ptd_last_error()      # and the same arguments, valid, go through
+    torch.cuda.synchronize()
+
+
 def test_static_scratch_entry_point_rejects_oversize():
     lib = _lib.require()
     fn = lib.ptd_bn_backward_static
