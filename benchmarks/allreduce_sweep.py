@@ -50,6 +50,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-mb", type=float, default=256)
     ap.add_argument("--out", default=None)
+    ap.add_argument("--mc-blocks", default="", help="comma-separated CTA counts: also time the switch kernel at each")
     ap.add_argument("--sizes", default="", help="comma-separated sizes in bytes (default: 1 KB x4 ... plus 25 MiB)")
     args = ap.parse_args()
     from pytorchdistributed_b200 import _lib
@@ -69,12 +70,13 @@ def main():
             s *= 4
         sizes = sorted(set(sizes + [b for b in (25 << 20, 64 << 20) if b <= args.max_mb * (1 << 20)]))
     rows = []
+    sampler = ClockSampler(lr, period_ms=50).start() if rank == 0 else None       # one sampler for the whole sweep
     for size in sizes:
         n = size // 4
         ours = be.alloc(n, torch.float32, dev)
         ref = torch.empty(n, dtype=torch.float32, device=dev)
         iters = 50 if size <= (16 << 20) else 10
-        sampler = ClockSampler(lr, period_ms=100).start() if rank == 0 else None
+        mark = sampler.mark() if sampler else 0
         res, ok = {}, {}
         reg, off = be._loc(ours)
         st = lambda: torch.cuda.current_stream(dev).cuda_stream  # noqa: E731
@@ -84,7 +86,14 @@ def main():
             _lib.call("ptd_allreduce_inplace", be._ptrs(reg, off), pads, rank, world, (n + 3) // 4 * 4, 0, 1.0 / world,
                       be.blocks, st())
 
-        arms = [("ours", lambda: be.all_reduce_avg(ours, wire=False)), ("two_shot", two_shot),
+        def nvls():
+            _lib.call("ptd_allreduce_mc", reg.mc + off, pads, be._pad(0)[1], rank, world, (n + 3) // 4 * 4, 0, 1.0 / world,
+                      be.blocks, st())
+
+        arms = [("ours", lambda: be.all_reduce_avg(ours, wire=False)), ("two_shot", two_shot)]
+        if reg.mc:
+            arms.append(("nvls", nvls))
+        arms += [
                 ("wire_bf16", lambda: be.all_reduce_avg(ours, wire=True)),
                 ("nccl", lambda: dist.all_reduce(ref, op=dist.ReduceOp.AVG))]
         for name, fn in arms:
@@ -93,7 +102,14 @@ def main():
             res[name] = timed(fn, iters, dev)
             tgt = ref if name == "nccl" else ours
             ok[name] = bool(torch.allclose(tgt, torch.ones_like(tgt)))     # the average of ones stays one
-        clocks = sampler.stop() if sampler else {}
+        by_blocks = {}
+        if args.mc_blocks and reg.mc and size >= (1 << 20):
+            keep = be.blocks
+            for b in [int(v) for v in args.mc_blocks.split(",")]:
+                be.blocks = b
+                by_blocks[b] = round(timed(nvls, iters, dev), 2)
+            be.blocks = keep
+        clocks = sampler.summary(since=mark) if sampler else {}     # the samples taken while this row ran
         bus = 2.0 * (world - 1) / world * size
         nvls_bytes = (1.0 + 1.0 / world) * size
         row = {"bytes": size, "mode": be.mode, "clocks": clocks}
@@ -105,15 +121,21 @@ def main():
         if be.mode == "nvls":
             row["frac_roofline_nvls_of_measured"] = round(nvls_bytes / res["ours"] / 1e3 / NVLINK_GBS, 3)
         row["speedup_vs_nccl"] = round(res["nccl"] / res["ours"], 3)
+        if by_blocks:
+            row["nvls_us_by_blocks"] = by_blocks
         rows.append(row)
         if rank == 0:
             print(f"{size:>11d} B  " + "  ".join(f"{k} {v:8.1f} us" for k, v in res.items())
                   + f"   ours {row['ours_busbw_gbs']:7.1f} GB/s bus = {row['frac_roofline_of_measured']:.2f} of roofline,"
-                  f" {row['speedup_vs_nccl']:.2f}x nccl  ok={all(ok.values())}  clocks={clocks.get('sm_mhz')} {clocks.get('reasons')}",
-                  flush=True)
+                  f" {row['speedup_vs_nccl']:.2f}x nccl  ok={all(ok.values())}  clocks={clocks.get('sm_mhz')} {clocks.get('reasons')}"
+                  + (f"  nvls by blocks {by_blocks}" if by_blocks else ""), flush=True)
         del ours, ref
+    clocks_all = sampler.stop() if sampler else {}
+    for row in rows:                  # rows shorter than the sampling period: the whole sweep's record stands in
+        if not row["clocks"].get("samples"):
+            row["clocks"] = dict(clocks_all, note="whole-sweep record (row shorter than the sampling period)")
     if rank == 0 and args.out:
-        json.dump({"world": world, "dtype": "float32", "mode": be.mode, "mode_note": be.mode_note,
+        json.dump({"world": world, "dtype": "float32", "mode": be.mode, "mode_note": be.mode_note, "clocks": clocks_all,
                    "nvlink_gbs_per_direction_measured": NVLINK_GBS, "rows": rows}, open(args.out, "w"), indent=1)
     be.close()
     destroy_process_group()

@@ -662,7 +662,7 @@ int pick_blocks_mc(long long work_items, int requested) {
     long long b = (work_items + AR_THREADS * 4 - 1) / (AR_THREADS * 4);
     if (b < 1) b = 1;
     static int cap = -1;
-    if (cap < 0) cap = env_int("PTDB200_MC_MAX_BLOCKS", 48);
+    if (cap < 0) cap = env_int("PTDB200_MC_MAX_BLOCKS", 32);     // measured at N = 4: 16-32 CTAs already give the full rate
     if (b > cap) b = cap;
     return (int)b;
 }
@@ -913,7 +913,8 @@ extern "C" int ptd_allreduce_wire_bf16(float* grad, const void* const* stages, v
     if (rc) return rc;
     PTD_REQUIRE(numel % 8 == 0 && ((uintptr_t)grad & 15) == 0, "allreduce_wire_bf16: numel (%lld) %% 8 and a 16-byte aligned buffer", numel);
     const long long n8 = numel / 8;
-    const int grid = mc_stage ? pick_blocks_mc((n8 + world - 1) / world, blocks) : pick_blocks((n8 + world - 1) / world, blocks);
+    // phases A and C are local HBM passes over the whole buffer: they want a full-size grid whatever phase B uses
+    const int grid = pick_blocks(n8, blocks);
     cudaStream_t st = (cudaStream_t)stream;
 #define PTD_WIRE(W)                                                                                                      \
     case W:                                                                                                              \

@@ -21,6 +21,7 @@ Serves what the reference gets from ``init_process_group("nccl")`` + DDP's inter
 """
 from __future__ import annotations
 
+import array
 import bisect
 import ctypes
 import os
@@ -118,7 +119,9 @@ class FdChannel:
         self._tag = 0
 
     def _send(self, dst: int, tag: int, fd: int) -> None:
-        socket.send_fds(self.sock, [struct.pack("ii", tag, self.rank)], [fd], 0, self.names[dst])
+        # (socket.send_fds of Python 3.12 drops its `address` argument, hence sendmsg itself)
+        self.sock.sendmsg([struct.pack("ii", tag, self.rank)],
+                          [(socket.SOL_SOCKET, socket.SCM_RIGHTS, array.array("i", [fd]))], 0, self.names[dst])
 
     def _recv(self, tag: int, src: int) -> int:
         while (tag, src) not in self._stash:
@@ -356,6 +359,12 @@ class P2PCollectives:
         self.wire_dtype = torch.bfloat16 if wire_dtype == torch.bfloat16 else None
         self.blocks = int(os.environ.get("PTDB200_AR_BLOCKS", "0"))
         self.mc_barrier = os.environ.get("PTDB200_MC_BARRIER", "1") != "0"
+        # Which all-reduce runs on multicast-capable memory.  Per direction of a port the switch path moves (1 + 1/N) x
+        # the buffer, the two-shot path 2 (N-1)/N x: two ranks are better off peer-to-peer (1.0 vs 1.5), three break even,
+        # four and more win through the switch (N = 8: 1.125 vs 1.75).  Measured at N = 2: 433 vs 684 us at 256 MB.
+        self.algo = os.environ.get("PTDB200_AR_ALGO", "auto")
+        if self.algo not in ("auto", "nvls", "two_shot"):
+            raise RuntimeError(f"PTDB200_AR_ALGO={self.algo!r}: expected auto, nvls or two_shot")
         self.arena_bytes = int(arena_bytes or float(os.environ.get("PTDB200_ARENA_MB", "128")) * (1 << 20))
         self.stats = {"nvls": 0, "two_shot": 0, "wire_bf16": 0}
         self._regions: List[_Region] = []           # sorted by local_ptr
@@ -460,13 +469,14 @@ class P2PCollectives:
             n8 = (n + 7) // 8 * 8                        # allocations are padded to 256 B, the tail is ours
             stage = self._stage(n8)
             sreg, soff = self._loc(stage)
-            _lib.call("ptd_allreduce_wire_bf16", flat, self._ptrs(sreg, soff), (sreg.mc + soff) if sreg.mc else None,
+            via_switch = sreg.mc and (self.algo == "nvls" or (self.algo == "auto" and self.world >= 3))
+            _lib.call("ptd_allreduce_wire_bf16", flat, self._ptrs(sreg, soff), (sreg.mc + soff) if via_switch else None,
                       pads, mc_pad, self.rank, self.world, n8, scale, self.blocks, self._stream())
             self.stats["wire_bf16"] += 1
             return
         per = 8 if is_bf16 else 4
         n_pad = (n + per - 1) // per * per
-        if reg.mc and self.world > 1:
+        if reg.mc and self.world > 1 and (self.algo == "nvls" or (self.algo == "auto" and self.world >= 3)):
             _lib.call("ptd_allreduce_mc", reg.mc + off, pads, mc_pad, self.rank, self.world, n_pad, int(is_bf16), scale,
                       self.blocks, self._stream())
             self.stats["nvls"] += 1

@@ -49,11 +49,15 @@ class ClockSampler:
             self._thread.join(timeout=2)
         return self.summary()
 
-    def summary(self) -> Dict:
+    def mark(self) -> int:
+        """Position in the sample log; pass it to ``summary(since=...)`` to summarise only what came after."""
+        return len(self.lines)
+
+    def summary(self, since: int = 0) -> Dict:
         sm, mx, power = [], [], []
         reasons = set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for ln in self.lines[since:]:
             parts = [x.strip() for x in ln.split(",")]
             if len(parts) < 9:
                 continue

@@ -44,3 +44,38 @@ def test_data_parallel_without_gpu_is_passthrough():
     assert dp(x).shape == (32, 5)
     assert torch.equal(dp(x), m(x))
     assert list(dp.state_dict().keys())[0].startswith("module.")
+
+
+def _fd_exchange(rank, world):
+    """Every rank opens a pipe, writes its rank into it and hands the READ end to everybody (unix-socket fd passing,
+    the way the VMM handles of comm/p2p.py travel); reading from a received descriptor yields the sender's rank."""
+    import os
+    from pytorchdistributed_b200.comm.p2p import FdChannel
+    chan = FdChannel(None)
+    out = {}
+    for round_ in range(2):                                  # two exchanges back to back: tags keep them apart
+        r, w = os.pipe()
+        os.write(w, bytes([10 * round_ + rank]) * (world - 1))
+        got = chan.all_to_all(r)
+        out[("a2a", round_)] = [None if fd is None else os.read(fd, 1)[0] for fd in got]
+        for fd in got:
+            if fd is not None:
+                os.close(fd)
+        os.close(r)
+        os.close(w)
+    r, w = os.pipe()
+    os.write(w, bytes([77]) * world)
+    fd = chan.from_root(r if rank == 0 else None, 0)
+    out["root"] = None if fd is None else os.read(fd, 1)[0]
+    chan.close()
+    return out
+
+
+def test_fd_channel_passes_descriptors_between_ranks():
+    from tests._mp import run_ranks
+    world = 3
+    res = run_ranks(_fd_exchange, world, backend="gloo")
+    for rank, out in enumerate(res):
+        for round_ in range(2):
+            assert out[("a2a", round_)] == [None if r == rank else 10 * round_ + r for r in range(world)]
+        assert out["root"] == (None if rank == 0 else 77)

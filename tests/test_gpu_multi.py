@@ -15,6 +15,7 @@ def _need(n):
 def _collectives(rank, world, mode):
     import os
     os.environ["PTDB200_P2P_MODE"] = mode
+    os.environ["PTDB200_AR_ALGO"] = "nvls" if mode == "nvls" else "auto"     # at 2 ranks `auto` prefers two-shot
     os.environ["PTDB200_QUIET"] = "1"
     import torch
     import torch.distributed as dist
@@ -292,7 +293,7 @@ def _loss_curve(rank, world, impl):
         from pytorchdistributed_b200.parallel import DistributedDataParallel as DDP
         model = ours.to(dev).train()
         ddp = DDP(model, device_ids=[rank])
-        opt = SGD(model.parameters(), lr=0.02, momentum=0.9)
+        opt = SGD(model.parameters(), lr=0.003, momentum=0.9)
         fwd, loss_fn = ddp, K.cross_entropy
     else:
         import torchvision
@@ -300,7 +301,7 @@ def _loss_curve(rank, world, impl):
         model.load_state_dict(init)                                   # same initial weights: the layouts are compatible
         model = model.to(dev).to(memory_format=torch.channels_last).train()
         ddp = torch.nn.parallel.DistributedDataParallel(model, device_ids=[rank])
-        opt = torch.optim.SGD(model.parameters(), lr=0.02, momentum=0.9)
+        opt = torch.optim.SGD(model.parameters(), lr=0.003, momentum=0.9)
 
         def fwd(inp):
             with torch.autocast("cuda", dtype=torch.bfloat16):
@@ -324,9 +325,9 @@ def test_ddp_resnet_loss_curve_tracks_torch_ddp():
     print("ours :", [round(v, 3) for v in ours])
     print("torch:", [round(v, 3) for v in ref])
     assert abs(ours[0] - ref[0]) < 0.05                               # same weights, same batch: same first loss
-    assert ours[-1] < ours[0] - 0.5 and ref[-1] < ref[0] - 0.5        # both learn the fixed batch
+    assert ours[-1] < ours[0] - 0.3 and ref[-1] < ref[0] - 0.3        # both learn the fixed batch
     diff = [abs(a - b) for a, b in zip(ours, ref)]
-    assert sum(diff) / len(diff) < 0.35, diff                         # two bf16 runs of a BN network drift, not diverge
+    assert sum(diff) / len(diff) < 0.25, diff                         # two bf16 runs of a BN network drift, not diverge
 
 
 def test_pipeline_cuda_graph_matches_eager_pipeline():
@@ -359,7 +360,8 @@ def test_pipeline_cuda_graph_matches_eager_pipeline():
             loss = K.cross_entropy(model(x), y)
             loss.backward()
             losses.append(float(loss.detach()))
-        assert abs(losses[0] - losses[2]) < 3 * abs(losses[0] - losses[1]) + 2e-2 * max(1.0, abs(losses[0])), (step, losses)
+        # one |eager - eager2| sample is itself noisy (it can come out near zero): allow 5 % of the loss on top
+        assert abs(losses[0] - losses[2]) < 3 * abs(losses[0] - losses[1]) + 5e-2 * max(1.0, abs(losses[0])), (step, losses)
         for (k, pe), p2, pg in zip(eager.named_parameters(), eager2.parameters(), graph.parameters()):
             assert pg.grad is not None and torch.isfinite(pg.grad).all(), k
             ne, ng = float(pe.grad.norm()), float(pg.grad.norm())
@@ -450,7 +452,7 @@ def test_data_parallel_resnet_gradients_and_second_step_match_single_device():
                 assert rel(p.grad, q.grad) < 3 * noise + 2e-2, (k, noise, rel(p.grad, q.grad))
         for o in opts:
             o.step()
-    assert abs(losses[0][0] - losses[0][1]) < 2e-2, losses
+    assert abs(losses[0][0] - losses[0][1]) < 3 * abs(losses[0][1] - losses[0][2]) + 2e-2 * max(1.0, abs(losses[0][1])), losses
     # the regression itself: after the update the replica's bf16 weight copy is the cast of the NEW root weights
     root_w = models[0].layer1[0].conv1.weight.detach()
     rep_mod = dp.replicas[1].module.layer1[0].conv1
