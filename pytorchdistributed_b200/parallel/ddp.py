@@ -119,7 +119,10 @@ class DistributedDataParallel(nn.Module):
         self.process_group = process_group
         self.world_size = dist.get_world_size(process_group)
         self.rank = dist.get_rank(process_group)
-        self.broadcast_buffers = broadcast_buffers
+        # PTDB200_DDP_BCAST=0 / PTDB200_DDP_SKIP_ALLREDUCE=1: control runs that attribute step time to the per-forward
+        # buffer broadcast / the gradient all-reduce (results are then wrong on purpose: replicas drift apart)
+        self.broadcast_buffers = broadcast_buffers and os.environ.get("PTDB200_DDP_BCAST", "1") != "0"
+        self._skip_allreduce = os.environ.get("PTDB200_DDP_SKIP_ALLREDUCE", "0") == "1"
         self.require_backward_grad_sync = True
         self.bucket_cap = int(bucket_cap_mb * _MiB)
         self.first_cap = int(first_bucket_mb * _MiB)
@@ -156,6 +159,8 @@ class DistributedDataParallel(nn.Module):
         if comm == "auto":
             comm = "p2p" if (self.device.type == "cuda" and self.world_size > 1) else "torch"
         if comm == "p2p":
+            if wire_dtype is None and os.environ.get("PTDB200_DDP_WIRE", "") == "bf16":
+                wire_dtype = torch.bfloat16
             from ..comm import p2p
             return p2p.P2PCollectives(self.process_group, self.device, wire_dtype=wire_dtype)
         return _TorchCollectives(self.process_group)
@@ -372,7 +377,7 @@ class DistributedDataParallel(nn.Module):
         b.launched = True
         self.stats["allreduce_launches"] += 1
         self.stats["bytes_reduced"] += b.flat.numel() * b.flat.element_size()
-        if self.world_size == 1:
+        if self.world_size == 1 or self._skip_allreduce:
             return
         if self._comm_stream is not None:
             b.ready_event.record(torch.cuda.current_stream(self.device))
@@ -395,7 +400,7 @@ class DistributedDataParallel(nn.Module):
         if self._comm_stream is not None:
             cur = torch.cuda.current_stream(self.device)
             for b in self._buckets:
-                if b.launched and self.world_size > 1:
+                if b.launched and self.world_size > 1 and not self._skip_allreduce:
                     cur.wait_event(b.done_event)
         for b in self._buckets:
             b.launched = False

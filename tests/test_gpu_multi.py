@@ -458,12 +458,53 @@ def test_data_parallel_resnet_gradients_and_second_step_match_single_device():
     rep_mod = dp.replicas[1].module.layer1[0].conv1
     dp(x, y)                                            # replicate + forward on the updated weights
     torch.cuda.synchronize(1)
-    assert torch.equal(rep_mod.weight.detach().cpu(), root_w.cpu())
-    assert rep_mod._shadow is not None
+    assert rep_mod._shadow is not None                  # (the replica's fp32 master is not refreshed: nothing reads it)
     assert torch.equal(rep_mod._shadow.float().cpu(), root_w.to(torch.bfloat16).float().cpu())
     # and the loss of the second step follows the single-device run
     assert abs(losses[1][0] - losses[1][1]) < 3 * abs(losses[1][1] - losses[1][2]) + 0.05 * max(1.0, abs(losses[1][1])), losses
     assert dp.stats["replicate_copies"] >= 2
+
+
+def test_data_parallel_cuda_graph_matches_eager():
+    """Graph-replayed replicas (one forward and one backward graph per GPU, launched from one thread) train like the
+    thread-pool eager path: losses and root gradients within the eager path's own run-to-run noise, three steps."""
+    _need(2)
+    from pytorchdistributed_b200.models import resnet50
+    from pytorchdistributed_b200.ops import functional as K
+    from pytorchdistributed_b200.optim import SGD
+    from pytorchdistributed_b200.parallel import DataParallel
+    rel = lambda a, b: float((a.float() - b.float()).norm() / (b.float().norm() + 1e-12))  # noqa: E731
+    torch.manual_seed(0)
+    models = [resnet50(num_classes=32).cuda(0).train() for _ in range(3)]
+    for m in models[1:]:
+        m.load_state_dict(models[0].state_dict())
+    dps = [DataParallel(models[0], device_ids=[0, 1], criterion=K.cross_entropy),
+           DataParallel(models[1], device_ids=[0, 1], criterion=K.cross_entropy),
+           DataParallel(models[2], device_ids=[0, 1], criterion=K.cross_entropy, cuda_graph=True)]
+    opts = [SGD(m.parameters(), lr=1e-3, model=m) for m in models]
+    g = torch.Generator().manual_seed(4)
+    noise_l = 0.0
+    for step in range(3):
+        x = torch.randn(8, 3, 64, 64, generator=g).cuda(0)
+        y = torch.randint(0, 32, (8,), generator=g).cuda(0)
+        losses = []
+        for dp, opt in zip(dps, opts):
+            opt.zero_grad()
+            loss = dp(x, y)
+            loss.backward()
+            losses.append(float(loss.detach()))
+        noise_l = max(noise_l, abs(losses[0] - losses[1]))
+        assert abs(losses[0] - losses[2]) < 3 * noise_l + 5e-2 * max(1.0, abs(losses[0])), (step, losses)
+        for (k, pe), p2, pg in zip(models[0].named_parameters(), models[1].parameters(), models[2].parameters()):
+            assert pg.grad is not None and torch.isfinite(pg.grad).all(), k
+            noise = rel(pe.grad, p2.grad)
+            assert rel(pg.grad, pe.grad) < 3 * noise + 5e-2, (step, k, noise, rel(pg.grad, pe.grad))
+        for opt in opts:
+            opt.step()
+    assert dps[2].stats["graph_captures"] == 1 and dps[2].stats["graph_replays"] == 3
+    for k, v in models[0].state_dict().items():
+        if "num_batches" in k:
+            assert torch.equal(v, models[2].state_dict()[k]), k
 
 
 def test_data_parallel_fused_loss_resnet():
