@@ -81,7 +81,10 @@ def _timed(fn, steps: int, device) -> float:
     torch.cuda.synchronize(device)
     dist.barrier()
     ms = torch.tensor([e0.elapsed_time(e1)], device=device)
-    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    every = [torch.zeros_like(ms) for _ in range(dist.get_world_size())]
+    dist.all_gather(every, ms)
+    _timed.by_rank = [round(float(t.item()) / steps, 3) for t in every]      # ms per step on every rank (spread = the
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)                                 # slowest chip sets the job's rate)
     return float(ms.item())
 
 
@@ -139,7 +142,7 @@ def run_ours(args, rank, local_rank, world):
                 break
             step_dev(i)
         step_dev(0)
-    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    sampler = ClockSampler(local_rank, period_ms=50).start() if rank == 0 else None
     l0 = _lib.LAUNCHES
     ms = _timed(step_dev, args.steps, device)
     launches = _lib.LAUNCHES - l0
@@ -151,9 +154,13 @@ def run_ours(args, rank, local_rank, world):
     final_loss = float(trainer.last_loss.item())
     stats = dict(trainer.model.stats)
     comm = getattr(trainer.model.backend, "name", "?")
+    if hasattr(trainer.model.backend, "mode"):          # nvls = reduced inside the NVSwitch, vmm / ipc = two-shot peer-to-peer
+        comm += ":" + trainer.model.backend.mode + ":" + str(dict(trainer.model.backend.stats))
+    by_rank = list(getattr(_timed, "by_rank", []) or [])
     destroy_process_group()
     return ms, ms_e2e, launches, clocks, {"final_loss": final_loss, "ddp": stats, "grad_comm": comm,
-                                          "cuda_graph": bool(trainer._graph is not None)}
+                                          "cuda_graph": bool(trainer._graph is not None),
+                                          "ms_per_step_by_rank": by_rank}
 
 
 def run_reference(args, rank, local_rank, world):
@@ -206,7 +213,7 @@ def run_reference(args, rank, local_rank, world):
 
     for i in range(args.warmup):
         step_dev(i)
-    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    sampler = ClockSampler(local_rank, period_ms=50).start() if rank == 0 else None
     ms = _timed(step_dev, args.steps, device)
     clocks = sampler.stop() if sampler else {}
     for i in range(max(1, args.warmup // 2)):

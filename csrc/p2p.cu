@@ -662,7 +662,7 @@ int pick_blocks_mc(long long work_items, int requested) {
     long long b = (work_items + AR_THREADS * 4 - 1) / (AR_THREADS * 4);
     if (b < 1) b = 1;
     static int cap = -1;
-    if (cap < 0) cap = env_int("PTDB200_MC_MAX_BLOCKS", 32);     // measured at N = 4: 16-32 CTAs already give the full rate
+    if (cap < 0) cap = env_int("PTDB200_MC_MAX_BLOCKS", 16);     // measured at N = 4 and 8: 8-16 CTAs already give the full rate (profiles/allreduce_sweep_n8.json)
     if (b > cap) b = cap;
     return (int)b;
 }
