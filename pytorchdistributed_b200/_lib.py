@@ -165,10 +165,22 @@ def stream_ptr(device: Optional[torch.device] = None) -> int:
 LAUNCHES = 0   # entry-point calls that launch device work (bench.py reports it as gpu_launches)
 
 
+_PEER_OK = ("ptd_peer_copy", "ptd_peer_copy_bulk", "ptd_reduce_sum_f32", "ptd_allreduce", "ptd_broadcast", "ptd_shard",
+            "ptd_p2p", "ptd_vmm")      # entry points whose tensors legitimately live on other GPUs
+
+
 def call(name: str, *args: Any) -> None:
     global LAUNCHES
     lib = require()
     LAUNCHES += 1
+    if not name.startswith(_PEER_OK):
+        for a in args:
+            if isinstance(a, torch.Tensor):
+                if a.is_cuda and a.device.index != torch.cuda.current_device():
+                    raise RuntimeError(f"{name}: tensor on {a.device} but the current device is cuda:"
+                                       f"{torch.cuda.current_device()} - kernels launch on the current device "
+                                       "(wrap the call in torch.cuda.device(...))")
+                break
     rc = getattr(lib, name)(*[_conv(a) for a in args])
     if rc != 0:
         msg = lib.ptd_last_error()

@@ -61,7 +61,8 @@ class Conv2d(nn.Module):
                     if self._shadow is None or self._shadow.shape != w.shape or self._shadow.device != w.device:
                         self._shadow = torch.empty(w.shape, device=w.device, dtype=torch.bfloat16, memory_format=CL)
                     from .. import _lib
-                    _lib.call("ptd_cast_f32_to_bf16", w.detach(), self._shadow, w.numel(), F_._stream())
+                    with torch.cuda.device(w.device):       # the cast runs on the weight's GPU, whatever is current
+                        _lib.call("ptd_cast_f32_to_bf16", w.detach(), self._shadow, w.numel(), F_._stream())
             self._shadow_key = key
         return self._shadow
 
@@ -171,17 +172,19 @@ class Linear(nn.Module):
                     if self._shadow is None or self._shadow.device != w.device:
                         self._shadow = torch.empty(w.shape, device=w.device, dtype=torch.bfloat16)
                     from .. import _lib
-                    _lib.call("ptd_cast_f32_to_bf16", w.detach().contiguous(), self._shadow, w.numel(), F_._stream())
+                    with torch.cuda.device(w.device):
+                        _lib.call("ptd_cast_f32_to_bf16", w.detach().contiguous(), self._shadow, w.numel(), F_._stream())
                 else:
                     self._shadow = w.detach().to(torch.bfloat16)
             self._shadow_key = key
         return self._shadow
 
-    def forward(self, x: torch.Tensor, relu: bool = False) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, relu: bool = False, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """``out``: preallocated fp32 ``[rows, out_features]`` block to write the result into (tensor-core path only)."""
         if self.small:
             return F_.small_linear(x, self.weight, self.bias, relu)
-        out = F_.linear(x.reshape(x.size(0), -1), self.weight, self.shadow(), self.bias)
-        return torch.relu(out) if relu else out
+        res = F_.linear(x.reshape(x.size(0), -1), self.weight, self.shadow(), self.bias, out=None if relu else out)
+        return torch.relu(res) if relu else res
 
     def extra_repr(self) -> str:
         return f"in_features={self.in_features}, out_features={self.out_features}, bias={self.bias is not None}"

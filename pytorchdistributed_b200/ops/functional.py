@@ -16,6 +16,7 @@ Reference call sites: every layer of torchvision ``ResNet(Bottleneck,[3,4,6,3])`
 from __future__ import annotations
 
 import ctypes
+import functools
 import os
 import weakref
 from typing import Optional, Tuple
@@ -30,6 +31,19 @@ CL = torch.channels_last
 
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
+
+
+def _on_device(fn):
+    """Run ``fn`` with its first argument's GPU as the current device.  Kernels launch on the CURRENT device and
+    stream: a module living on cuda:1 that is called while cuda:0 is current (a model-parallel forward) would
+    otherwise run on GPU 0's SMs and reach its own tensors over NVLink - or fault where peer access is off."""
+    @functools.wraps(fn)
+    def wrapper(x, *args, **kwargs):
+        if isinstance(x, torch.Tensor) and x.is_cuda and x.device.index != torch.cuda.current_device():
+            with torch.cuda.device(x.device):
+                return fn(x, *args, **kwargs)
+        return fn(x, *args, **kwargs)
+    return wrapper
 
 
 # ------------------------------------------------------------------------------------------------
@@ -61,6 +75,7 @@ def is_nhwc_bf16(x: torch.Tensor) -> bool:
     return x.dtype == torch.bfloat16 and x.dim() == 4 and x.is_contiguous(memory_format=CL)
 
 
+@_on_device
 def as_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
     """Bring any 4-D activation to bf16 channels_last (no copy if already there)."""
     if is_nhwc_bf16(x):
@@ -182,6 +197,7 @@ class _ConvBnAct(torch.autograd.Function):
         return dx, dw, None, dgamma, dbeta, None, None, gout, None, None, None, None, None, None
 
 
+@_on_device
 def conv_bn_act(x, weight, w_bf16, gamma, beta, running_mean, running_var, residual=None, stride=1, pad=0,
                 eps=1e-5, momentum=0.1, relu=True, stem=False):
     if not x.is_cuda:
@@ -211,6 +227,7 @@ class _Conv(torch.autograd.Function):
         return dx, dw, None, None, None
 
 
+@_on_device
 def conv2d(x, weight, w_bf16, stride=1, pad=0):
     if not x.is_cuda:
         return ref.conv2d(x, weight, stride, pad)
@@ -238,12 +255,14 @@ class _BnAct(torch.autograd.Function):
         return dy, dgamma, dbeta, None, None, gout, None, None, None
 
 
+@_on_device
 def batch_norm_act(y, gamma, beta, running_mean, running_var, residual=None, eps=1e-5, momentum=0.1, relu=False):
     if not y.is_cuda:
         return ref.batch_norm_act(y, gamma, beta, running_mean, running_var, residual, eps, momentum, relu)
     return _BnAct.apply(y, gamma, beta, running_mean, running_var, residual, eps, momentum, relu)
 
 
+@_on_device
 def affine_act(y, scale, shift, residual=None, relu=False):
     """Inference-mode BN (per-channel affine) + residual + ReLU; no autograd (eval only)."""
     if not y.is_cuda:
@@ -258,6 +277,7 @@ def affine_act(y, scale, shift, residual=None, relu=False):
 # ------------------------------------------------------------------------------------------------
 # stem helpers
 # ------------------------------------------------------------------------------------------------
+@_on_device
 def to_nhwc4(x: torch.Tensor) -> torch.Tensor:
     """fp32 NCHW image batch [N,3,H,W] -> bf16 NHWC with a zero 4th channel (stem input, any H x W)."""
     n, c, h, w = x.shape
@@ -273,6 +293,7 @@ def stem_s2d_ok(h: int, w: int) -> bool:
     return h % 16 == 0 and w % 32 == 0 and os.environ.get("PTDB200_STEM_S2D", "1") != "0"
 
 
+@_on_device
 def to_s2d(x: torch.Tensor) -> torch.Tensor:
     """fp32 NCHW image batch [N,3,H,W] -> bf16 space-to-depth stem input, logical shape [N,16,H/2+3,W/2+3]
     (channels_last): pixel (hs, ws) = the 2x2 block at (2hs-3, 2ws-3) of the zero-padded image, 12 of 16 channels
@@ -290,6 +311,7 @@ def stem_input(x: torch.Tensor) -> torch.Tensor:
     return to_s2d(x) if stem_s2d_ok(x.shape[2], x.shape[3]) else to_nhwc4(x)
 
 
+@_on_device
 def stem_pack(weight: torch.Tensor) -> torch.Tensor:
     """bf16 [2][64][256]: [0] = [64][8][8][4] for the NHWC4 stem, [1] = [64][4][4][16] for the space-to-depth stem."""
     wp = torch.empty((2, 64, 256), device=weight.device, dtype=torch.bfloat16)
@@ -299,6 +321,7 @@ def stem_pack(weight: torch.Tensor) -> torch.Tensor:
     return wp
 
 
+@_on_device
 def stem_fprop_raw(xin: torch.Tensor, wp: torch.Tensor):
     """``xin`` from :func:`stem_input` (16 channels = space-to-depth, 4 = NHWC4), ``wp`` from :func:`stem_pack`."""
     n, c, h, w = xin.shape
@@ -358,6 +381,7 @@ class _StemBnReluPool(torch.autograd.Function):
         return None, dw, None, sums[1], sums[0], None, None, None, None
 
 
+@_on_device
 def stem_bn_relu_pool(xin, weight, wp, gamma, beta, running_mean, running_var, eps=1e-5, momentum=0.1):
     """Training-mode stem + BN + ReLU + maxpool on a CUDA stem input whose conv output has even height and width."""
     return _StemBnReluPool.apply(xin, weight, wp, gamma, beta, running_mean, running_var, eps, momentum)
@@ -389,6 +413,7 @@ class _MaxPool(torch.autograd.Function):
         return dx
 
 
+@_on_device
 def max_pool_3x3_s2(x):
     if not x.is_cuda:
         return ref.max_pool_3x3_s2(x)
@@ -414,6 +439,7 @@ class _AvgPool(torch.autograd.Function):
         return dx
 
 
+@_on_device
 def global_avg_pool(x):
     """[N,C,H,W] -> [N,C] (bf16), i.e. AdaptiveAvgPool2d(1) + flatten."""
     if not x.is_cuda:
@@ -426,11 +452,18 @@ def global_avg_pool(x):
 # ------------------------------------------------------------------------------------------------
 class _Linear(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, a, weight, w_bf16, bias):
+    def forward(ctx, a, weight, w_bf16, bias, out_box=None):
         a = a.to(torch.bfloat16).contiguous()
         m, k = a.shape
         n = weight.shape[0]
-        out = torch.empty((m, n), device=a.device, dtype=torch.float32)
+        # out_box: a one-element list holding a preallocated fp32 [m, n] row block (e.g. the rows of a micro-batch inside
+        # the pipeline's output tensor) that the kernel writes in place of a fresh tensor.  Boxed so that autograd does
+        # not see it as an input of this node.
+        if out_box is not None:
+            out = out_box[0]
+            assert out.shape == (m, n) and out.dtype == torch.float32 and out.is_contiguous() and out.device == a.device
+        else:
+            out = torch.empty((m, n), device=a.device, dtype=torch.float32)
         _lib.call("ptd_linear_fwd", a, w_bf16, bias, out, m, n, k, _stream())
         ctx.save_for_backward(a, w_bf16)
         ctx.has_bias = bias is not None
@@ -451,13 +484,43 @@ class _Linear(torch.autograd.Function):
             _lib.call("ptd_linear_wgrad", a, d16, dw, m, n, k, _stream())
         if ctx.has_bias and ctx.needs_input_grad[3]:
             db = dout.float().sum(0)
-        return da, dw, None, db
+        return da, dw, None, db, None
 
 
-def linear(a, weight, w_bf16, bias):
+@_on_device
+def linear(a, weight, w_bf16, bias, out=None):
+    """``out``: optional preallocated fp32 ``[rows, out_features]`` block the result is written into (CUDA only)."""
     if not a.is_cuda:
-        return ref.linear(a, weight, bias)
-    return _Linear.apply(a, weight, w_bf16, bias)
+        res = ref.linear(a, weight, bias)
+        if out is not None:
+            out.copy_(res.detach())
+        return res
+    return _Linear.apply(a, weight, w_bf16, bias, None if out is None else [out])
+
+
+class _GatherRows(torch.autograd.Function):
+    """The pieces ARE consecutive row blocks of ``buf`` already (each was written there by its producer): returns
+    ``buf`` as one tensor without a concatenation pass; the backward hands every piece its rows of the gradient."""
+
+    @staticmethod
+    def forward(ctx, buf_box, *pieces):
+        buf = buf_box[0]
+        ctx.sizes = [p.size(0) for p in pieces]
+        row = 0
+        for p in pieces:
+            if p.data_ptr() != buf[row:row + p.size(0)].data_ptr():      # a producer that could not write in place
+                buf[row:row + p.size(0)].copy_(p)
+            row += p.size(0)
+        return buf.view_as(buf)
+
+    @staticmethod
+    def backward(ctx, g):
+        return (None,) + tuple(g.split(ctx.sizes, dim=0))
+
+
+def gather_rows(buf: torch.Tensor, pieces):
+    """``torch.cat(pieces)`` for pieces that already live in consecutive row blocks of ``buf``."""
+    return _GatherRows.apply([buf], *pieces)
 
 
 class _SoftmaxCE(torch.autograd.Function):
@@ -480,6 +543,7 @@ class _SoftmaxCE(torch.autograd.Function):
         return dlogits * g, None
 
 
+@_on_device
 def cross_entropy(logits, target):
     """Mean softmax cross-entropy; ``target`` is class indices [B] or probabilities [B, C]."""
     if not logits.is_cuda:
@@ -518,6 +582,7 @@ class _SmallLinear(torch.autograd.Function):
         return dx, dw, db, None
 
 
+@_on_device
 def small_linear(x, w, b, relu=False):
     if not x.is_cuda:
         return ref.small_linear(x, w, b, relu)
@@ -693,6 +758,7 @@ class _Bottleneck(torch.autograd.Function):
         return tuple(grads)
 
 
+@_on_device
 def bottleneck(x, units, stride: int, eps: float, momentum: float):
     """``units``: list of (weight, w_bf16, gamma, beta, running_mean, running_var) for conv1, conv2, conv3 and
     optionally the downsample branch.  CUDA, training mode only."""

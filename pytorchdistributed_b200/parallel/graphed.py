@@ -23,10 +23,22 @@ import torch
 from torch import nn
 
 
+def _dense(t: torch.Tensor) -> bool:
+    return t.is_contiguous() or (t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last))
+
+
 def _mark_shadows_stale(module: nn.Module) -> None:
     for m in module.modules():
         if hasattr(m, "_shadow_key"):
             m._shadow_key = None
+
+
+def _order_after(consumer: torch.device, producer: torch.device) -> None:
+    """``consumer``'s current stream waits for everything issued so far on ``producer``'s current stream."""
+    if consumer != producer:
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(producer))
+        torch.cuda.current_stream(consumer).wait_event(ev)
 
 
 class _Replay(torch.autograd.Function):
@@ -34,7 +46,14 @@ class _Replay(torch.autograd.Function):
     def forward(ctx, x: torch.Tensor, anchor: torch.Tensor, owner: "GraphedStage", i: int):
         ctx.owner, ctx.i = owner, i
         with torch.cuda.device(owner.device):           # replay launches on the current device's stream
-            owner.static_in[i].copy_(x)
+            if owner.pull_from is not None and x.data_ptr() == owner.pull_from[i].data_ptr():
+                # the forward graph itself pulls its input from the producer stage's static output (peer memory):
+                # only the ordering between the two devices' streams is left to do here
+                _order_after(owner.device, x.device)
+            else:
+                owner.static_in[i].copy_(x)
+                if owner.pull_from is not None:      # unexpected input: the captured pull would overwrite it
+                    raise RuntimeError("graphed stage with a captured input pull got a different input tensor")
             owner.fwd[i].replay()
         return owner.static_out[i].detach()
 
@@ -42,9 +61,15 @@ class _Replay(torch.autograd.Function):
     def backward(ctx, g: torch.Tensor):
         owner, i = ctx.owner, ctx.i
         with torch.cuda.device(owner.device):
-            owner.static_gout[i].copy_(g)
+            if g.data_ptr() != owner.static_gout[i].data_ptr():      # (a consumer stage may have pushed it there already)
+                owner.static_gout[i].copy_(g)
             owner.bwd[i].replay()
             owner.accumulate(i)
+        if owner.push_gin_to is not None:
+            # the backward graph pushed the input gradient into the producer stage's buffer on the other device
+            gin = owner.push_gin_to[i]
+            _order_after(gin.device, owner.device)
+            return gin, None, None, None
         gin = owner.static_gin[i]
         return gin, None, None, None
 
@@ -53,8 +78,25 @@ class GraphedStage:
     """``n`` graph pairs for ``module`` on ``device`` with inputs shaped like ``sample`` (one micro-batch)."""
 
     def __init__(self, module: nn.Module, device: torch.device, sample: torch.Tensor, n: int,
-                 input_requires_grad: bool) -> None:
+                 input_requires_grad: bool, pull_from: Optional[Sequence[torch.Tensor]] = None,
+                 push_gin_to: Optional[Sequence[torch.Tensor]] = None,
+                 out_slices: Optional[Sequence[torch.Tensor]] = None) -> None:
+        """``pull_from[i]``: tensor (usually on the previous stage's GPU) that micro-batch i's forward graph copies
+        into its static input with a captured peer-copy kernel; ``push_gin_to[i]``: tensor (on that GPU) its backward
+        graph writes the input gradient into - the stage boundary then costs no launch of its own.  ``out_slices[i]``:
+        preallocated block handed to the module as ``out=`` (the classifier writes its logits there)."""
+        from .. import _lib
         self.module, self.device, self.n = module, device, n
+        self.pull_from = list(pull_from) if pull_from is not None else None
+        self.push_gin_to = list(push_gin_to) if push_gin_to is not None else None
+
+        def peer_copy(dst: torch.Tensor, src: torch.Tensor) -> None:
+            nb = src.numel() * src.element_size()
+            if nb % 16 == 0 and dst.data_ptr() % 16 == 0 and src.data_ptr() % 16 == 0:
+                _lib.call("ptd_peer_copy", dst, src, nb, torch.cuda.current_stream(device).cuda_stream)
+            else:
+                dst.copy_(src, non_blocking=True)
+
         self.params: List[nn.Parameter] = [p for p in module.parameters() if p.requires_grad]
         self.fwd: List[torch.cuda.CUDAGraph] = []
         self.bwd: List[torch.cuda.CUDAGraph] = []
@@ -90,7 +132,10 @@ class GraphedStage:
                     _mark_shadows_stale(module)
                 gf = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(gf, pool=pool, stream=side):
-                    out = module(x)
+                    if self.pull_from is not None:
+                        with torch.no_grad():
+                            peer_copy(x, self.pull_from[i])
+                    out = module(x) if out_slices is None else module(x, out=out_slices[i])
                 outs.append(out)
                 self.fwd.append(gf)
                 self.static_in.append(x)
@@ -104,6 +149,9 @@ class GraphedStage:
                 with torch.cuda.graph(gb, pool=pool, stream=side):
                     grads = torch.autograd.grad(outs[i], ([self.static_in[i]] if input_requires_grad else []) + self.params,
                                                 self.static_gout[i], allow_unused=True)
+                    if self.push_gin_to is not None and input_requires_grad:
+                        with torch.no_grad():
+                            peer_copy(self.push_gin_to[i], grads[0].contiguous() if not _dense(grads[0]) else grads[0])
                 outs[i] = None
                 self.bwd[i] = gb
                 self.static_gin[i] = grads[0] if input_requires_grad else None

@@ -25,6 +25,7 @@ from torch import nn
 from .. import _lib
 from ..comm import p2p as _p2p  # noqa: F401
 from ..models.resnet import Bottleneck, ResNet
+from ..ops import functional as F_
 
 _GROUPS = {}
 
@@ -125,9 +126,17 @@ class _Stage2(nn.Module):
         super().__init__()
         self.seq2, self.fc = seq2, fc
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         x = self.seq2(x)
-        return self.fc(x.view(x.size(0), -1))
+        return _fc_into(self.fc, x.view(x.size(0), -1), out)
+
+
+def _fc_into(fc: nn.Module, feat: torch.Tensor, out: Optional[torch.Tensor]) -> torch.Tensor:
+    """Classifier of one micro-batch, written straight into its rows of the pipeline's output tensor when the layer
+    can do that (our tensor-core ``Linear`` on CUDA); any other layer returns a fresh tensor and is copied in later."""
+    if out is not None and feat.is_cuda and getattr(fc, "small", True) is False:
+        return fc(feat, out=out)
+    return fc(feat)
 
 
 class PipelineParallelResNet50(ModelParallelResNet50):
@@ -152,7 +161,18 @@ class PipelineParallelResNet50(ModelParallelResNet50):
             o = g1.static_out[0]                 # shape / strides of the activation that crosses the boundary
             act = torch.empty_strided(o.shape, o.stride(), dtype=o.dtype, device=self.devices[1]).normal_()
             stage2 = _Stage2(self.seq2, self.fc)
-            g2 = GraphedStage(stage2, self.devices[1], act, n_full, input_requires_grad=True)
+            # every micro-batch's logits land in their rows of ONE output tensor (room for an eager tail split)
+            with torch.cuda.device(self.devices[1]):
+                self._out_buf = torch.empty(((n_full + 1) * self.split_size, self.fc.out_features),
+                                            dtype=torch.float32, device=self.devices[1])
+            slices = [self._out_buf[i * self.split_size:(i + 1) * self.split_size] for i in range(n_full)]
+            if self.transfer == "p2p":
+                # the stage boundary rides inside the replayed work: stage 2's forward graph pulls the activation out
+                # of stage 1's static output, its backward graph pushes the activation gradient into stage 1's buffer
+                g2 = GraphedStage(stage2, self.devices[1], act, n_full, input_requires_grad=True,
+                                  pull_from=g1.static_out, push_gin_to=g1.static_gout, out_slices=slices)
+            else:
+                g2 = GraphedStage(stage2, self.devices[1], act, n_full, input_requires_grad=True, out_slices=slices)
             self._graphs = (n_full, g1, g2)
         return self._graphs
 
@@ -164,33 +184,49 @@ class PipelineParallelResNet50(ModelParallelResNet50):
             s = splits[i]
             return g1(s, i) if i < n_full else self.seq1(s)
 
+        fused_boundary = g2.pull_from is not None
+        rows = [s.size(0) for s in splits]
+        starts = [sum(rows[:i]) for i in range(len(rows))]
+        out_buf = self._out_buf[:x.size(0)]
+
         def stage2(a, i):
             if i < n_full:
                 return g2(a, i)
             a = self.seq2(a)
-            return self.fc(a.view(a.size(0), -1))
+            return _fc_into(self.fc, a.view(a.size(0), -1), out_buf[starts[i]:starts[i] + rows[i]])
+
+        def boundary(a, i):
+            # graph-replayed micro-batches carry the transfer inside stage 2's graphs
+            return a if (fused_boundary and i < n_full) else self._boundary(a)
 
         ret: List[torch.Tensor] = []
-        prev = self._boundary(stage1(0))
+        prev = boundary(stage1(0), 0)
         for i in range(1, len(splits)):
             ret.append(stage2(prev, i - 1))
-            prev = self._boundary(stage1(i))
+            prev = boundary(stage1(i), i)
         ret.append(stage2(prev, len(splits) - 1))
-        return torch.cat(ret)
+        # (the returned tensor aliases the stage's static output buffer: the next forward overwrites it)
+        return F_.gather_rows(out_buf, ret)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self.cuda_graph and self.training and torch.is_grad_enabled() and self._graphed(x) is not None:
             return self._forward_graphed(x)
-        splits = iter(x.split(self.split_size, dim=0))
-        s_next = next(splits)
-        s_prev = self._boundary(self.seq1(s_next))
+        # Every micro-batch's classifier writes its [b, classes] rows of ONE preallocated output (no concatenation pass
+        # at the end, unlike the reference's torch.cat, notebook 03 cell 12).
+        parts = list(x.split(self.split_size, dim=0))
+        out_dev = self.devices[1] if self._on_gpu else x.device
+        out = torch.empty((x.size(0), self.fc.out_features), dtype=torch.float32, device=out_dev)
         ret: List[torch.Tensor] = []
-        for s_next in splits:
-            # A. s_prev runs on the second device
-            s_prev = self.seq2(s_prev)
-            ret.append(self.fc(s_prev.view(s_prev.size(0), -1)))
-            # B. s_next runs on the first device, concurrently with A; its transfer rides the side streams
-            s_prev = self._boundary(self.seq1(s_next))
-        s_prev = self.seq2(s_prev)
-        ret.append(self.fc(s_prev.view(s_prev.size(0), -1)))
-        return torch.cat(ret)
+        row = 0
+
+        def head(feat: torch.Tensor) -> None:
+            nonlocal row
+            ret.append(_fc_into(self.fc, feat.view(feat.size(0), -1), out[row:row + feat.size(0)]))
+            row += feat.size(0)
+
+        s_prev = self._boundary(self.seq1(parts[0]))
+        for s_next in parts[1:]:
+            head(self.seq2(s_prev))                        # A. the previous micro-batch runs on the second device
+            s_prev = self._boundary(self.seq1(s_next))     # B. the next one on the first, concurrently; its transfer
+        head(self.seq2(s_prev))                            #    rides the side streams
+        return F_.gather_rows(out, ret)

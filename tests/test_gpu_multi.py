@@ -552,3 +552,98 @@ def test_pipeline_matches_unsplit_model(transfer):
     mp_.load_state_dict(pp.state_dict())
     with torch.no_grad():
         assert torch.allclose(mp_(x).cpu(), pp.eval()(x).cpu(), atol=2e-2, rtol=2e-2)
+
+
+@pytest.mark.parametrize("split,graph", [(2, False), (3, False), (8, False), (3, True)])
+def test_pipeline_gradients_match_unsplit_model_per_split_size(split, graph):
+    """Training-mode gradient parity per split size (3 leaves an uneven tail of 2): the pipeline must equal the
+    UNSPLIT model run micro-batch by micro-batch (BatchNorm sees micro-batch statistics in both), within the
+    distance between two runs of that reference; output rows land in one preallocated tensor (no concatenation)."""
+    _need(2)
+    from pytorchdistributed_b200.models import resnet50
+    from pytorchdistributed_b200.ops import functional as K
+    from pytorchdistributed_b200.parallel import PipelineParallelResNet50
+    rel = lambda a, b: float((a.float() - b.float()).norm() / (b.float().norm() + 1e-12))  # noqa: E731
+    torch.manual_seed(0)
+    pp = PipelineParallelResNet50(split_size=split, num_classes=32, transfer="p2p", cuda_graph=graph).train()
+    refs = [resnet50(num_classes=32).cuda(0).train() for _ in range(2)]
+    for r in refs:
+        r.load_state_dict(pp.state_dict())
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(8, 3, 64, 64, generator=g).cuda(0)
+    y = torch.randint(0, 32, (8,), generator=g)
+    for it in range(2 if graph else 1):              # graph mode: the second pass replays what the first captured
+        for m in [pp] + refs:
+            for p in m.parameters():
+                p.grad = None
+        out = pp(x)
+        assert out.shape == (8, 32) and out.device.index == 1
+        loss = K.cross_entropy(out, y.cuda(1))
+        loss.backward()
+        ref_losses = []
+        for r in refs:
+            # cross_entropy is the mean over rows, so micro-batch losses are weighted by their share of the batch
+            total = 0.0
+            for lo in range(0, 8, split):
+                hi = min(8, lo + split)
+                l = K.cross_entropy(r(x[lo:hi]), y[lo:hi].cuda(0)) * ((hi - lo) / 8)
+                l.backward()
+                total += float(l.detach())
+            ref_losses.append(total)
+        noise_l = abs(ref_losses[0] - ref_losses[1])
+        assert abs(float(loss.detach()) - ref_losses[0]) < 3 * noise_l + 3e-2 * max(1.0, abs(ref_losses[0])), (it, float(loss), ref_losses)
+        for (k, p), q, q2 in zip(pp.named_parameters(), refs[0].parameters(), refs[1].parameters()):
+            assert p.grad is not None and torch.isfinite(p.grad).all(), k
+            noise = rel(q.grad, q2.grad)
+            assert rel(p.grad.cpu(), q.grad.cpu()) < 3 * noise + 5e-2, (it, k, noise, rel(p.grad.cpu(), q.grad.cpu()))
+
+
+def _stage_run_gpu(rank, world, schedule, recompute):
+    """Process-per-stage pipeline on GPUs: rank r owns one stage of ResNet-50, activations / gradients travel with
+    NCCL send/recv; every rank also runs the FULL model on its own GPU as the reference for its stage's gradients."""
+    import torch
+    from pytorchdistributed_b200.models import resnet50
+    from pytorchdistributed_b200.ops import functional as K
+    from pytorchdistributed_b200.parallel import PipelineStage
+    from pytorchdistributed_b200.parallel.pipeline import _Stage2
+    dev = torch.device("cuda", rank)
+    rel = lambda a, b: float((a.float() - b.float()).norm() / (b.float().norm() + 1e-12))  # noqa: E731
+    torch.manual_seed(0)
+    models = [resnet50(num_classes=32).to(dev).train() for _ in range(3)]          # staged, reference, reference again
+    for m in models[1:]:
+        m.load_state_dict(models[0].state_dict())
+    seq1, seq2, fc = models[0].stage_modules()
+    part = seq1 if rank == 0 else _Stage2(seq2, fc)
+    stage = PipelineStage(part, rank, world, device=dev, loss_fn=K.cross_entropy, schedule=schedule, recompute=recompute)
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(10, 3, 64, 64, generator=g)
+    y = torch.randint(0, 32, (10,), generator=g)
+    loss = stage.train_step(x if rank == 0 else None, y if rank == world - 1 else None, split_size=4, batch_rows=10)
+    ref_losses = []
+    for m in models[1:]:
+        total = 0.0
+        for lo in range(0, 10, 4):
+            hi = min(10, lo + 4)
+            l = K.cross_entropy(m(x[lo:hi].to(dev)), y[lo:hi].to(dev)) * ((hi - lo) / 10)
+            l.backward()
+            total += float(l.detach())
+        ref_losses.append(total)
+    torch.cuda.synchronize(dev)
+    mine = {id(p) for p in part.parameters()}
+    worst = 0.0
+    for (k, p), q, q2 in zip(models[0].named_parameters(), models[1].parameters(), models[2].parameters()):
+        if id(p) not in mine:
+            continue
+        assert p.grad is not None and torch.isfinite(p.grad).all(), k
+        worst = max(worst, rel(p.grad, q.grad) - 3 * rel(q.grad, q2.grad))
+    return (float(loss) if loss is not None else None), ref_losses, worst
+
+
+@pytest.mark.parametrize("schedule,recompute", [("1f1b", False), ("gpipe", True)])
+def test_process_per_stage_pipeline_on_gpus(schedule, recompute):
+    _need(2)
+    res = run_ranks(_stage_run_gpu, 2, (schedule, recompute), backend="nccl")
+    loss, ref_losses, _ = res[1]
+    assert abs(loss - ref_losses[0]) < 3 * abs(ref_losses[0] - ref_losses[1]) + 3e-2 * max(1.0, abs(ref_losses[0])), (loss, ref_losses)
+    for rank, (_, _, worst) in enumerate(res):
+        assert worst < 5e-2, (rank, worst)            # beyond 3x the reference's own run-to-run noise by at most 5 %
