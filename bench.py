@@ -164,6 +164,12 @@ def run_ours(args, rank, local_rank, world):
 
 
 def run_reference(args, rank, local_rank, world):
+    global REF_SCRIPT
+    if not os.path.exists(REF_SCRIPT):
+        # baseline/_ref is git-ignored: on a fresh clone fall back to the read-only reference tree itself
+        alt = os.path.join("/root/reference", "02 DDP基本概念", "ddp_gpus_torchrun.py")
+        if os.path.exists(alt):
+            REF_SCRIPT = alt
     if not os.path.exists(REF_SCRIPT):
         return None, f"reference copy missing at {os.path.relpath(REF_SCRIPT, ROOT)}"
     try:

@@ -3,20 +3,25 @@
 // Two warp-specialised kernels cover every GEMM-shaped op of the framework:
 //
 //   igemm_f  ("forward-like", persistent):  D[M,N] = A[M,K] * B[N,K]^T
-//       A rows are output pixels.  A is either a plain K-major matrix fetched by TMA (1x1 stride-1
-//       convolutions, FC) or gathered on the fly from an NHWC tensor by four producer warps with
-//       cp.async into the same 128-byte-swizzled image TMA would have written (3x3/7x7/strided
-//       convolutions, data-gradient).  B (weights) always arrives by TMA, K-major (fprop) or
-//       MN-major (dgrad reads the forward weight tensor in place - no transposed copy exists).
-//       Epilogue: TMEM -> registers -> bf16 NHWC store, fused per-channel sum / sum-of-squares
-//       for BatchNorm, optional residual addend, or fp32 + bias for the classifier.
+//       A rows are output pixels.  The pixel-row operand reaches shared memory by TMA in three forms - a plain
+//       K-major tile (1x1 stride-1 convolutions, FC), an im2col walk over the NHWC tensor (3x3, strided 1x1, data
+//       gradients: cuTensorMapEncodeIm2col, zero fill in the padding) or an overlapping-window patch (the
+//       space-to-depth stem) - always as the 128-byte-swizzled image tcgen05 reads.  A cp.async gather by four extra
+//       producer warps survives as the fallback for stem inputs the patch form cannot take (and as an A/B switch,
+//       PTD_IGEMM_FORCE_GATHER).  B (weights) always arrives by TMA, K-major (fprop) or MN-major (dgrad reads the
+//       forward weight tensor in place - no transposed copy exists).  CTA pairs (cta_group::2) share 256-row tiles
+//       on the K-heavy 1x1 layers.
+//       Epilogue: TMEM -> registers -> bf16 staged in shared memory -> TMA store (or LDS + STG when rows are
+//       remapped / an addend is fused), fused per-channel sum / sum-of-squares for BatchNorm, optional (mask-gated)
+//       residual addend, or fp32 + bias for the classifier.
 //
 //   igemm_w  ("weight-gradient", split-K):  dW[Cout,Kw] += dY[P,Cout]^T * Xcol[P,Kw]
-//       Both operands are MN-major (the reduction runs over pixels).  dY arrives by TMA, Xcol by
-//       TMA (1x1) or gather.  fp32 partial tiles are reduced with vector red.global.add.
+//       Both operands are MN-major (the reduction runs over pixels).  dY arrives by TMA, Xcol by TMA (tiled, im2col
+//       or patch).  fp32 partial tiles are reduced with vector red.global.add - straight into whatever buffer the
+//       caller names (with DDP: the gradient bucket itself).
 //
-// Roles per CTA: warps 0-7 epilogue (TMEM lane quarter = warp % 4), warp 8 TMA producer,
-// warp 9 TMEM allocator + single-thread MMA issuer, warps 10-13 gather producers.
+// Roles per CTA: 8 or 16 epilogue warps (TMEM lane quarter = warp % 4), one TMA producer warp, one warp that allocates
+// TMEM and issues tcgen05.mma from a single thread, and (gather fallback only) four cp.async producer warps.
 // The reference reaches these ops through cuDNN/cuBLAS (call sites
 // R/03 模型并行/03_model_parallel.ipynb#cell4-7,12).
 #include <stdlib.h>

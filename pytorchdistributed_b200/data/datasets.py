@@ -6,8 +6,8 @@
   ``randn(size, 10)`` inputs, ``randint(0, 1, (size, 5))`` int64 labels (all zero).
 * ``generate_random_data`` - ``R/03 模型并行/03_model_parallel.ipynb#cell7``: a CPU batch
   ``randn(B,3,H,W)`` and float one-hot labels ``[B, num_classes]``.
-* ``SyntheticImageDataset`` / ``DeviceSyntheticBatches`` are additions for the
-  ResNet-50 benchmarks (no dataset can be downloaded on the bench box).
+* ``SyntheticImageDataset`` is an addition for the ResNet-50 runs of the CLI scripts (no dataset can be
+  downloaded on the bench box).
 """
 from __future__ import annotations
 

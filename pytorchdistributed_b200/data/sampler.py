@@ -6,7 +6,7 @@ Behavioural contract (what the reference relies on at
 permutation of ``range(len(dataset))`` (seed + epoch), the list is padded by
 wrap-around (or truncated with ``drop_last``) to a multiple of the world size,
 and rank ``r`` keeps positions ``r, r+W, r+2W, ...``.  ``set_epoch`` reseeds
-(``ddp_gpus.py:47``).  ``tests/test_sampler.py`` checks index-for-index parity
+(``ddp_gpus.py:47``).  ``tests/test_cpu_data.py`` checks index-for-index parity
 against torch's sampler over a grid.
 """
 from __future__ import annotations

@@ -94,6 +94,12 @@ class ModelParallelResNet50(ResNet):
             seq1.to(self.devices[0])
             seq2.to(self.devices[1])
             fc.to(self.devices[1])
+            d0, d1 = self.devices[0].index, self.devices[1].index
+            if d0 != d1 and _lib.available():
+                # our copy kernels address the other stage's memory directly: both directions must be mapped (torch
+                # only enables peer access lazily for its own copies)
+                _lib.call("ptd_p2p_enable_peer_access", d0, d1)
+                _lib.call("ptd_p2p_enable_peer_access", d1, d0)
 
     def _boundary(self, x: torch.Tensor) -> torch.Tensor:
         if not self._on_gpu:

@@ -26,14 +26,15 @@ from pytorchdistributed_b200.train import Trainer  # noqa: E402
 
 def main(rank: int, world_size: int, max_epochs: int, batch_size: int, train_dataset, extra: dict):
     os.environ["MASTER_PORT"] = str(extra["port"])
-    ddp_setup(rank, world_size)
+    ddp_setup(rank, world_size, backend="gloo" if extra["backend"] == "gloo" else None)
     train_dataloader = DataLoader(train_dataset, batch_size=batch_size, pin_memory=torch.cuda.is_available(),
                                   shuffle=False, sampler=DistributedSampler(train_dataset))
     model = ToyLinear(20, 1)
     optimizer = SGD(model.parameters(), lr=1e-3)
     loss_fn = torch.nn.functional.mse_loss if extra["loss"] == "mse" else None
     trainer = Trainer(model=model, gpu_id=rank, optimizer=optimizer, train_dataloader=train_dataloader,
-                      save_every=extra["save_every"], snapshot_path=extra["snapshot_path"], loss_fn=loss_fn)
+                      save_every=extra["save_every"], snapshot_path=extra["snapshot_path"], loss_fn=loss_fn,
+                      ddp_kwargs=extra["ddp_kwargs"])
     trainer.train(max_epochs)
     destroy_process_group()
 
@@ -48,8 +49,18 @@ if __name__ == "__main__":
     parser.add_argument("--snapshot_path", default="snapshot.pt")
     parser.add_argument("--loss", choices=["ce", "mse"], default="ce")
     parser.add_argument("--port", type=int, default=12355)
+    # communication knobs (additive; see scripts/train_ddp_torchrun.py)
+    parser.add_argument("--backend", choices=["auto", "p2p", "nccl", "gloo"], default="auto")
+    parser.add_argument("--dtype", choices=["fp32", "bf16"], default="fp32", help="gradient format on the wire")
+    parser.add_argument("--bucket_cap_mb", type=float, default=25)
     args = parser.parse_args()
 
     world_size = args.world_size or torch.cuda.device_count() or 2
-    extra = dict(save_every=args.save_every, snapshot_path=args.snapshot_path, loss=args.loss, port=args.port)
+    kw = {"bucket_cap_mb": args.bucket_cap_mb}
+    if args.backend != "auto":
+        kw["comm"] = "p2p" if args.backend == "p2p" else "torch"
+    if args.dtype == "bf16":
+        kw["wire_dtype"] = torch.bfloat16
+    extra = dict(save_every=args.save_every, snapshot_path=args.snapshot_path, loss=args.loss, port=args.port,
+                 backend=args.backend, ddp_kwargs=kw)
     mp.spawn(main, args=(world_size, args.max_epochs, args.batch_size, train_dataset, extra), nprocs=world_size)

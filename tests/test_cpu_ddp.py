@@ -170,3 +170,22 @@ def test_checkpoint_resume_roundtrip(tmp_path):
     second = torch.load(snap)
     assert second["EPOCHS_RUN"] == 2
     assert not torch.equal(first["MODEL_STATE"]["weight"], second["MODEL_STATE"]["weight"])
+
+
+def test_cli_communication_flags_are_additive(tmp_path):
+    """The survey's additive flags (--backend / --dtype / --bucket_cap_mb) parse on both launchers and keep the golden
+    output; the reference's own flags and defaults are unchanged (ddp_gpus.py:88-92, ddp_gpus_torchrun.py:88-96)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                          "--master-port", "29641", os.path.join(root, "scripts", "train_ddp_torchrun.py"),
+                          "--max_epochs", "1", "--batch_size", "32", "--backend", "gloo", "--dtype", "bf16",
+                          "--bucket_cap_mb", "1"], capture_output=True, text=True, env=env, timeout=280)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "Epoch: 0 | Batchsize: 32 | Steps: 32" in out.stdout
+    helptext = subprocess.run([sys.executable, os.path.join(root, "scripts", "train_ddp_spawn.py"), "--help"],
+                              capture_output=True, text=True, timeout=120).stdout
+    for flag in ("--max_epochs", "--batch_size", "--backend", "--dtype", "--bucket_cap_mb"):
+        assert flag in helptext
