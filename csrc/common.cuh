@@ -186,25 +186,6 @@ __device__ __forceinline__ void tma_load_im2col(uint32_t dst, const CUtensorMap*
         : "memory");
 }
 
-// Multicast variants: the box lands at the same shared-memory offset of every CTA in `mask` and completes bytes on
-// the mbarrier at the same offset in each of them.
-__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1,
-                                               uint16_t mask) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-        " [%0], [%1, {%3, %4}], [%2], %5;"
-        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask)
-        : "memory");
-}
-__device__ __forceinline__ void tma_load_im2col_mc(uint32_t dst, const CUtensorMap* m, uint64_t* bar, int c, int w,
-                                                   int h, int n, uint32_t off_w, uint32_t off_h, uint16_t mask) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes.multicast::cluster"
-        " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8}, %9;"
-        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n),
-          "h"((uint16_t)off_w), "h"((uint16_t)off_h), "h"(mask)
-        : "memory");
-}
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }

@@ -700,11 +700,11 @@ __device__ __forceinline__ void w_gather_loop(const WParams& p, Barriers<Cfg::ST
     }
 }
 
-// CL2: launched as clusters of two CTAs that work on neighbouring Cout blocks of the same (n block, split): the
-// im2col / activation tile (B) is identical for both, so each CTA fetches half of its sub-tiles and TMA-multicasts
-// them into both shared memories - the L2 traffic of B halves (the kernel is L2-bandwidth bound: loads alone take
-// 89 of 97 us on layer3's 3x3, profiles/).  A stage is recycled only after BOTH MMAs released it (multicast commit).
-template <int NSUB, int B_MODE, bool CL2, bool M2>
+// (A variant that ran CTA pairs on neighbouring Cout blocks and multicast the shared activation tile into both was
+// measured no faster - the kernel is bound by per-SM ingress, which multicast does not reduce - and is gone: TMA
+// multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung
+// the GPU, and a weight-gradient operand handed in through the C ABI may be peer memory.)
+template <int NSUB, int B_MODE, bool M2>
 __global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_kernel(const __grid_constant__ WParams p) {
     using Cfg = WCfg<NSUB, B_MODE, M2>;
     constexpr int MROWS = M2 ? 256 : 128;
@@ -720,19 +720,9 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_ke
 
     // CTA -> (split, m block, n block)
     int bid = blockIdx.x;
-    int n_blk, m_blk, split;
-    const uint32_t crank = CL2 ? cluster_ctarank() : 0;
-    if (CL2) {
-        int pq = bid >> 1;
-        n_blk = pq % p.n_blocks; pq /= p.n_blocks;
-        const int mpairs = p.m_blocks >> 1;
-        m_blk = (pq % mpairs) * 2 + (int)crank;
-        split = pq / mpairs;
-    } else {
-        n_blk = bid % p.n_blocks; bid /= p.n_blocks;
-        m_blk = bid % p.m_blocks; bid /= p.m_blocks;
-        split = bid;
-    }
+    const int n_blk = bid % p.n_blocks; bid /= p.n_blocks;
+    const int m_blk = bid % p.m_blocks; bid /= p.m_blocks;
+    const int split = bid;
     const int kb_begin = split * p.kb_per_split;
     const int kb_end = min(p.num_kb, kb_begin + p.kb_per_split);
     const int nkb = kb_end - kb_begin;     // host guarantees >= 1
@@ -742,7 +732,7 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_ke
         if (B_TMA) tma_prefetch_desc(&p.tmB);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&bars->full[s], B_TMA ? 1 : 1 + NUM_GATHER_THREADS);
-            mbar_init(&bars->empty[s], CL2 ? 2 : 1);
+            mbar_init(&bars->empty[s], 1);
         }
         mbar_init(&bars->tmem_full[0], 1);
         mbar_fence_init();
@@ -750,7 +740,6 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_ke
     if (warp == MMA_WARP) tmem_alloc<Cfg::TMEM_COLS>(&bars->tmem_base);
     tc_fence_before();
     __syncthreads();
-    if (CL2) cluster_sync_all();          // the peer's barriers exist before anything is multicast at them
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_base;
 
@@ -787,16 +776,8 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_ke
                 }
                 if (B_MODE == AM_TILED && !skip_b) {
 #pragma unroll
-                    for (int j = 0; j < NSUB; ++j) {
-                        if (CL2) {
-                            if ((j & 1) == (int)crank)
-                                tma_load_2d_mc(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage],
-                                               (n_blk * NSUB + j) * 64, kb * 64, 3);
-                        } else {
-                            tma_load_2d(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage],
-                                        (n_blk * NSUB + j) * 64, kb * 64);
-                        }
-                    }
+                    for (int j = 0; j < NSUB; ++j)
+                        tma_load_2d(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage], (n_blk * NSUB + j) * 64, kb * 64);
                 }
                 if (B_MODE == AM_IM2COL && !skip_b) {
                     // 64 output pixels starting at kb*64: one im2col load per (tap, channel block) sub-tile
@@ -812,13 +793,7 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_ke
                         const int tap = sj / p.g.cblocks;
                         const int cb = sj - tap * p.g.cblocks;
                         const int r = tap / p.g.S, s_ = tap - r * p.g.S;
-                        if (CL2) {
-                            if ((j & 1) == (int)crank)
-                                tma_load_im2col_mc(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage], cb * 64, iw0, ih0,
-                                                   n0, s_, r, 3);
-                        } else {
-                            tma_load_im2col(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage], cb * 64, iw0, ih0, n0, s_, r);
-                        }
+                        tma_load_im2col(b_dst + j * SUB_TILE_BYTES, &p.tmB, &bars->full[stage], cb * 64, iw0, ih0, n0, s_, r);
                     }
                 }
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -844,8 +819,7 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_ke
                         umma_f16(tmem_base + h * BLOCK_N, adesc, bdesc, idesc, (i | kk) != 0 ? 1u : 0u);
                     }
                 }
-                if (CL2) umma_commit_mc(&bars->empty[stage], 3);      // releases the stage in both CTAs of the pair
-                else umma_commit(&bars->empty[stage]);
+                umma_commit(&bars->empty[stage]);
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
             umma_commit(&bars->tmem_full[0]);
@@ -880,7 +854,6 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_ke
 
     tc_fence_before();
     __syncthreads();
-    if (CL2) cluster_sync_all();          // neither CTA leaves while the other may still signal or write into it
     if (warp == MMA_WARP) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
@@ -988,10 +961,10 @@ int pick_block_n(int n) {
     return 64;
 }
 
-template <int NSUB, int B_MODE, bool CL2, bool M2>
+template <int NSUB, int B_MODE, bool M2>
 int launch_w_impl(WParams& p, int grid, cudaStream_t stream) {
     using Cfg = WCfg<NSUB, B_MODE, M2>;
-    auto kern = igemm_w_kernel<NSUB, B_MODE, CL2, M2>;
+    auto kern = igemm_w_kernel<NSUB, B_MODE, M2>;
     static bool configured[64] = {false};
     int dev = 0;
     PTD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -999,24 +972,7 @@ int launch_w_impl(WParams& p, int grid, cudaStream_t stream) {
         PTD_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
         configured[dev & 63] = true;
     }
-    if (!CL2) {
-        kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>(p);
-    } else {
-        cudaLaunchConfig_t cfg;
-        memset(&cfg, 0, sizeof(cfg));
-        cfg.gridDim = dim3(grid);
-        cfg.blockDim = dim3(Cfg::THREADS);
-        cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
-        cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 2;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        PTD_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p));
-    }
+    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>(p);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }
@@ -1044,15 +1000,8 @@ int launch_w(WParams& p, cudaStream_t stream) {
     p.kb_per_split = ceil_div_i(p.num_kb, splits);
     p.splits = ceil_div_i(p.num_kb, p.kb_per_split);            // no empty split
     const int grid = tiles * p.splits;
-    static int use_cluster = -1;
-    // measured: correct, but no faster than unicast on B200 (L2 already merges the pair's requests; the kernel is
-    // bound by per-SM ingress, which multicast does not reduce) - kept as an option, off by default
-    if (use_cluster < 0) { const char* e = getenv("PTD_WGRAD_CLUSTER"); use_cluster = e ? atoi(e) : 0; }
-    if (m2) return launch_w_impl<NSUB, B_MODE, false, M2_OK>(p, grid, stream);
-    constexpr bool CL_OK = (B_MODE == AM_TILED || B_MODE == AM_IM2COL) && NSUB % 2 == 0;
-    if (CL_OK && (p.m_blocks % 2) == 0 && use_cluster)
-        return launch_w_impl<NSUB, B_MODE, CL_OK, false>(p, grid, stream);
-    return launch_w_impl<NSUB, B_MODE, false, false>(p, grid, stream);
+    if (m2) return launch_w_impl<NSUB, B_MODE, M2_OK>(p, grid, stream);
+    return launch_w_impl<NSUB, B_MODE, false>(p, grid, stream);
 }
 
 template <int B_MODE>
