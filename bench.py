@@ -119,7 +119,8 @@ def run_ours(args, rank, local_rank, world):
     torch.manual_seed(0)
     model = resnet50()
     opt = SGD(model.parameters(), lr=1e-3)
-    trainer = Trainer(model, train_dataloader=None, optimizer=opt, quiet=True, cuda_graph=args.graph)
+    trainer = Trainer(model, train_dataloader=None, optimizer=opt, quiet=True, cuda_graph=args.graph,
+                      fuse_optimizer=os.environ.get("PTDB200_BENCH_FUSE_SGD", "0") == "1")
     n_stage = 2
     hx, hy = _make_batches(n_stage, args.batch, args.img, pinned=True, seed=1234 + rank)
     dx = [x.to(device) for x in hx]
@@ -160,6 +161,8 @@ def run_ours(args, rank, local_rank, world):
     destroy_process_group()
     return ms, ms_e2e, launches, clocks, {"final_loss": final_loss, "ddp": stats, "grad_comm": comm,
                                           "cuda_graph": bool(trainer._graph is not None),
+                                          "fused_sgd_in_allreduce": bool(trainer.fused_optimizer),
+                                          "native_reducer": bool(getattr(trainer.model, "_native", False)),
                                           "ms_per_step_by_rank": by_rank}
 
 

@@ -181,10 +181,58 @@ __device__ __forceinline__ void st_u4(uint4* p, const uint4& v) {
     asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// ---- optimizer update fused behind the reduction (DDP: `loss.backward(); optimizer.step()`, ddp_gpus.py:41-42) ----------
+// The parameters, momentum buffers and bf16 weight shadows of a gradient bucket live in flat arrays with the BUCKET'S
+// layout (element i of the bucket belongs to element i of each), so the SGD step is a pure element-wise pass:
+//     g = grad[i] + wd * p[i];   buf[i] = mom * buf[i] + g  (buf starts at zero, which makes the first step buf = g);
+//     p[i] -= lr * g;   shadow[i] = bf16(p[i])
+// It runs at the END of the all-reduce kernel, on exactly the vectors whose reduction this block has seen complete:
+// block b of rank r reduces vectors {begin_r + b*T + t + k*G*T}; the closing rank barrier tells block b of every rank
+// that block b of every OTHER rank has stored ITS such vectors everywhere - so block b may update the same index
+// pattern of all N slices without any grid-wide synchronisation.  The gradient stays in the bucket untouched.
+struct SgdEpilogue {
+    float* param;            // nullptr = no fused update
+    float* momentum_buf;     // nullptr = plain SGD
+    __nv_bfloat162* shadow;  // nullptr = no bf16 shadow to refresh
+    const float* lr_dev;     // learning rate in device memory (a captured step follows the host's schedule)
+    float momentum, weight_decay;
+};
+
+__device__ __forceinline__ void sgd_epilogue(const SgdEpilogue& sg, const float4* grad, int world, long long n4) {
+    const float lr = *sg.lr_dev;
+    const long long per = (n4 + world - 1) / world;
+    const long long stride = (long long)gridDim.x * AR_THREADS;
+    const long long t0 = (long long)blockIdx.x * AR_THREADS + threadIdx.x;
+    float4* p4 = reinterpret_cast<float4*>(sg.param);
+    float4* m4 = reinterpret_cast<float4*>(sg.momentum_buf);
+    for (int s = 0; s < world; ++s) {
+        const long long b = min(n4, per * s), e = min(n4, b + per);
+        for (long long i = b + t0; i < e; i += stride) {
+            const float4 g0 = ld_f4(grad + i);          // system-scope load: written by a peer (or the switch) just now
+            float4 p = p4[i];
+            float4 g = make_float4(fmaf(sg.weight_decay, p.x, g0.x), fmaf(sg.weight_decay, p.y, g0.y),
+                                   fmaf(sg.weight_decay, p.z, g0.z), fmaf(sg.weight_decay, p.w, g0.w));
+            if (m4 != nullptr) {
+                const float4 m = m4[i];
+                g = make_float4(fmaf(sg.momentum, m.x, g.x), fmaf(sg.momentum, m.y, g.y), fmaf(sg.momentum, m.z, g.z),
+                                fmaf(sg.momentum, m.w, g.w));
+                m4[i] = g;
+            }
+            p.x -= lr * g.x; p.y -= lr * g.y; p.z -= lr * g.z; p.w -= lr * g.w;
+            p4[i] = p;
+            if (sg.shadow != nullptr) {
+                sg.shadow[2 * i] = __floats2bfloat162_rn(p.x, p.y);
+                sg.shadow[2 * i + 1] = __floats2bfloat162_rn(p.z, p.w);
+            }
+        }
+    }
+}
+
 // ---- two-shot all-reduce, fp32 storage ------------------------------------------------------------
 // n4 = number of float4 elements (buffer length is padded to a multiple of 4 floats by the caller).
 template <int WORLD, bool WEAK>
-__global__ void __launch_bounds__(AR_THREADS) allreduce_f32_kernel(PeerPtrs pp, int rank, long long n4, float scale) {
+__global__ void __launch_bounds__(AR_THREADS) allreduce_f32_kernel(PeerPtrs pp, int rank, long long n4, float scale,
+                                                                   SgdEpilogue sg) {
     const uint32_t seq = seq_begin(pp, rank);
     rank_barrier(pp, rank, WORLD, seq);
     const long long per = (n4 + WORLD - 1) / WORLD;
@@ -230,6 +278,7 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_f32_kernel(PeerPtrs pp, 
     }
     rank_barrier(pp, rank, WORLD, seq + 1);
     seq_end(pp, rank, seq + 1);
+    if (sg.param != nullptr) sgd_epilogue(sg, reinterpret_cast<const float4*>(pp.buf[rank]), WORLD, n4);
 }
 
 // ---- two-shot all-reduce, bf16 storage (fp32 accumulate) -----------------------------------------------
@@ -274,7 +323,7 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_bf16_kernel(PeerPtrs pp,
 // switch sums the N copies in fp32) and one multimem.st (the switch writes all N copies) per vector.
 template <bool BF16>
 __global__ void __launch_bounds__(AR_THREADS) allreduce_mc_kernel(PeerPtrs pp, uint4* mc, int rank, int world,
-                                                                  long long nvec, float scale) {
+                                                                  long long nvec, float scale, SgdEpilogue sg) {
     const uint32_t seq = seq_begin(pp, rank);
     rank_sync(pp, rank, world, seq);                    // every rank's contribution is final
     const long long per = (nvec + world - 1) / world;
@@ -327,6 +376,8 @@ __global__ void __launch_bounds__(AR_THREADS) allreduce_mc_kernel(PeerPtrs pp, u
     }
     rank_sync(pp, rank, world, seq + 1);                // every rank's stores have landed everywhere
     seq_end(pp, rank, seq + 1);
+    // pp.buf[rank] = the local (unicast) mapping of the bucket, only needed for the fused update
+    if (!BF16 && sg.param != nullptr) sgd_epilogue(sg, reinterpret_cast<const float4*>(pp.buf[rank]), world, nvec);
 }
 
 // ---- all-reduce of an fp32 buffer with a bf16 wire format, one kernel, three phases ----------------------------
@@ -743,8 +794,8 @@ extern "C" int ptd_p2p_max_blocks() { return MAX_BLOCKS; }
 // ---- collectives --------------------------------------------------------------------------------------------
 // bufs / pads: HOST arrays of `world` device pointers (this rank's mapping of every rank's buffer / signal pad).
 // Kernels sharing a signal pad must be stream-ordered with respect to each other.
-extern "C" int ptd_allreduce_inplace(const void* const* bufs, const void* const* pads, int rank, int world,
-                                     long long numel, int is_bf16, float scale, int blocks, void* stream) {
+static int launch_two_shot(const void* const* bufs, const void* const* pads, int rank, int world, long long numel,
+                           int is_bf16, float scale, int blocks, void* stream, const SgdEpilogue& sg) {
     PeerPtrs pp;
     int rc = fill_peers(pp, bufs, pads, world);
     if (rc) return rc;
@@ -758,8 +809,8 @@ extern "C" int ptd_allreduce_inplace(const void* const* bufs, const void* const*
 #define PTD_AR(W)                                                                                   \
     case W:                                                                                         \
         if (is_bf16) allreduce_bf16_kernel<W><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale); \
-        else if (weak) allreduce_f32_kernel<W, true><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale); \
-        else allreduce_f32_kernel<W, false><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale);      \
+        else if (weak) allreduce_f32_kernel<W, true><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale, sg); \
+        else allreduce_f32_kernel<W, false><<<grid, AR_THREADS, 0, st>>>(pp, rank, nvec, scale, sg);      \
         break;
     switch (world) {
         PTD_AR(1) PTD_AR(2) PTD_AR(3) PTD_AR(4) PTD_AR(5) PTD_AR(6) PTD_AR(7) PTD_AR(8)
@@ -767,6 +818,13 @@ extern "C" int ptd_allreduce_inplace(const void* const* bufs, const void* const*
 #undef PTD_AR
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
+}
+
+extern "C" int ptd_allreduce_inplace(const void* const* bufs, const void* const* pads, int rank, int world,
+                                     long long numel, int is_bf16, float scale, int blocks, void* stream) {
+    SgdEpilogue none;
+    memset(&none, 0, sizeof(none));
+    return launch_two_shot(bufs, pads, rank, world, numel, is_bf16, scale, blocks, stream, none);
 }
 
 extern "C" int ptd_broadcast_inplace(const void* const* bufs, const void* const* pads, int rank, int world, int root,
@@ -885,10 +943,11 @@ extern "C" int ptd_reduce_sum_f32(float* dst, const void* const* srcs, int n_src
 // ---- NVLS / bf16-wire entry points --------------------------------------------------------------------------
 // In-place all-reduce through the switch.  mc_buf: multicast mapping of the symmetric buffer (csrc/vmm.cu); pads:
 // unicast pads; mc_pad: multicast mapping of the pads (NULL = flag barrier).  scale as in ptd_allreduce_inplace.
-extern "C" int ptd_allreduce_mc(void* mc_buf, const void* const* pads, const void* mc_pad, int rank, int world,
-                                long long numel, int is_bf16, float scale, int blocks, void* stream) {
+static int launch_mc(void* mc_buf, const void* const* bufs, const void* const* pads, const void* mc_pad, int rank,
+                     int world, long long numel, int is_bf16, float scale, int blocks, void* stream,
+                     const SgdEpilogue& sg) {
     PeerPtrs pp;
-    int rc = fill_peers(pp, nullptr, pads, world, mc_pad);
+    int rc = fill_peers(pp, bufs, pads, world, mc_pad);
     if (rc) return rc;
     PTD_REQUIRE(mc_buf != nullptr && ((uintptr_t)mc_buf & 15) == 0, "allreduce_mc: needs a 16-byte aligned multicast address");
     const int per_vec = is_bf16 ? 8 : 4;
@@ -896,10 +955,34 @@ extern "C" int ptd_allreduce_mc(void* mc_buf, const void* const* pads, const voi
     const long long nvec = numel / per_vec;
     const int grid = pick_blocks_mc((nvec + world - 1) / world, blocks);
     cudaStream_t st = (cudaStream_t)stream;
-    if (is_bf16) allreduce_mc_kernel<true><<<grid, AR_THREADS, 0, st>>>(pp, (uint4*)mc_buf, rank, world, nvec, scale);
-    else allreduce_mc_kernel<false><<<grid, AR_THREADS, 0, st>>>(pp, (uint4*)mc_buf, rank, world, nvec, scale);
+    if (is_bf16) allreduce_mc_kernel<true><<<grid, AR_THREADS, 0, st>>>(pp, (uint4*)mc_buf, rank, world, nvec, scale, sg);
+    else allreduce_mc_kernel<false><<<grid, AR_THREADS, 0, st>>>(pp, (uint4*)mc_buf, rank, world, nvec, scale, sg);
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
+}
+
+extern "C" int ptd_allreduce_mc(void* mc_buf, const void* const* pads, const void* mc_pad, int rank, int world,
+                                long long numel, int is_bf16, float scale, int blocks, void* stream) {
+    SgdEpilogue none;
+    memset(&none, 0, sizeof(none));
+    return launch_mc(mc_buf, nullptr, pads, mc_pad, rank, world, numel, is_bf16, scale, blocks, stream, none);
+}
+
+// fp32 all-reduce (through the switch when mc_buf is given, two-shot otherwise) with the SGD step of the bucket's
+// parameters fused behind it - see SgdEpilogue.  bufs[rank] must be the local mapping of the bucket in both cases.
+extern "C" int ptd_allreduce_fused_sgd(const void* const* bufs, void* mc_buf, const void* const* pads, const void* mc_pad,
+                                       int rank, int world, long long numel, float scale, int blocks,
+                                       const PtdSgdEpilogue* sgd, void* stream) {
+    PTD_REQUIRE(sgd != nullptr && sgd->param != nullptr && sgd->lr_dev != nullptr,
+                "allreduce_fused_sgd: param and lr_dev are required");
+    PTD_REQUIRE(bufs != nullptr && bufs[rank] != nullptr, "allreduce_fused_sgd: the local mapping of the bucket is required");
+    PTD_REQUIRE((((uintptr_t)sgd->param | (uintptr_t)sgd->momentum_buf | (uintptr_t)sgd->shadow_bf16) & 15) == 0,
+                "allreduce_fused_sgd: param / momentum / shadow arrays must be 16-byte aligned");
+    SgdEpilogue sg;
+    sg.param = sgd->param; sg.momentum_buf = sgd->momentum_buf; sg.shadow = (__nv_bfloat162*)sgd->shadow_bf16;
+    sg.lr_dev = sgd->lr_dev; sg.momentum = sgd->momentum; sg.weight_decay = sgd->weight_decay;
+    if (mc_buf != nullptr) return launch_mc(mc_buf, bufs, pads, mc_pad, rank, world, numel, 0, scale, blocks, stream, sg);
+    return launch_two_shot(bufs, pads, rank, world, numel, 0, scale, blocks, stream, sg);
 }
 
 // All-reduce of the LOCAL fp32 buffer `grad` (numel a multiple of 8) with bf16 on the wire: `stages` are the unicast

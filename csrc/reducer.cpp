@@ -1,4 +1,6 @@
-// Host-side gradient bucket planner and ready-tracking reducer (no CUDA in this file).
+// Host-side gradient bucket planner and reducer: ready tracking AND, for buckets bound to a communication recipe, the
+// whole launch sequence of a finished bucket (event on the compute stream, wait on the communication stream, the
+// all-reduce kernel - optionally with the fused SGD step -, completion event) in ONE native call per parameter.
 //
 // Serves the role of torch's C++ Reducer + _compute_bucket_assignment_by_size that the reference
 // reaches through DDP(model, device_ids=[gpu_id]) (R/02 DDP基本概念/ddp_gpus.py:35):
@@ -8,8 +10,12 @@
 //     size reaches the limit;
 //   * during backward each parameter is marked ready once; when the last parameter of a bucket
 //     arrives the bucket index is returned so the caller can launch that bucket's all-reduce;
-//   * the order in which parameters became ready is recorded for the one-time bucket rebuild.
+//   * the order in which parameters became ready is recorded for the one-time bucket rebuild;
+//   * ptd_reducer_bind_bucket attaches what a bucket's reduction needs (mappings, pads, scale, algorithm);
+//     ptd_reducer_mark_ready_launch then issues it the moment the bucket completes and ptd_reducer_finalize makes the
+//     compute stream wait for everything issued in this backward - the Python wrapper only counts.
 #include <stdint.h>
+#include <string.h>
 
 #include <algorithm>
 #include <mutex>
@@ -21,7 +27,15 @@
 
 namespace {
 
+struct BucketComm {
+    bool bound = false;
+    bool launched = false;
+    PtdBucketComm c;
+    cudaEvent_t ready = nullptr, done = nullptr;
+};
+
 struct Reducer {
+    std::vector<BucketComm> comm;     // per bucket
     std::vector<int> bucket_of;
     std::vector<int> bucket_size;     // parameters per bucket
     std::vector<int> pending;         // parameters not yet ready, per bucket
@@ -76,6 +90,7 @@ extern "C" int ptd_reducer_create(const int* bucket_of, int n_params, int n_buck
         r.bucket_size[bucket_of[i]]++;
     }
     r.pending = r.bucket_size;
+    r.comm.resize(n_buckets);
     r.ready.assign(n_params, 0);
     r.ready_order.reserve(n_params);
     std::lock_guard<std::mutex> lk(g_mu);
@@ -150,5 +165,93 @@ extern "C" int ptd_reducer_reset(int id) {
 
 extern "C" int ptd_reducer_destroy(int id) {
     std::lock_guard<std::mutex> lk(g_mu);
-    return g_reducers.erase(id) ? 0 : -3;
+    auto it = g_reducers.find(id);
+    if (it == g_reducers.end()) return -3;
+    for (auto& bc : it->second.comm) {
+        if (bc.ready) cudaEventDestroy(bc.ready);
+        if (bc.done) cudaEventDestroy(bc.done);
+    }
+    g_reducers.erase(it);
+    return 0;
+}
+
+// Attach the communication recipe of `bucket` (copied).  algo: 1 = two-shot peer-to-peer, 2 = through the switch
+// (multimem), 3 = bf16 wire format; fuse_sgd != 0 adds the fused SGD step (algo 1 and 2).  Creates the bucket's two
+// events on the current device.
+extern "C" int ptd_reducer_bind_bucket(int id, int bucket, const PtdBucketComm* c) {
+    PTD_REQUIRE(c != nullptr && c->algo >= 1 && c->algo <= 3, "reducer_bind_bucket: algo must be 1, 2 or 3");
+    PTD_REQUIRE(c->world >= 2 && c->world <= 8 && c->rank >= 0 && c->rank < c->world, "reducer_bind_bucket: bad rank / world");
+    PTD_REQUIRE(!(c->fuse_sgd && c->algo == 3), "reducer_bind_bucket: the fused SGD step needs fp32 on the wire");
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_reducers.find(id);
+    PTD_REQUIRE(it != g_reducers.end(), "reducer_bind_bucket: unknown reducer %d", id);
+    Reducer& r = it->second;
+    PTD_REQUIRE(bucket >= 0 && bucket < (int)r.comm.size(), "reducer_bind_bucket: bucket %d outside [0,%d)", bucket, (int)r.comm.size());
+    BucketComm& bc = r.comm[bucket];
+    bc.c = *c;
+    if (!bc.ready) PTD_CUDA_CHECK(cudaEventCreateWithFlags(&bc.ready, cudaEventDisableTiming));
+    if (!bc.done) PTD_CUDA_CHECK(cudaEventCreateWithFlags(&bc.done, cudaEventDisableTiming));
+    bc.bound = true;
+    bc.launched = false;
+    return PTD_OK;
+}
+
+static int launch_bucket(BucketComm& bc, cudaStream_t compute, cudaStream_t comm) {
+    const PtdBucketComm& c = bc.c;
+    PTD_CUDA_CHECK(cudaEventRecord(bc.ready, compute));          // the bucket's gradients are final on the compute stream
+    PTD_CUDA_CHECK(cudaStreamWaitEvent(comm, bc.ready, 0));
+    int rc;
+    if (c.algo == 3) {
+        rc = ptd_allreduce_wire_bf16((float*)c.local, c.stages, c.mc_stage, c.pads, c.mc_pad, c.rank, c.world, c.numel,
+                                     c.scale, c.blocks, comm);
+    } else if (c.fuse_sgd) {
+        rc = ptd_allreduce_fused_sgd(c.bufs, c.algo == 2 ? c.mc_buf : nullptr, c.pads, c.mc_pad, c.rank, c.world, c.numel,
+                                     c.scale, c.blocks, &c.sgd, comm);
+    } else if (c.algo == 2) {
+        rc = ptd_allreduce_mc(c.mc_buf, c.pads, c.mc_pad, c.rank, c.world, c.numel, 0, c.scale, c.blocks, comm);
+    } else {
+        rc = ptd_allreduce_inplace(c.bufs, c.pads, c.rank, c.world, c.numel, 0, c.scale, c.blocks, comm);
+    }
+    if (rc) return rc;
+    PTD_CUDA_CHECK(cudaEventRecord(bc.done, comm));
+    bc.launched = true;
+    return PTD_OK;
+}
+
+// ptd_reducer_mark_ready + launch: when `param` completes a bound bucket, its reduction is issued on `comm_stream`
+// behind everything recorded so far on `compute_stream`.  Same return values as ptd_reducer_mark_ready; -5 if the
+// launch itself failed (ptd_last_error tells why).
+extern "C" int ptd_reducer_mark_ready_launch(int id, int param, void* compute_stream, void* comm_stream) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_reducers.find(id);
+    if (it == g_reducers.end()) return -3;
+    Reducer& r = it->second;
+    if (param < 0 || param >= (int)r.ready.size()) return -4;
+    if (r.ready[param]) return -2;
+    r.ready[param] = 1;
+    r.ready_order.push_back(param);
+    const int b = r.bucket_of[param];
+    if (--r.pending[b] != 0) return -1;
+    r.buckets_done++;
+    if (r.comm[b].bound && launch_bucket(r.comm[b], (cudaStream_t)compute_stream, (cudaStream_t)comm_stream) != PTD_OK)
+        return -5;
+    return b;
+}
+
+// End of a backward pass: `compute_stream` waits for every reduction issued in it.  Returns 1 when every bucket
+// completed, 0 when some did not (ptd_reducer_incomplete lists them), negative on error.  Does not reset the ready state.
+extern "C" int ptd_reducer_finalize(int id, void* compute_stream) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_reducers.find(id);
+    if (it == g_reducers.end()) return -3;
+    Reducer& r = it->second;
+    for (auto& bc : r.comm) {
+        if (!bc.launched) continue;
+        if (cudaStreamWaitEvent((cudaStream_t)compute_stream, bc.done, 0) != cudaSuccess) {
+            ptd_set_error("reducer_finalize: cudaStreamWaitEvent failed: %s", cudaGetErrorString(cudaGetLastError()));
+            return -5;
+        }
+        bc.launched = false;
+    }
+    return r.buckets_done == (int)r.bucket_size.size() ? 1 : 0;
 }

@@ -248,6 +248,19 @@ int ptd_vmm_destroy(int id);
  * ddp_gpus.py:41 (loss.backward() under DDP). */
 int ptd_allreduce_mc(void* mc_buf, const void* const* pads, const void* mc_pad, int rank, int world, long long numel,
                      int is_bf16, float scale, int blocks, void* stream);
+/* The same two reductions (mc_buf given: through the switch; NULL: two-shot) with the SGD step of the bucket fused behind
+ * them: parameters, momentum buffers and bf16 shadows are flat arrays in the BUCKET'S element order, updated by the block
+ * that has just seen the reduction of those elements complete.  `loss.backward(); optimizer.step()` of ddp_gpus.py:41-42
+ * with the communication kernel as the last touch of every gradient. */
+typedef struct {
+    float* param;            /* fp32 masters, bucket layout */
+    float* momentum_buf;     /* NULL = no momentum; starts at zero */
+    void* shadow_bf16;       /* NULL = none; bf16 copy of param refreshed in the same pass */
+    const float* lr_dev;     /* learning rate, one float in device memory */
+    float momentum, weight_decay;
+} PtdSgdEpilogue;
+int ptd_allreduce_fused_sgd(const void* const* bufs, void* mc_buf, const void* const* pads, const void* mc_pad, int rank,
+                            int world, long long numel, float scale, int blocks, const PtdSgdEpilogue* sgd, void* stream);
 /* Broadcast through the switch: the root stores each vector once (multimem.st), the NVSwitch writes every copy.  DDP's
  * construction-time parameter broadcast and per-forward buffer broadcast (ddp_gpus.py:35). */
 int ptd_broadcast_mc(const void* const* bufs, void* mc_buf, const void* const* pads, const void* mc_pad, int rank,
@@ -266,6 +279,28 @@ int ptd_reducer_ready_order(int id, int* out, int n);
 int ptd_reducer_incomplete(int id, int* out, int n);
 int ptd_reducer_reset(int id);
 int ptd_reducer_destroy(int id);
+/* What the reduction of one bucket needs, bound once per bucket; ptd_reducer_mark_ready_launch then issues it natively the
+ * moment the bucket's last gradient is marked (record an event on the compute stream, make the communication stream wait,
+ * launch the all-reduce - with the fused SGD step when fuse_sgd -, record the completion event) and ptd_reducer_finalize
+ * makes the compute stream wait for all of them: torch's C++ Reducer::mark_variable_ready / finalize_backward. */
+typedef struct {
+    int algo;                      /* 1 two-shot peer-to-peer, 2 through the switch (multimem), 3 bf16 wire format */
+    int rank, world, blocks;
+    long long numel;               /* fp32 elements, padded as the kernels require */
+    float scale;
+    void* local;                   /* this rank's bucket */
+    const void* bufs[8];           /* unicast mappings of every rank's bucket */
+    void* mc_buf;                  /* multicast mapping (algo 2) */
+    const void* stages[8];         /* bf16 staging buffers (algo 3) */
+    void* mc_stage;
+    const void* pads[8];
+    const void* mc_pad;
+    int fuse_sgd;
+    PtdSgdEpilogue sgd;
+} PtdBucketComm;
+int ptd_reducer_bind_bucket(int id, int bucket, const PtdBucketComm* c);
+int ptd_reducer_mark_ready_launch(int id, int param, void* compute_stream, void* comm_stream);
+int ptd_reducer_finalize(int id, void* compute_stream);
 
 #ifdef __cplusplus
 }

@@ -89,6 +89,18 @@ class BottleneckBwd(ctypes.Structure):
                 ("dz1", P), ("dx", P), ("mask", P * 4), ("gdst", P * 8)]
 
 
+class SgdEpilogue(ctypes.Structure):
+    """Mirror of PtdSgdEpilogue (include/ptdb200.h)."""
+    _fields_ = [("param", P), ("momentum_buf", P), ("shadow_bf16", P), ("lr_dev", P), ("momentum", F), ("weight_decay", F)]
+
+
+class BucketComm(ctypes.Structure):
+    """Mirror of PtdBucketComm (include/ptdb200.h)."""
+    _fields_ = [("algo", I), ("rank", I), ("world", I), ("blocks", I), ("numel", L), ("scale", F), ("local", P),
+                ("bufs", P * 8), ("mc_buf", P), ("stages", P * 8), ("mc_stage", P), ("pads", P * 8), ("mc_pad", P),
+                ("fuse_sgd", I), ("sgd", SgdEpilogue)]
+
+
 _LIB: Optional[ctypes.CDLL] = None
 _LOAD_ERROR: Optional[str] = None
 LIB_PATH = Path(__file__).resolve().parent / "lib" / "libptdb200.so"

@@ -67,6 +67,7 @@ _lib.register("ptd_vmm_destroy", [I])
 _lib.register("ptd_allreduce_mc", [P, P, P, I, I, L, I, F, I, P])
 _lib.register("ptd_allreduce_wire_bf16", [P, P, P, P, P, I, I, L, F, I, P])
 _lib.register("ptd_broadcast_mc", [P, P, P, P, I, I, I, L, I, P])
+_lib.register("ptd_allreduce_fused_sgd", [P, P, P, P, I, I, L, F, I, P, P])
 
 _LIVE: "weakref.WeakSet" = weakref.WeakSet()
 MODES = ("nvls", "vmm", "ipc")
@@ -484,6 +485,43 @@ class P2PCollectives:
         _lib.call("ptd_allreduce_inplace", self._ptrs(reg, off), pads, self.rank, self.world, n_pad, int(is_bf16),
                   scale, self.blocks, self._stream())
         self.stats["two_shot"] += 1
+
+    def bucket_comm(self, flat: torch.Tensor, sgd=None) -> "_lib.BucketComm":
+        """The recipe of ``all_reduce_avg(flat)`` as a ``PtdBucketComm`` for the native reducer (fp32 buckets): the same
+        algorithm choice, resolved once.  ``sgd``: an ``_lib.SgdEpilogue`` to fuse behind the reduction."""
+        reg, off = self._loc(flat)
+        n = flat.numel()
+        c = _lib.BucketComm()
+        c.rank, c.world, c.blocks = self.rank, self.world, self.blocks
+        c.scale = 1.0 / self.world
+        c.local = flat.data_ptr()
+        via_switch = lambda r: bool(r.mc) and (self.algo == "nvls" or (self.algo == "auto" and self.world >= 3))  # noqa: E731
+        for r in range(self.world):
+            c.bufs[r] = reg.ptrs[r] + off
+        preg, poff = self._loc(self.pads[0])
+        for r in range(self.world):
+            c.pads[r] = preg.ptrs[r] + poff
+        c.mc_pad = (preg.mc + poff) if (preg.mc and self.mc_barrier) else None
+        if self.wire_dtype is not None and sgd is None:
+            n8 = (n + 7) // 8 * 8
+            stage = self._stage(n8)
+            sreg, soff = self._loc(stage)
+            for r in range(self.world):
+                c.stages[r] = sreg.ptrs[r] + soff
+            c.mc_stage = (sreg.mc + soff) if via_switch(sreg) else None
+            c.algo, c.numel = 3, n8
+        else:
+            c.numel = (n + 3) // 4 * 4
+            if via_switch(reg):
+                c.algo, c.mc_buf = 2, reg.mc + off
+            else:
+                c.algo = 1
+        if sgd is not None:
+            c.fuse_sgd, c.sgd = 1, sgd
+        return c
+
+    def count(self, c: "_lib.BucketComm") -> None:
+        self.stats[{1: "two_shot", 2: "nvls", 3: "wire_bf16"}[c.algo]] += 1
 
     def _stage(self, numel: int) -> torch.Tensor:
         """bf16 staging buffer of the wire format, grown collectively (every rank sees the same request sizes)."""

@@ -129,6 +129,19 @@ class SGD(_FusedBase):
     @torch.no_grad()
     def step(self, closure=None, grad_scale: float = 1.0):
         loss = closure() if closure is not None else None
+        fused = getattr(self, "_ddp_fused", None)
+        if fused is not None:
+            self._lr_tensor(0, fused.device, self.param_groups[0]["lr"])      # keep the device copy of lr current
+            if fused.consume_fused_step():
+                # DistributedDataParallel.fuse_optimizer: the gradient all-reduce kernels of the backward that just ran
+                # already applied this step (parameters, momentum, bf16 shadows); only the bookkeeping is left
+                ps = [p for p in self.param_groups[0]["params"]]
+                torch.autograd.graph.increment_version(ps)
+                for p in ps:
+                    mod = self._shadow_mods.get(id(p))
+                    if mod is not None:
+                        mod.mark_shadow_fresh()
+                return loss
         for gi, group in enumerate(self.param_groups):
             lr, mom, wd = group["lr"], group["momentum"], group["weight_decay"]
             ps = [p for p in group["params"] if p.grad is not None]

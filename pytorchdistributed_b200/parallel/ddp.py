@@ -42,6 +42,9 @@ _MiB = 1024 * 1024
 
 _lib.register("ptd_plan_buckets", [ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_longlong, ctypes.c_void_p])
 _lib.register("ptd_reducer_create", [ctypes.c_void_p, ctypes.c_int, ctypes.c_int])
+_lib.register("ptd_reducer_bind_bucket", [ctypes.c_int, ctypes.c_int, ctypes.c_void_p])
+_lib.register("ptd_reducer_mark_ready_launch", [ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p])
+_lib.register("ptd_reducer_finalize", [ctypes.c_int, ctypes.c_void_p])
 _lib.register("ptd_reducer_mark_ready", [ctypes.c_int, ctypes.c_int])
 _lib.register("ptd_reducer_all_done", [ctypes.c_int])
 _lib.register("ptd_reducer_ready_order", [ctypes.c_int, ctypes.c_void_p, ctypes.c_int])
@@ -144,6 +147,8 @@ class DistributedDataParallel(nn.Module):
         self._index_of: Dict[int, int] = {id(p): i for i, p in enumerate(self._params)}
         self._reducer_id = 0
         self._buckets: List[_Bucket] = []
+        self._native = False
+        self._fused_opt = None
         self._grad_region: Optional[torch.Tensor] = None      # one symmetric allocation all buckets are carved from
         self._build_buckets(list(reversed(range(len(self._params)))))
         self._callback_queued = False
@@ -277,6 +282,94 @@ class DistributedDataParallel(nn.Module):
         if self._reducer_id <= 0:
             raise RuntimeError("ptd_reducer_create failed")
         self._view_of = {id(p): v for b in buckets for p, v in zip(b.params, b.views)}
+        self._bucket_starts = [b.flat.storage_offset() - self._grad_region.storage_offset() for b in buckets]
+        if getattr(self, "_fused_opt", None) is not None:
+            self._rehome_state()               # the flat optimizer state follows the (new) bucket layout
+        self._bind_native()
+
+    def _bind_native(self) -> None:
+        """Hand every bucket's reduction recipe to the native reducer: from then on marking a parameter ready is one
+        native call that also issues the finished bucket's all-reduce (events, stream switch, kernel)."""
+        self._native = False
+        self._bucket_comms = []
+        if (self.world_size == 1 or self._skip_allreduce or self._comm_stream is None
+                or not hasattr(self.backend, "bucket_comm") or os.environ.get("PTDB200_DDP_NATIVE", "1") == "0"):
+            return
+        fused = getattr(self, "_fused_opt", None) is not None
+        for bi, b in enumerate(self._buckets):
+            sgd = self._sgd_epilogue(bi) if fused else None
+            c = self.backend.bucket_comm(b.flat, sgd=sgd)
+            _lib.call("ptd_reducer_bind_bucket", self._reducer_id, bi, ctypes.addressof(c))
+            self._bucket_comms.append(c)
+        self._native = True
+
+    # ------------------------------------------------------------------ optimizer step fused behind the reduction
+    def fuse_optimizer(self, optimizer) -> bool:
+        """Let the all-reduce kernel of every bucket apply ``optimizer``'s SGD step to that bucket's parameters as its
+        epilogue (``csrc/p2p.cu: sgd_epilogue``): the communication kernel becomes the last touch of each gradient, and
+        ``optimizer.step()`` turns into bookkeeping.  Parameters, momentum buffers and the bf16 weight shadows are
+        re-homed into flat arrays that mirror the bucket layout.  Needs our fused ``SGD`` (one parameter group), the
+        peer-to-peer backend with fp32 on the wire and more than one rank; returns ``False`` (and changes nothing)
+        otherwise.  Between ``backward()`` and ``step()`` the parameters are then already updated - gradient clipping or
+        a skipped ``step()`` are not possible in this mode."""
+        from ..optim import SGD
+        ok = (isinstance(optimizer, SGD) and len(optimizer.param_groups) == 1 and self.world_size > 1
+              and hasattr(self.backend, "bucket_comm") and getattr(self.backend, "wire_dtype", None) is None
+              and self.device.type == "cuda" and not self._skip_allreduce
+              and {id(p) for p in optimizer.param_groups[0]["params"]} == {id(p) for p in self._params})
+        if not ok:
+            return False
+        self._fused_opt = optimizer
+        self._fused_stepped = False
+        self._rehome_state()
+        self._bind_native()
+        optimizer._ddp_fused = self
+        return True
+
+    def _rehome_state(self) -> None:
+        opt = self._fused_opt
+        group = opt.param_groups[0]
+        n = self._grad_region.numel()
+        with torch.no_grad():
+            new_p = torch.zeros(n, dtype=torch.float32, device=self.device)
+            new_s = torch.zeros(n, dtype=torch.bfloat16, device=self.device)
+            new_m = torch.zeros(n, dtype=torch.float32, device=self.device) if group["momentum"] != 0.0 else None
+            mods = opt._shadow_mods
+            for b, start in zip(self._buckets, self._bucket_starts):
+                for p, off in zip(b.params, b.offsets):
+                    pv = torch.as_strided(new_p, p.shape, p.stride(), start + off)
+                    pv.copy_(p.detach())
+                    p.data = pv
+                    if new_m is not None:
+                        mv = torch.as_strided(new_m, p.shape, p.stride(), start + off)
+                        old = opt.state[p].get("momentum_buffer")
+                        if old is not None:
+                            mv.copy_(old)
+                        opt.state[p]["momentum_buffer"] = mv
+                    m = mods.get(id(p))
+                    if m is not None:        # the module's bf16 shadow becomes a view of the flat shadow array
+                        m._shadow = torch.as_strided(new_s, p.shape, p.stride(), start + off)
+                        m._shadow_key = None
+                        m.shadow()
+            self._param_region, self._shadow_region, self._mom_region = new_p, new_s, new_m
+        opt._tables.clear()
+        self._lr_dev = opt._lr_tensor(0, self.device, group["lr"])
+
+    def _sgd_epilogue(self, bi: int) -> "_lib.SgdEpilogue":
+        group = self._fused_opt.param_groups[0]
+        start = self._bucket_starts[bi]
+        e = _lib.SgdEpilogue()
+        e.param = self._param_region.data_ptr() + 4 * start
+        e.momentum_buf = (self._mom_region.data_ptr() + 4 * start) if self._mom_region is not None else None
+        e.shadow_bf16 = self._shadow_region.data_ptr() + 2 * start
+        e.lr_dev = self._lr_dev.data_ptr()
+        e.momentum, e.weight_decay = float(group["momentum"]), float(group["weight_decay"])
+        return e
+
+    def consume_fused_step(self) -> bool:
+        """Called by ``optimizer.step()``: ``True`` when the backward that just ran already applied the update."""
+        done, self._fused_stepped = getattr(self, "_fused_stepped", False), False
+        return done
 
     # ------------------------------------------------------------------ public surface
     @contextlib.contextmanager
@@ -367,6 +460,19 @@ class DistributedDataParallel(nn.Module):
         if not self._callback_queued:
             torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
             self._callback_queued = True
+        if self._native:
+            # one native call: mark, and if this completed a bucket: event, stream switch, all-reduce kernel, event
+            b = _lib.call_ret("ptd_reducer_mark_ready_launch", self._reducer_id, self._index_of[id(p)],
+                              torch.cuda.current_stream(self.device).cuda_stream, self._comm_stream.cuda_stream)
+            if b >= 0:
+                bk = self._buckets[b]
+                self.stats["allreduce_launches"] += 1
+                self.stats["bytes_reduced"] += bk.flat.numel() * bk.flat.element_size()
+                self.backend.count(self._bucket_comms[b])
+                _lib.LAUNCHES += 1
+            elif b < -2:
+                raise RuntimeError(f"reducer error {b}: {_lib.require().ptd_last_error().decode()}")
+            return
         b = _lib.call_ret("ptd_reducer_mark_ready", self._reducer_id, self._index_of[id(p)])
         if b >= 0:
             self._launch_bucket(self._buckets[b])
@@ -390,6 +496,12 @@ class DistributedDataParallel(nn.Module):
 
     def _finalize_backward(self) -> None:
         self._callback_queued = False
+        if self._native:
+            rc = _lib.call_ret("ptd_reducer_finalize", self._reducer_id, torch.cuda.current_stream(self.device).cuda_stream)
+            if rc < 0:
+                raise RuntimeError(f"reducer error {rc}: {_lib.require().ptd_last_error().decode()}")
+            if rc == 1 and getattr(self, "_fused_opt", None) is not None:
+                self._fused_stepped = True          # every bucket's kernel also applied its SGD step
         if _lib.call_ret("ptd_reducer_all_done", self._reducer_id) != 1:
             n = len(self._buckets)
             out = (ctypes.c_int * n)()

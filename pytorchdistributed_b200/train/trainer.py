@@ -34,7 +34,7 @@ class Trainer:
                  gpu_id: Optional[int] = None, *, save_every: int = 0, snapshot_path: str = "snapshot.pt",
                  loss_fn: Optional[Callable] = None, resume: bool = False, ddp_kwargs: Optional[dict] = None,
                  quiet: bool = False, cuda_graph: bool = False, graph_warmup: int = 3,
-                 metrics_path: Optional[str] = None) -> None:
+                 metrics_path: Optional[str] = None, fuse_optimizer: bool = False) -> None:
         self.gpu_id = int(os.environ.get("LOCAL_RANK", 0)) if gpu_id is None else gpu_id
         self.device = torch.device("cuda", self.gpu_id) if torch.cuda.is_available() else torch.device("cpu")
         self.model = model.to(self.device)
@@ -54,6 +54,9 @@ class Trainer:
         self.model = DDP(self.model, device_ids=[self.gpu_id] if self.device.type == "cuda" else None, **kw)
         if hasattr(optimizer, "attach_model"):
             optimizer.attach_model(self.model.module)
+        # SGD step applied by the gradient all-reduce kernels themselves (DistributedDataParallel.fuse_optimizer);
+        # silently stays unfused where that is not possible (one rank, NCCL / gloo backend, another optimizer)
+        self.fused_optimizer = bool(fuse_optimizer) and self.model.fuse_optimizer(optimizer)
         # CUDA-graph replay of the whole step (zero_grad .. optimizer.step) once shapes have settled
         self.cuda_graph = bool(cuda_graph) and self.device.type == "cuda"
         self._graph_warmup = max(int(graph_warmup), 2)
