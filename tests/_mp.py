@@ -17,7 +17,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _entry(rank, world, port, fn, args, ret, backend):
+def _entry(rank, world, port, fn, args, ret, backend, hard_exit=False):
     sys.path.insert(0, ROOT)
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), LOCAL_RANK=str(rank),
                       WORLD_SIZE=str(world))
@@ -29,6 +29,8 @@ def _entry(rank, world, port, fn, args, ret, backend):
             dist.init_process_group("gloo", rank=rank, world_size=world)
         out = fn(rank, world, *args)
         ret[rank] = ("ok", out)
+        if hard_exit:              # the function killed its CUDA context on purpose: no orderly teardown is possible
+            os._exit(0)
     except Exception:  # noqa: BLE001
         ret[rank] = ("err", traceback.format_exc())
     finally:
@@ -39,12 +41,12 @@ def _entry(rank, world, port, fn, args, ret, backend):
             pass
 
 
-def run_ranks(fn, world=2, args=(), backend="gloo", timeout=240):
+def run_ranks(fn, world=2, args=(), backend="gloo", timeout=240, hard_exit=False):
     ctx = mp.get_context("spawn")
     mgr = ctx.Manager()
     ret = mgr.dict()
     port = _free_port()
-    procs = [ctx.Process(target=_entry, args=(r, world, port, fn, args, ret, backend)) for r in range(world)]
+    procs = [ctx.Process(target=_entry, args=(r, world, port, fn, args, ret, backend, hard_exit)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:

@@ -723,3 +723,111 @@ def test_process_per_stage_pipeline_on_gpus(schedule, recompute):
     assert abs(loss - ref_losses[0]) < 3 * abs(ref_losses[0] - ref_losses[1]) + 3e-2 * max(1.0, abs(ref_losses[0])), (loss, ref_losses)
     for rank, (_, _, worst) in enumerate(res):
         assert worst < 5e-2, (rank, worst)            # beyond 3x the reference's own run-to-run noise by at most 5 %
+
+
+def _stress(rank, world, mode):
+    """>= 1000 collectives of mixed kinds and sizes back to back, on both signal pads, with NO host synchronisation in
+    between; every buffer is poisoned with a rank-specific value right before its collective and checked on the device
+    right after it (a mismatch bumps a device-side counter).  What a lost flag, a stale sequence number, a reused
+    staging buffer or a missing fence would turn into a wrong value or a time-out."""
+    import os
+    os.environ["PTDB200_P2P_MODE"] = mode
+    os.environ["PTDB200_AR_ALGO"] = "nvls" if mode == "nvls" else "auto"
+    os.environ["PTDB200_QUIET"] = "1"
+    os.environ["PTDB200_P2P_TIMEOUT_S"] = "30"
+    import torch
+    from pytorchdistributed_b200.comm.p2p import P2PCollectives
+    dev = torch.device("cuda", rank)
+    be = P2PCollectives(None, dev)
+    sizes = [8, 1000, 65536 + 8, (1 << 20) + 24, 3 * (1 << 20)]
+    bufs = [be.alloc(n, torch.float32, dev) for n in sizes]
+    errors = torch.zeros((), dtype=torch.int64, device=dev)
+    total = float(sum(range(1, world + 1)))
+    count = 0
+    for it in range(260):
+        buf = bufs[it % len(bufs)]
+        base = float(it % 7 + 1)                       # small integers: exact in fp32 and in bf16, in any order
+        kind = it % 5
+        buf.fill_(base * (rank + 1))
+        if kind == 0:
+            be.all_reduce_avg(buf, scale=1.0)
+            exp_val = base * total
+        elif kind == 1:
+            be.all_reduce_avg(buf, scale=1.0, wire=True)
+            exp_val = base * total
+        elif kind == 2:
+            src = it % world
+            be.broadcast(buf, src=src)
+            exp_val = base * (src + 1)
+        elif kind == 3:
+            be.reduce_scatter(buf, scale=1.0)
+            be.all_gather(buf)
+            exp_val = base * total
+            count += 1
+        else:
+            if buf.numel() * 4 <= (4 << 20):
+                be.all_reduce_oneshot(buf, scale=1.0)
+                exp_val = base * total
+            else:
+                be.barrier()
+                exp_val = base * (rank + 1)
+        count += 1
+        exp = torch.full_like(buf, exp_val)               # (expected values are known on the host: no read-back here)
+        errors += (buf != exp).any().to(torch.int64)
+        # a second, different collective on the same buffer right behind it (write-after-read across ranks)
+        summed = base * total if (kind == 4 and buf.numel() * 4 > (4 << 20)) else exp_val * world
+        be.all_reduce_avg(buf, scale=1.0 / total)
+        errors += ((buf - summed / total).abs() > 1e-3 * abs(summed)).any().to(torch.int64)
+        count += 1
+        for _ in range(2):                             # and two tiny ones: latency-bound, flags flip fastest
+            bufs[0].fill_(float(rank + 1))
+            be.all_reduce_avg(bufs[0], scale=1.0)
+            errors += (bufs[0] != total).any().to(torch.int64)
+            count += 1
+    torch.cuda.synchronize()
+    out = {"errors": int(errors.item()), "collectives": count, "mode": be.mode, "stats": dict(be.stats)}
+    be.close()
+    return out
+
+
+@pytest.mark.parametrize("mode", ["nvls", "ipc"])
+def test_p2p_stress_mixed_collectives(mode):
+    _need(2)
+    for res in run_ranks(_stress, 2, (mode,), backend="nccl", timeout=400):
+        assert res["collectives"] >= 1000
+        assert res["errors"] == 0, res
+
+
+def _dead_peer(rank, world):
+    """Rank 1 never joins the collective: rank 0's kernel must give up after PTDB200_P2P_TIMEOUT_S, name the missing
+    peer and fail the stream - not spin on the GPU forever."""
+    import os
+    import time
+    os.environ["PTDB200_P2P_TIMEOUT_S"] = "3"
+    os.environ["PTDB200_QUIET"] = "1"
+    import torch
+    from pytorchdistributed_b200.comm.p2p import P2PCollectives
+    dev = torch.device("cuda", rank)
+    be = P2PCollectives(None, dev)
+    buf = be.alloc(1 << 16, torch.float32, dev)
+    buf.fill_(1.0)
+    be.all_reduce_avg(buf)                             # one healthy round first
+    torch.cuda.synchronize()
+    if rank == 1:
+        time.sleep(12)                                 # alive, but never launches the second collective
+        return {"role": "absent"}
+    t0 = time.time()
+    be.all_reduce_avg(buf)
+    try:
+        torch.cuda.synchronize()
+        return {"role": "waiter", "failed": False, "seconds": time.time() - t0}
+    except Exception as e:  # noqa: BLE001 - the trap surfaces as a CUDA error on the next synchronisation
+        return {"role": "waiter", "failed": True, "seconds": time.time() - t0, "error": str(e)[:200]}
+
+
+def test_dead_peer_is_reported_instead_of_hanging():
+    _need(2)
+    res = run_ranks(_dead_peer, 2, backend="nccl", timeout=120, hard_exit=True)
+    waiter = res[0]
+    assert waiter["failed"], waiter
+    assert 2.0 < waiter["seconds"] < 11.0, waiter      # the 3 s budget, not the 12 s the peer stays away

@@ -529,3 +529,104 @@ def test_optimizer_refreshes_bf16_shadow():
     opt.step()
     assert torch.equal(conv.shadow(), conv.weight.detach().to(torch.bfloat16))
     assert not torch.equal(conv.shadow(), sh0)
+
+
+# Every convolution of ResNet-50 (the 22 bottleneck shapes; the stem has its own tests above) at
+# its real spatial size and a batch that gives several waves of tiles, so the persistent loops, the TMEM double
+# buffering and the CTA-pair kernel (K >= 512 1x1 layers, e.g. 1024 -> 512 at 14 x 14: 24.5 256-row tiles) all run
+# multi-tile, plus shapes whose M = N*OH*OW is NOT a multiple of the 128-row tile (layer4: 32 * 49 = 1568; batch 5).
+RESNET_SHAPES = [
+    # cin, cout, k, stride, h_in, batch
+    (64, 64, 1, 1, 56, 16), (64, 64, 3, 1, 56, 16), (64, 256, 1, 1, 56, 16), (256, 64, 1, 1, 56, 16),
+    (256, 128, 1, 1, 56, 16), (128, 128, 3, 2, 56, 16), (128, 512, 1, 1, 28, 16), (256, 512, 1, 2, 56, 16),
+    (512, 128, 1, 1, 28, 16), (128, 128, 3, 1, 28, 16),
+    (512, 256, 1, 1, 28, 32), (256, 256, 3, 2, 28, 32), (256, 1024, 1, 1, 14, 32), (512, 1024, 1, 2, 28, 32),
+    (1024, 256, 1, 1, 14, 32), (256, 256, 3, 1, 14, 32),
+    (1024, 512, 1, 1, 14, 32), (512, 512, 3, 2, 14, 32), (512, 2048, 1, 1, 7, 32), (1024, 2048, 1, 2, 14, 32),
+    (2048, 512, 1, 1, 7, 32), (512, 512, 3, 1, 7, 32),
+    # odd batches: M not a multiple of 128 for every shape family (1x1, 3x3, strided, pair kernel)
+    (64, 64, 3, 1, 56, 5), (256, 64, 1, 1, 56, 3), (128, 128, 3, 2, 28, 5), (1024, 512, 1, 1, 14, 5),
+    (256, 512, 1, 2, 28, 3),
+]
+
+
+@pytest.mark.parametrize("cin,cout,k,stride,h,n", RESNET_SHAPES)
+def test_conv_all_resnet_shapes_multi_tile(cin, cout, k, stride, h, n):
+    pad = k // 2
+    x, w = _act(n, cin, h, h), _wt(cout, cin, k)
+    oh = (h + 2 * pad - k) // stride + 1
+    dy = _act(n, cout, oh, oh, seed=3)
+    y, stats = K.conv_fprop_raw(x, w, stride, pad, True)
+    ref = F.conv2d(x.float(), w.float(), None, stride, pad)
+    assert _rel(y, ref) < 1e-2
+    assert _rel(stats[1], (ref * ref).sum((0, 2, 3))) < 1e-2
+    dx = K.conv_dgrad_raw(dy, w, x.shape, stride, pad)
+    assert _rel(dx, torch.nn.grad.conv2d_input(x.shape, w.float(), dy.float(), stride, pad)) < 1e-2
+    dw = K.conv_wgrad_raw(x, dy, w.shape, stride, pad)
+    assert _rel(dw, torch.nn.grad.conv2d_weight(x.float(), w.shape, dy.float(), stride, pad)) < 1e-2
+
+
+def test_kernels_stay_inside_their_outputs():
+    """Our own memcheck (compute-sanitizer is refused on this pool, profiles/sanitizer_closed.txt): every output lives
+    in the middle of a poisoned buffer; after the kernel the guard bands on both sides must be untouched.  Shapes are
+    picked so that tiles overhang the tensor (M and N not multiples of the tile, strided row maps, split-K atomics)."""
+    guard = 1 << 16
+
+    def banded(numel, dtype):
+        buf = torch.full((numel + 2 * guard,), 7.0, device=DEV, dtype=dtype)
+        return buf, buf[guard:guard + numel]
+
+    def intact(buf, numel, what):
+        assert bool((buf[:guard] == 7).all()) and bool((buf[guard + numel:] == 7).all()), f"{what} wrote outside its output"
+
+    st = torch.cuda.current_stream().cuda_stream
+    for cin, cout, k, stride, h, n in [(64, 64, 1, 1, 10, 3), (64, 128, 3, 1, 10, 3), (128, 64, 3, 2, 12, 3),
+                                       (512, 256, 1, 1, 7, 5), (256, 512, 1, 2, 14, 3)]:
+        pad = k // 2
+        oh = (h + 2 * pad - k) // stride + 1
+        x, w = _act(n, cin, h, h), _wt(cout, cin, k)
+        dy = _act(n, cout, oh, oh, seed=3)
+        ybuf, y = banded(n * oh * oh * cout, torch.bfloat16)
+        sbuf, stats = banded(2 * cout, torch.float32)
+        stats.zero_()
+        _lib.call("ptd_conv_fprop", x, w, y, stats[:cout], stats[cout:], n, h, h, cin, cout, k, k, stride, pad, st)
+        dxbuf, dx = banded(n * h * h * cin, torch.bfloat16)
+        _lib.call("ptd_conv_dgrad", dy, w, dx, None, n, h, h, cin, cout, k, k, stride, pad, st)
+        dwbuf, dw = banded(cout * k * k * cin, torch.float32)
+        dw.zero_()
+        _lib.call("ptd_conv_wgrad", x, dy, dw, n, h, h, cin, cout, k, k, stride, pad, st)
+        torch.cuda.synchronize()
+        tag = f"conv {cin}->{cout} k{k} s{stride}"
+        intact(ybuf, y.numel(), tag + " fprop")
+        intact(sbuf, stats.numel(), tag + " stats")
+        intact(dxbuf, dx.numel(), tag + " dgrad")
+        intact(dwbuf, dw.numel(), tag + " wgrad")
+        ref = F.conv2d(x.float(), w.float(), None, stride, pad)
+        assert _rel(y.view(n, oh, oh, cout).permute(0, 3, 1, 2), ref) < 1e-2
+    # classifier: N = 1000 is not a multiple of the 128-wide tile, M = 37 not of the 128-row tile
+    a = (torch.randn(37, 2048, device=DEV) * 0.1).to(torch.bfloat16)
+    wl = (torch.randn(1000, 2048, device=DEV) * 0.02).to(torch.bfloat16)
+    obuf, out = banded(37 * 1000, torch.float32)
+    _lib.call("ptd_linear_fwd", a, wl, None, out, 37, 1000, 2048, st)
+    torch.cuda.synchronize()
+    intact(obuf, out.numel(), "linear_fwd")
+    assert _rel(out.view(37, 1000), a.float() @ wl.float().t()) < 1e-2
+    # BatchNorm apply (+ bit mask) and max-pool on a row count that is not a multiple of anything convenient
+    n, c, h = 3, 64, 9
+    yb = _act(n, c, h, h)
+    stats = K.bn_stats_raw(yb)
+    zbuf, z = banded(yb.numel(), torch.bfloat16)
+    mbuf, mask = banded(yb.numel() // 8, torch.uint8)
+    saved = torch.empty(2, c, device=DEV)
+    ones, zeros = torch.ones(c, device=DEV), torch.zeros(c, device=DEV)
+    _lib.call("ptd_bn_apply_mask", yb, None, z, mask, stats[0], stats[1], ones, zeros, zeros.clone(), ones.clone(),
+              saved[0], saved[1], n * h * h, c, 1e-5, 0.1, 1, st)
+    oh = (h + 2 - 3) // 2 + 1
+    pbuf, p = banded(n * oh * oh * c, torch.bfloat16)
+    ibuf, idx = banded(n * oh * oh * c, torch.uint8)
+    _lib.call("ptd_maxpool3x3s2_fwd", yb, p, idx, n, h, h, c, st)
+    torch.cuda.synchronize()
+    intact(zbuf, z.numel(), "bn_apply")
+    intact(mbuf, mask.numel(), "bn mask")
+    intact(pbuf, p.numel(), "maxpool")
+    intact(ibuf, idx.numel(), "maxpool index")
