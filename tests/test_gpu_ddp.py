@@ -69,7 +69,9 @@ def test_direct_bucket_gradients_match_accumulate_grad_path(pg):
     # differ by several per cent on their own (chaotic bf16 gradients), so the bound only has to tell "added"
     # (distance ~ noise) from "overwritten" (distance 0.5) - for a parameter on the direct path and one that is not
     for k in ("layer4.2.conv3.weight", "layer1.0.bn1.weight", "fc.weight"):
-        assert _rel(a[1][k], 2 * a[0][k]) < 0.25, (k, _rel(a[1][k], 2 * a[0][k]))
+        ratio = float(a[1][k].float().norm() / a[0][k].float().norm())
+        assert 1.6 < ratio < 2.5, (k, ratio)              # added: ~2; overwritten: ~1
+        assert _rel(a[1][k], 2 * a[0][k]) < 0.45, (k, _rel(a[1][k], 2 * a[0][k]))
 
 
 def _train(cuda_graph: bool, steps: int = 8):
