@@ -42,12 +42,13 @@ def _grads(direct: bool, seed_model=0, steps=2):
     x = torch.randn(8, 3, 64, 64, generator=g).cuda()
     y = torch.randint(0, 32, (8,), generator=g).cuda()
     out = []
+    for p in model.parameters():
+        p.grad = None
+    # two backward passes over the SAME forward (retain_graph): the second must ADD into the bucket views, not
+    # overwrite them - and with identical saved activations the two passes differ only by atomics noise
+    loss = K.cross_entropy(ddp(x), y)
     for s in range(steps):
-        if s == 0:
-            for p in model.parameters():
-                p.grad = None
-        # step 1 accumulates on top of step 0 (no zero_grad): kernels must ADD into the views, not overwrite them
-        K.cross_entropy(ddp(x), y).backward()
+        loss.backward(retain_graph=s + 1 < steps)
         torch.cuda.synchronize()
         out.append({k: p.grad.detach().clone() for k, p in model.named_parameters()})
     stats = dict(ddp.stats)
@@ -65,13 +66,12 @@ def test_direct_bucket_gradients_match_accumulate_grad_path(pg):
             assert torch.isfinite(a[step][k]).all(), k
             noise = _rel(b[step][k], c[step][k])
             assert _rel(a[step][k], b[step][k]) < 3 * noise + 2e-2, (step, k, noise, _rel(a[step][k], b[step][k]))
-    # accumulation: the second backward on the same batch doubles the gradient.  Two backward passes of this network
-    # differ by several per cent on their own (chaotic bf16 gradients), so the bound only has to tell "added"
-    # (distance ~ noise) from "overwritten" (distance 0.5) - for a parameter on the direct path and one that is not
-    for k in ("layer4.2.conv3.weight", "layer1.0.bn1.weight", "fc.weight"):
+    # accumulation: the second backward over the same graph doubles every gradient - on the direct path (weight-gradient
+    # kernels reducing into the views, BatchNorm sums added by the block's scatter kernel) and on the autograd path
+    for k in ("layer4.2.conv3.weight", "layer4.2.bn3.weight", "layer1.0.bn1.weight", "conv1.weight", "fc.weight"):
         ratio = float(a[1][k].float().norm() / a[0][k].float().norm())
-        assert 1.6 < ratio < 2.5, (k, ratio)              # added: ~2; overwritten: ~1
-        assert _rel(a[1][k], 2 * a[0][k]) < 0.45, (k, _rel(a[1][k], 2 * a[0][k]))
+        assert 1.7 < ratio < 2.3, (k, ratio)              # added: 2; overwritten: 1
+        assert _rel(a[1][k], 2 * a[0][k]) < 0.2, (k, _rel(a[1][k], 2 * a[0][k]))
 
 
 def _train(cuda_graph: bool, steps: int = 8):
