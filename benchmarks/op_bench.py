@@ -68,6 +68,8 @@ def main():
     if os.path.exists(pk):
         peaks.update(json.load(open(pk)))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    from pytorchdistributed_b200.utils import ClockSampler
+    sampler = ClockSampler(0, period_ms=100).start()       # SM clocks / throttle reasons over the whole table
     rows = []
     n = args.batch
     for name, cin, cout, h, k, s, p in SHAPES:
@@ -129,8 +131,10 @@ def main():
                 rows.append({"layer": name, "op": opn, "us": round(us, 1), "gbs": round(gbs, 0),
                              "frac_hbm_of_measured": round(gbs / peaks["hbm_gbs"], 3)})
                 print(f"{name:28s} {opn:10s} {us:9.1f} us  {gbs:6.0f} GB/s ({gbs / peaks['hbm_gbs']:.2f} of measured HBM)", flush=True)
+    clocks = sampler.stop()
+    print(f"clocks over the run: {clocks}")
     if args.out:
-        json.dump(rows, open(args.out, "w"), indent=1)
+        json.dump({"batch": n, "iters": args.iters, "clocks": clocks, "peaks": peaks, "rows": rows}, open(args.out, "w"), indent=1)
 
 
 if __name__ == "__main__":
