@@ -76,6 +76,16 @@ struct alignas(64) FParams {
     float* out_f32;
     const float* bias;
     int ldo;
+    // BatchNorm-backward reduction fused into a data-gradient epilogue (BNR kernels): the tile this kernel writes is the
+    // gradient dz behind a BatchNorm + ReLU whose conv output `bn_y` and ReLU bit mask `bn_mask` have the output's shape;
+    // the epilogue accumulates sum(g) and sum(g * xhat), g = mask ? dz : 0, per channel - what bn_bwd_reduce would
+    // otherwise re-read dz, y and the mask for.
+    const bf16* bn_y;
+    const uint8_t* bn_mask;
+    const float* bn_mean;
+    const float* bn_invstd;
+    float* bn_sum_g;     // += sum g         (dbeta)
+    float* bn_sum_gx;    // += sum g * xhat  (dgamma)
     int dbg;             // experiment switches (PTD_IGEMM_DBG), 0 in production
     int stats_smem;      // BN partial sums: 1 = column sums read back from the bf16 staging tile, 0 = register transpose
     // im2col tap table: k-block kb belongs to table entry kb / cblocks; `wtap` is the filter tap (r*S+s) whose
@@ -297,7 +307,7 @@ __device__ __forceinline__ void f_gather_loop(const FParams& p, Barriers<Cfg::ST
     }
 }
 
-template <int BLOCK_N, int A_MODE, bool B_MN, int EPI, bool PAIR = false>
+template <int BLOCK_N, int A_MODE, bool B_MN, int EPI, bool PAIR = false, bool BNR = false>
 __global__ void __launch_bounds__(FCfg<BLOCK_N, A_MODE, B_MN, EPI, PAIR>::THREADS, 1)
 igemm_f_kernel(const __grid_constant__ FParams p) {
     using Cfg = FCfg<BLOCK_N, A_MODE, B_MN, EPI, PAIR>;
@@ -463,8 +473,17 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
         // The register transpose-reduce (one column per lane: .x = sum, .z = sum of squares) stays for tiles with a
         // long K loop: there the epilogue hides under the MMAs either way, and the denser instruction stream of the
         // shared-memory variant was measured to slow the main loop down by 7-12 % (profiles/README.md).
-        const bool do_stats = (EPI == 0) && p.stat_sum != nullptr;
+        const bool do_stats = (EPI == 0) && !BNR && p.stat_sum != nullptr;      // (a data gradient feeds no BN statistics)
         const bool stats_smem = p.stats_smem != 0;
+        // BNR: lane (pc = lane & 3) owns columns pc*8 .. pc*8+7 of each of the warp's (at most two) 32-column chunks and
+        // accumulates raw sums over every row it sees: S1 = sum g, S2 = sum g*y; xhat enters at the very end
+        // (sum g*xhat = invstd * (S2 - mean * S1)), so the loop needs no per-channel constants.
+        float bs1a[8], bs2a[8], bs1b[8], bs2b[8];
+        if (BNR) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { bs1a[e] = bs2a[e] = bs1b[e] = bs2b[e] = 0.f; }
+        }
+        static_assert(!BNR || (EPI == 0 && Cfg::CHUNKS_PER_WARP <= 2), "BNR: at most two 32-column chunks per epilogue warp");
         int it = 0;
         for (int t = worker; t < num_tiles; t += n_workers, ++it) {
             const int acc = it & 1;
@@ -557,6 +576,9 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                                     ow[e] = pack_bf16x2(f.x + g.x, f.y + g.y);
                                 }
                                 o = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+                                if (BNR)       // the fused BatchNorm reduction below reads the FINAL gradient from the tile
+                                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(stg + row * 64 + ((pc ^ ((row >> 1) & 3)) << 4)),
+                                                 "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
                             }
                             *reinterpret_cast<uint4*>(p.out + off) = o;
                         }
@@ -594,6 +616,64 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                             default: acc3.x += s_lo; acc3.y += s_hi; acc3.z += q_lo; acc3.w += q_hi; break;
                         }
                     }
+                    if (BNR) {
+                        // Same 16-byte pieces as the copy-out: 4 lanes cover one row's 64 bytes.  dz comes from the bf16
+                        // staging tile (the values that were stored; when an addend is fused the copy-out loop above
+                        // wrote the sums back into the tile), y and the mask bits from global memory at the same offset.
+                        __syncwarp();
+                        float t1[8], t2[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) { t1[e] = 0.f; t2[e] = 0.f; }
+#pragma unroll
+                        for (int hh = 0; hh < 2; ++hh) {          // two pieces at a time: half the registers in flight
+                            uint4 dzp[2], yp[2];
+                            uint32_t mb[2];
+#pragma unroll
+                            for (int i = 0; i < 2; ++i) {
+                                const int piece = (int)lane + 32 * (2 * hh + i);
+                                const int row = piece >> 2, pc = piece & 3;
+                                const long long mr = m_base + row;
+                                dzp[i] = make_uint4(0u, 0u, 0u, 0u);
+                                yp[i] = dzp[i];
+                                mb[i] = 0u;
+                                if (mr < p.M) {
+                                    long long orow = mr;
+                                    if (p.map_mul != 0) {
+                                        const int n_ = (int)(mr / p.map_sub_ohw);
+                                        const int rem_ = (int)(mr - (long long)n_ * p.map_sub_ohw);
+                                        const int a_ = rem_ / p.map_sub_ow, b_ = rem_ - a_ * p.map_sub_ow;
+                                        orow = ((long long)n_ * p.map_oH + a_ * p.map_mul + p.map_ph) * p.map_oW + b_ * p.map_mul + p.map_pw;
+                                    }
+                                    const size_t off = (size_t)orow * p.ldo + n0 + col + pc * 8;
+                                    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                                                 : "=r"(dzp[i].x), "=r"(dzp[i].y), "=r"(dzp[i].z), "=r"(dzp[i].w)
+                                                 : "r"(stg + row * 64 + ((pc ^ ((row >> 1) & 3)) << 4)));
+                                    yp[i] = *reinterpret_cast<const uint4*>(p.bn_y + off);
+                                    mb[i] = p.bn_mask[off >> 3];
+                                }
+                            }
+#pragma unroll
+                            for (int i = 0; i < 2; ++i) {
+                                const uint32_t dw_[4] = {dzp[i].x, dzp[i].y, dzp[i].z, dzp[i].w};
+                                const uint32_t yw_[4] = {yp[i].x, yp[i].y, yp[i].z, yp[i].w};
+#pragma unroll
+                                for (int e = 0; e < 4; ++e) {
+                                    const float2 d2 = unpack_bf16x2(dw_[e]), y2 = unpack_bf16x2(yw_[e]);
+                                    const float g0 = ((mb[i] >> (2 * e)) & 1u) ? d2.x : 0.f;
+                                    const float g1 = ((mb[i] >> (2 * e + 1)) & 1u) ? d2.y : 0.f;
+                                    t1[2 * e] += g0; t1[2 * e + 1] += g1;
+                                    t2[2 * e] = fmaf(g0, y2.x, t2[2 * e]); t2[2 * e + 1] = fmaf(g1, y2.y, t2[2 * e + 1]);
+                                }
+                            }
+                        }
+                        if (c == 0) {
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) { bs1a[e] += t1[e]; bs2a[e] += t2[e]; }
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) { bs1b[e] += t1[e]; bs2b[e] += t2[e]; }
+                        }
+                    }
                     __syncwarp();
                 } else {
                     if (row_ok) {
@@ -611,6 +691,26 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
             else mbar_arrive(&bars->tmem_empty[acc]);
         }
         if (EPI == 0 && p.tma_store != 0 && lane == 0) bulk_wait_group<0>();      // this warp's stores are complete
+        if (BNR) {
+            // lanes with equal (lane & 3) hold partial sums of the same 8 columns: fold them, lanes 0..3 publish
+#pragma unroll
+            for (int c = 0; c < Cfg::CHUNKS_PER_WARP; ++c) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    float s1 = c == 0 ? bs1a[e] : bs1b[e], s2 = c == 0 ? bs2a[e] : bs2b[e];
+#pragma unroll
+                    for (int o = 4; o <= 16; o <<= 1) {
+                        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+                        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+                    }
+                    if (lane < 4) {
+                        const int n = n0 + half * Cfg::COLS_PER_GROUP + c * 32 + (int)lane * 8 + e;
+                        atomicAdd(p.bn_sum_g + n, s1);
+                        atomicAdd(p.bn_sum_gx + n, p.bn_invstd[n] * (s2 - p.bn_mean[n] * s1));
+                    }
+                }
+            }
+        }
         if (do_stats) {
             const float4 fa[4] = {acc0, acc1, acc2, acc3};
 #pragma unroll
@@ -860,10 +960,10 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_ke
 // ------------------------------------------------------------------------------------------
 // Host launchers
 // ------------------------------------------------------------------------------------------
-template <int BLOCK_N, int A_MODE, bool B_MN, int EPI>
+template <int BLOCK_N, int A_MODE, bool B_MN, int EPI, bool BNR = false>
 int launch_f(FParams& p, cudaStream_t stream) {
     using Cfg = FCfg<BLOCK_N, A_MODE, B_MN, EPI>;
-    auto kern = igemm_f_kernel<BLOCK_N, A_MODE, B_MN, EPI>;
+    auto kern = igemm_f_kernel<BLOCK_N, A_MODE, B_MN, EPI, false, BNR>;
     static bool configured[64] = {false};
     int dev = 0;
     PTD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -890,10 +990,10 @@ int launch_f(FParams& p, cudaStream_t stream) {
 }
 
 // CTA-pair launch (cluster of 2, tcgen05 cta_group::2): 256 x BLOCK_N tiles, tiled 1x1 path.
-template <int BLOCK_N, bool B_MN>
+template <int BLOCK_N, bool B_MN, bool BNR = false>
 int launch_f_pair(FParams& p, cudaStream_t stream) {
     using Cfg = FCfg<BLOCK_N, AM_TILED, B_MN, 0, true>;
-    auto kern = igemm_f_kernel<BLOCK_N, AM_TILED, B_MN, 0, true>;
+    auto kern = igemm_f_kernel<BLOCK_N, AM_TILED, B_MN, 0, true, BNR>;
     static bool configured[64] = {false};
     int dev = 0;
     PTD_CUDA_CHECK(cudaGetDevice(&dev));
@@ -940,12 +1040,31 @@ bool use_pair(const FParams& p, int block_n) {
 }
 template <bool B_MN>
 int dispatch_f_pair(FParams& p, int block_n, cudaStream_t stream) {
+    if constexpr (B_MN) {                 // data gradients may carry the fused BatchNorm-backward reduction
+        if (p.bn_y != nullptr) {
+            if (block_n == 256) return launch_f_pair<256, B_MN, true>(p, stream);
+            return launch_f_pair<128, B_MN, true>(p, stream);
+        }
+    }
     if (block_n == 256) return launch_f_pair<256, B_MN>(p, stream);
     return launch_f_pair<128, B_MN>(p, stream);
 }
 
 template <int A_MODE, bool B_MN, int EPI>
 int dispatch_f(FParams& p, int block_n, cudaStream_t stream) {
+    if constexpr (B_MN && EPI == 0 && A_MODE != AM_GATHER) {
+        if (p.bn_y != nullptr) {
+            switch (block_n) {
+                case 64: return launch_f<64, A_MODE, B_MN, EPI, true>(p, stream);
+                case 128: return launch_f<128, A_MODE, B_MN, EPI, true>(p, stream);
+                case 256: return launch_f<256, A_MODE, B_MN, EPI, true>(p, stream);
+            }
+        }
+    }
+    if (p.bn_y != nullptr) {
+        ptd_set_error("igemm_f: this kernel variant cannot carry the fused BatchNorm reduction");
+        return PTD_ERR_UNSUPPORTED;
+    }
     switch (block_n) {
         case 64: return launch_f<64, A_MODE, B_MN, EPI>(p, stream);
         case 128: return launch_f<128, A_MODE, B_MN, EPI>(p, stream);
@@ -1101,22 +1220,77 @@ extern "C" int ptd_conv_fprop(const void* x, const void* w, void* y, float* stat
     return dispatch_f<AM_GATHER, false, 0>(p, bn, stream);
 }
 
+namespace {
+// Fused BatchNorm-backward reduction riding on a data gradient (see FParams::bn_*): all six pointers or none.
+struct BnReduce {
+    const void* y;
+    const void* mask;
+    const float* mean;
+    const float* invstd;
+    float* sum_g;
+    float* sum_gx;
+};
+void set_bn(FParams& p, const BnReduce* bn) {
+    if (bn == nullptr || bn->y == nullptr) return;
+    p.bn_y = (const bf16*)bn->y; p.bn_mask = (const uint8_t*)bn->mask; p.bn_mean = bn->mean; p.bn_invstd = bn->invstd;
+    p.bn_sum_g = bn->sum_g; p.bn_sum_gx = bn->sum_gx;
+}
+int conv_dgrad_impl(const void* dy, const void* w, void* dx, const void* addend, const void* addend_mask, const BnReduce* bnr,
+                    int N, int H, int W, int Cin, int Cout, int R, int S, int stride, int pad, void* stream_);
+}  // namespace
+
 extern "C" int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const void* addend, int N, int H, int W,
                               int Cin, int Cout, int R, int S, int stride, int pad, void* stream_) {
+    return conv_dgrad_impl(dy, w, dx, addend, nullptr, nullptr, N, H, W, Cin, Cout, R, S, stride, pad, stream_);
+}
+
+// Data gradient with everything the residual block's backward fuses into it: an addend (optionally gated by a ReLU bit
+// mask: the identity-branch gradient), and the reduction pass of the BatchNorm backward that CONSUMES this gradient -
+// dx is the gradient behind BatchNorm + ReLU of a layer whose conv output is bn_y (dx's shape) and whose ReLU bits are
+// bn_mask; sum_g[c] += sum(g), sum_gx[c] += sum(g * xhat) with g = mask ? dx : 0, exactly what ptd_bn_bwd_reduce
+// (relu = 2) computes from a second read of dx, y and the mask.  Returns PTD_ERR_UNSUPPORTED before launching anything
+// when the shape takes the gather fallback (the caller then runs the separate reduce kernel).
+extern "C" int ptd_conv_dgrad_fused(const void* dy, const void* w, void* dx, const void* addend, const void* addend_mask,
+                                    const void* bn_y, const void* bn_mask, const float* bn_mean, const float* bn_invstd,
+                                    float* sum_g, float* sum_gx, int N, int H, int W, int Cin, int Cout, int R, int S,
+                                    int stride, int pad, void* stream_) {
+    BnReduce bn = {bn_y, bn_mask, bn_mean, bn_invstd, sum_g, sum_gx};
+    if (bn_y != nullptr)
+        PTD_REQUIRE(bn_mask && bn_mean && bn_invstd && sum_g && sum_gx, "conv_dgrad_fused: the BatchNorm reduction needs all six pointers");
+    return conv_dgrad_impl(dy, w, dx, addend, addend_mask, bn_y ? &bn : nullptr, N, H, W, Cin, Cout, R, S, stride, pad, stream_);
+}
+
+namespace {
+int conv_dgrad_impl(const void* dy, const void* w, void* dx, const void* addend, const void* addend_mask, const BnReduce* bnr,
+                    int N, int H, int W, int Cin, int Cout, int R, int S, int stride, int pad, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     const int OH = (H + 2 * pad - R) / stride + 1, OW = (W + 2 * pad - S) / stride + 1;
     PTD_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "conv_dgrad: Cin (%d) and Cout (%d) must be multiples of 64", Cin, Cout);
     FParams p;
     memset(&p, 0, sizeof(p));
     p.M = N * H * W; p.N = Cin; p.num_kb = R * S * Cout / 64;
-    p.out = (bf16*)dx; p.ldo = Cin; p.addend = (const bf16*)addend;
+    p.out = (bf16*)dx; p.ldo = Cin; p.addend = (const bf16*)addend; p.addend_mask = (const uint8_t*)addend_mask;
     p.b_tap_cols = Cin; p.b_cblocks = Cout / 64;
+    PTD_REQUIRE(addend_mask == nullptr || addend != nullptr, "conv_dgrad: an addend mask needs an addend");
+    const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
+    const bool tma_path = !force_gather() && R == S && R * S <= 9 &&
+                          (plain || stride == 1 ||
+                           (stride == 2 && R == 3 && (H % 2 == 0) && (W % 2 == 0) &&
+                            (H + 2 * pad - R) / 2 + 1 == H / 2 && (W + 2 * pad - S) / 2 + 1 == W / 2));
+    if (bnr != nullptr && !tma_path) {
+        ptd_set_error("conv_dgrad_fused: this shape takes the gather fallback, which cannot carry the BatchNorm reduction");
+        return PTD_ERR_UNSUPPORTED;
+    }
+    if (addend_mask != nullptr && !plain) {
+        ptd_set_error("conv_dgrad_fused: a gated addend is only supported on the 1x1 stride-1 path");
+        return PTD_ERR_UNSUPPORTED;
+    }
+    set_bn(p, bnr);
     const int bn = pick_block_n(Cin);
     // forward weight tensor viewed as [Cout rows][R*S*Cin cols]; a 64x64 box at (tap*Cin + n, cout) is the
     // MN-major B sub-tile of that tap.
     int rc = ptd_make_tmap_2d_bf16(&p.tmB, w, (uint64_t)R * S * Cin, Cout, (uint64_t)R * S * Cin * 2, 64, 64);
     if (rc) return rc;
-    const bool plain = (R == 1 && S == 1 && stride == 1 && pad == 0);
     if (plain) {
         rc = ptd_make_tmap_2d_bf16(&p.tmA, dy, Cout, p.M, (uint64_t)Cout * 2, 64, BLOCK_M);
         if (rc) return rc;
@@ -1188,25 +1362,15 @@ extern "C" int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const voi
     }
     return dispatch_f<AM_GATHER, true, 0>(p, bn, stream);
 }
+}  // namespace
 
 // 1x1 stride-1 data gradient with a gated addend: dx = dy * W + (mask bit ? addend : 0).  `mask` is the ReLU bit
 // tensor of ptd_bn_apply_mask over dx's shape: the residual block's identity-branch gradient is the block-output
 // gradient behind the final ReLU, so it can be taken from dz directly instead of from a materialised copy.
 extern "C" int ptd_conv_dgrad_masked_addend(const void* dy, const void* w, void* dx, const void* addend,
                                             const void* mask, int N, int H, int W, int Cin, int Cout, void* stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    PTD_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "conv_dgrad: Cin (%d) and Cout (%d) must be multiples of 64", Cin, Cout);
     PTD_REQUIRE(addend != nullptr && mask != nullptr, "conv_dgrad_masked_addend: addend and mask are required");
-    FParams p;
-    memset(&p, 0, sizeof(p));
-    p.M = N * H * W; p.N = Cin; p.num_kb = Cout / 64;
-    p.out = (bf16*)dx; p.ldo = Cin; p.addend = (const bf16*)addend; p.addend_mask = (const uint8_t*)mask;
-    p.b_tap_cols = Cin; p.b_cblocks = Cout / 64;
-    int rc = ptd_make_tmap_2d_bf16(&p.tmB, w, (uint64_t)Cin, Cout, (uint64_t)Cin * 2, 64, 64);
-    if (rc) return rc;
-    rc = ptd_make_tmap_2d_bf16(&p.tmA, dy, Cout, p.M, (uint64_t)Cout * 2, 64, BLOCK_M);
-    if (rc) return rc;
-    return dispatch_f<AM_TILED, true, 0>(p, pick_block_n(Cin), stream);
+    return conv_dgrad_impl(dy, w, dx, addend, mask, nullptr, N, H, W, Cin, Cout, 1, 1, 1, 0, stream_);
 }
 
 // dx += conv_transpose(dy, w)  (in place).  For the 1x1 stride-2 shortcut convolution this touches only the

@@ -34,6 +34,14 @@ int ptd_conv_dgrad(const void* dy, const void* w, void* dx, const void* addend, 
 int ptd_conv_dgrad_masked_addend(const void* dy, const void* w, void* dx, const void* addend, const void* mask, int N,
                                  int H, int W, int Cin, int Cout, void* stream);
 /* dx += conv_transpose(dy, w), in place (the 1x1 stride-2 shortcut only touches the strided quarter of dx). */
+/* Data gradient with an optional (mask-gated) addend AND the reduction pass of the BatchNorm backward that consumes dx
+ * fused into its epilogue: sum_g[c] += sum(g), sum_gx[c] += sum(g * xhat), g = bn_mask ? dx : 0, xhat from bn_y / mean /
+ * invstd (all NULL = plain data gradient).  Saves ptd_bn_bwd_reduce's second read of dx, y and the mask (torchvision
+ * Bottleneck backward, notebook 03 cell 5).  PTD_ERR_UNSUPPORTED (-3), before any launch, for shapes on the gather fallback. */
+int ptd_conv_dgrad_fused(const void* dy, const void* w, void* dx, const void* addend, const void* addend_mask,
+                         const void* bn_y, const void* bn_mask, const float* bn_mean, const float* bn_invstd,
+                         float* sum_g, float* sum_gx, int N, int H, int W, int Cin, int Cout, int R, int S, int stride,
+                         int pad, void* stream);
 int ptd_conv_dgrad_accum(const void* dy, const void* w, void* dx, int N, int H, int W, int Cin, int Cout, int R, int S,
                          int stride, int pad, void* stream);
 /* dw[Cout,R,S,Cin] (fp32) += dy^T * im2col(x).  The caller zeroes dw (or keeps an accumulated value). */

@@ -24,6 +24,7 @@ _SIGS: dict[str, list] = {
     "ptd_conv_fprop": [P, P, P, P, P, I, I, I, I, I, I, I, I, I, P],
     "ptd_conv_dgrad": [P, P, P, P, I, I, I, I, I, I, I, I, I, P],
     "ptd_conv_dgrad_accum": [P, P, P, I, I, I, I, I, I, I, I, I, P],
+    "ptd_conv_dgrad_fused": [P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, P],
     "ptd_conv_wgrad": [P, P, P, I, I, I, I, I, I, I, I, I, P],
     "ptd_bottleneck_fwd": [P, P],
     "ptd_bottleneck_bwd": [P, P],

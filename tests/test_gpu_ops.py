@@ -630,3 +630,49 @@ def test_kernels_stay_inside_their_outputs():
     intact(mbuf, mask.numel(), "bn mask")
     intact(pbuf, p.numel(), "maxpool")
     intact(ibuf, idx.numel(), "maxpool index")
+
+
+@pytest.mark.parametrize("cin,cout,k,stride,h,n,gated", [
+    (64, 256, 1, 1, 14, 5, False),      # 1x1, 64-wide tiles, M = 980 (not a multiple of 128)
+    (256, 1024, 1, 1, 14, 6, False),    # 1x1, K = 1024: CTA-pair kernel, two chunks per epilogue warp
+    (128, 128, 3, 1, 14, 5, False),     # 3x3 stride 1: im2col + TMA store
+    (128, 128, 3, 2, 28, 3, False),     # 3x3 stride 2: four parity launches, rows remapped
+    (256, 64, 1, 1, 14, 5, True),       # 1x1 with the mask-gated addend (identity-branch gradient)
+    (512, 128, 1, 1, 8, 3, True),
+])
+def test_dgrad_with_fused_bn_backward_reduction(cin, cout, k, stride, h, n, gated):
+    """ptd_conv_dgrad_fused = the data gradient + ptd_bn_bwd_reduce (bit-mask mode) over its output, in one kernel."""
+    pad = k // 2
+    oh = (h + 2 * pad - k) // stride + 1
+    w = _wt(cout, cin, k)
+    dy = _act(n, cout, oh, oh, seed=3)
+    y = _act(n, cin, h, h, scale=2.0, seed=4)                      # conv output of the layer whose BN consumes dx
+    g = torch.Generator().manual_seed(7)
+    m = n * h * h
+    mask = torch.randint(0, 256, (m, cin // 8), generator=g, dtype=torch.uint8).to(DEV)
+    mean = (torch.randn(cin, generator=g) * 0.3).to(DEV)
+    invstd = (torch.rand(cin, generator=g) + 0.5).to(DEV)
+    addend = _act(n, cin, h, h, seed=5) if gated else None
+    amask = torch.randint(0, 256, (m, cin // 8), generator=g, dtype=torch.uint8).to(DEV) if gated else None
+    st = torch.cuda.current_stream().cuda_stream
+    dx = torch.empty_like(y)
+    sums = torch.zeros(2, cin, device=DEV)
+    _lib.call("ptd_conv_dgrad_fused", dy, w, dx, addend, amask, y, mask, mean, invstd, sums[0], sums[1],
+              n, h, h, cin, cout, k, k, stride, pad, st)
+    # the unfused statement: plain data gradient (+ gated addend), then the separate reduce kernel over it
+    ref_dx = torch.empty_like(y)
+    if gated:
+        _lib.call("ptd_conv_dgrad_masked_addend", dy, w, ref_dx, addend, amask, n, h, h, cin, cout, st)
+    else:
+        _lib.call("ptd_conv_dgrad", dy, w, ref_dx, None, n, h, h, cin, cout, k, k, stride, pad, st)
+    ref_sums = torch.zeros(2, cin, device=DEV)
+    _lib.call("ptd_bn_bwd_reduce", ref_dx, mask, y, mean, invstd, ref_sums[0], ref_sums[1], m, cin, 2, st)
+    torch.cuda.synchronize()
+    assert torch.equal(dx, ref_dx)                                 # the gradient itself is untouched by the fusion
+    # and against plain fp32 PyTorch
+    bits = ((mask.view(m, cin // 8, 1) >> torch.arange(8, device=DEV, dtype=torch.uint8)) & 1).reshape(m, cin).float()
+    gflat = dx.permute(0, 2, 3, 1).reshape(m, cin).float() * bits
+    xhat = (y.permute(0, 2, 3, 1).reshape(m, cin).float() - mean) * invstd
+    for got, ref, oracle in ((sums[0], ref_sums[0], gflat.sum(0)), (sums[1], ref_sums[1], (gflat * xhat).sum(0))):
+        assert _rel(got, ref) < 2e-3, _rel(got, ref)
+        assert _rel(got, oracle) < 2e-3, _rel(got, oracle)
