@@ -60,6 +60,17 @@ bool dual_bn_enabled() {
     if (v < 0) { const char* e = getenv("PTDB200_DUAL_BN"); v = e ? atoi(e) : 1; }
     return v == 1;
 }
+// BN-backward reduce pass of conv1's / conv2's BatchNorm fused into the data-gradient kernel that produces their dz
+// (ptd_conv_dgrad_fused).  OFF by default: measured per layer at batch 256 (profiles/fused_bn_reduce_experiment.txt) the
+// fused kernel LOSES 3-144 us against data gradient + separate reduce kernel on every 1x1 and strided layer - those
+// data gradients are epilogue-bound (tiny K), and the reduction doubles the epilogue's load/ALU work, while the separate
+// reduce kernel already streams at ~4 TB/s; only the stride-1 3x3 layers gain 5-20 us.  Whole step: 19.30 ms fused vs
+// 18.95 ms unfused.  PTDB200_FUSE_BN_REDUCE=1 switches it on (A/B testing).
+bool fuse_bn_reduce_enabled() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("PTDB200_FUSE_BN_REDUCE"); v = e ? atoi(e) : 0; }
+    return v == 1;
+}
 bool overlap_enabled() {
     static int v = -1;
     if (v < 0) { const char* e = getenv("PTDB200_WGRAD_OVERLAP"); v = e ? atoi(e) : 1; }
@@ -151,6 +162,32 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
                               gout_, g[i].m_out, g[i].cout, mode, stream);                                             \
         if (rc) return rc;                                                                                             \
     } while (0)
+    /* BatchNorm backward of unit i with its reduce pass already done by the kernel that produced dz_ (sums are final) */
+#define BN_APPLY(i, dz_)                                                                                               \
+    do {                                                                                                               \
+        float* sm = d->sums + off[i];                                                                                  \
+        const float* sv = d->saved + off[i];                                                                           \
+        rc = ptd_bn_bwd_apply(dz_, d->mask[i], d->y[i], sv, sv + g[i].cout, d->gamma[i], sm, sm + g[i].cout, d->dy[i], \
+                              nullptr, g[i].m_out, g[i].cout, 2, stream);                                              \
+        if (rc) return rc;                                                                                             \
+    } while (0)
+    /* data gradient of unit i into dx_ = the gradient behind unit j's BatchNorm + ReLU, with unit j's reduce pass fused
+       into its epilogue; falls back to the separate kernels where the fused variant does not apply */
+#define DGRAD_BN(i, dx_, j)                                                                                            \
+    do {                                                                                                               \
+        bool fused = false;                                                                                            \
+        if (fuse_bn && d->mask[j] != nullptr) {                                                                        \
+            float* sm = d->sums + off[j];                                                                              \
+            const float* sv = d->saved + off[j];                                                                       \
+            rc = ptd_conv_dgrad_fused(d->dy[i], d->w[i], dx_, nullptr, nullptr, d->y[j], d->mask[j], sv, sv + g[j].cout, \
+                                      sm, sm + g[j].cout, d->N, g[i].h_in, g[i].w_in, g[i].cin, g[i].cout, g[i].k,      \
+                                      g[i].k, g[i].stride, g[i].pad, stream);                                          \
+            if (rc == PTD_OK) fused = true;                                                                            \
+            else if (rc != PTD_ERR_UNSUPPORTED) return rc;                                                             \
+        }                                                                                                              \
+        if (!fused) DGRAD(i, dx_, nullptr);                                                                            \
+        fused_unit[j] = fused;                                                                                         \
+    } while (0)
 #define DGRAD(i, dx_, addend_)                                                                                         \
     do {                                                                                                               \
         rc = ptd_conv_dgrad(d->dy[i], d->w[i], dx_, addend_, d->N, g[i].h_in, g[i].w_in, g[i].cin, g[i].cout, g[i].k,   \
@@ -189,12 +226,16 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
     } else {
         BN_BWD(2, d->dz, 1, gate ? nullptr : d->g_id);
     }
-    DGRAD(2, d->dz2, nullptr);
+    const bool fuse_bn = fuse_bn_reduce_enabled();
+    bool fused_unit[4] = {false, false, false, false};
+    DGRAD_BN(2, d->dz2, 1);                 // dz2 = gradient behind bn2 + ReLU: its reduce pass rides on this kernel
     WGRAD(2, d->z[1]);
-    BN_BWD(1, d->dz2, 1, nullptr);
-    DGRAD(1, d->dz1, nullptr);
+    if (fused_unit[1]) BN_APPLY(1, d->dz2);
+    else BN_BWD(1, d->dz2, 1, nullptr);
+    DGRAD_BN(1, d->dz1, 0);                 // likewise bn1's on the 3x3 data gradient
     WGRAD(1, d->z[0]);
-    BN_BWD(0, d->dz1, 1, nullptr);
+    if (fused_unit[0]) BN_APPLY(0, d->dz1);
+    else BN_BWD(0, d->dz1, 1, nullptr);
     if (d->has_ds) {
         if (dual) {
             /* the shortcut BN's backward ran together with the last BN's */
@@ -247,6 +288,8 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
         PTD_CUDA_CHECK(cudaStreamWaitEvent(st, e, 0));
     }
 #undef BN_BWD
+#undef BN_APPLY
+#undef DGRAD_BN
 #undef DGRAD
 #undef WGRAD
     return PTD_OK;
