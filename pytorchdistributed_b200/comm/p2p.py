@@ -209,7 +209,8 @@ class SymmetricBuffer(_Region):
         assert need <= self.nbytes
         return self.bytes_tensor[:need].view(dtype)
 
-    def close(self) -> None:
+    def close(self, barrier: bool = True) -> None:
+        """``barrier=False``: the caller has already synchronised the group (one barrier for many regions)."""
         if self._closed:
             return
         self._closed = True
@@ -218,7 +219,7 @@ class SymmetricBuffer(_Region):
             with torch.cuda.device(self.device):
                 for p in self._opened:
                     _lib.call("ptd_p2p_ipc_close", p)
-                if dist.is_initialized():
+                if barrier and dist.is_initialized():
                     dist.barrier(group=self.group)      # nobody frees while a peer still has it mapped
                 _lib.call("ptd_p2p_free", self.local_ptr)
         except Exception:  # noqa: BLE001 - teardown must not raise
@@ -304,13 +305,13 @@ class VmmBlock(_Region):
         if not step(ok):
             _lib.call_ret("ptd_vmm_mc_drop", bid)
 
-    def close(self) -> None:
+    def close(self, barrier: bool = True) -> None:
         if self._closed:
             return
         self._closed = True
         try:
             torch.cuda.synchronize(self.device)
-            if dist.is_initialized():
+            if barrier and dist.is_initialized():
                 dist.barrier(group=self.group)          # no peer kernel still touches this block
             with torch.cuda.device(self.device):
                 _lib.call_ret("ptd_vmm_destroy", self.block_id)
@@ -603,8 +604,15 @@ class P2PCollectives:
         _lib.call("ptd_p2p_barrier", self._pad(1)[0], self.rank, self.world, self._stream())
 
     def close(self) -> None:
+        """Collective: every rank calls it.  ONE group barrier, then every region is released locally."""
+        try:
+            torch.cuda.synchronize(self.device)
+            if dist.is_initialized() and self._regions:
+                dist.barrier(group=self.group)
+        except Exception:  # noqa: BLE001 - teardown must not raise
+            pass
         for reg in self._regions:
-            reg.close()
+            reg.close(barrier=False)
         self._regions.clear()
         self._bases.clear()
         self._ptr_cache.clear()
@@ -616,6 +624,18 @@ class P2PCollectives:
 
 
 def shutdown() -> None:
-    """Release every live symmetric allocation (called from ``destroy_process_group``)."""
-    for reg in list(_LIVE):
-        reg.close()
+    """Release every live symmetric allocation (called from ``destroy_process_group``).
+
+    Exactly ONE barrier, whatever this rank still holds: which regions are alive here depends on when Python's cyclic
+    garbage collector ran, and that differs between ranks - a barrier per region would leave the rank that holds more of
+    them waiting for a peer that has already left."""
+    regs = [r for r in list(_LIVE) if not getattr(r, "_closed", True)]
+    try:
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+        if dist.is_initialized() and dist.get_world_size() > 1 and dist.get_backend() != "gloo":
+            dist.barrier()
+    except Exception:  # noqa: BLE001 - teardown must not raise
+        pass
+    for reg in regs:
+        reg.close(barrier=False)
