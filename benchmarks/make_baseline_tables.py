@@ -32,14 +32,30 @@ def clk(c):
     return f"{'REJECTED: ' if bad else ''}{c.get('sm_mhz')} MHz of {c.get('sm_max_mhz')}, {note}"
 
 
+def comm_label(d):
+    """'p2p:nvls:{'nvls': 20, 'two_shot': 0, ...}' -> which all-reduce kernel actually ran."""
+    g = d.get("grad_comm", "?")
+    if g.startswith("p2p:") and ":{" in g:
+        import ast
+        stats = ast.literal_eval(g[g.index(":{") + 1:])
+        ran = [k for k in ("nvls", "two_shot", "wire_bf16") if stats.get(k)]
+        names = {"nvls": "switch reduction (multimem)", "two_shot": "two-shot peer-to-peer", "wire_bf16": "bf16 wire"}
+        g = "ours: " + " + ".join(names[k] for k in ran) if ran else "ours (p2p)"
+    elif g == "p2p":
+        g = "ours (p2p)"
+    elif g == "torch":
+        g = "none (one rank)"
+    return g + (" + SGD fused into the all-reduce" if d.get("fused_sgd_in_allreduce") else "")
+
+
 def bench_table(out):
     out.append("### Config 2 - ResNet-50 DDP, bf16, 3x224x224, 256 images per GPU, SGD (builder runs of `bench.py`; the "
                "driver's BENCH / SCALE records are the authoritative ones)\n")
     out.append("| GPUs | images/s (device-timed, max over ranks) | ms/step | e2e images/s | e2e ms/step | gradient path | clocks | file |")
     out.append("|---|---|---|---|---|---|---|---|")
     base = None
-    for n, f in [(1, "bench_n1_r2.json"), (2, "bench_n2_r2.json"), (4, "bench_n4_r2.json"), (8, "bench_n8_r2_default.json"),
-                 (8, "bench_n8_r2_default2.json")]:
+    for n, f in [(1, "bench_n1_r2.json"), (2, "bench_n2_r2_final.json"), (4, "bench_n4_r2_final.json"),
+                 (4, "bench_n4_r2_fused_sgd.json"), (8, "bench_n8_r2_default.json"), (8, "bench_n8_r2_default2.json")]:
         d = load(f)
         if d is None:
             continue
@@ -47,7 +63,7 @@ def bench_table(out):
             base = d["value"]
         eff = f" ({d['value'] / (n * base):.3f} of {n} x N=1)" if base and n > 1 else ""
         out.append(f"| {n} | {d['value']:.0f}{eff} | {d['ms_per_step']} | {d['e2e']['value']:.0f} | {d['e2e']['ms_per_step']} | "
-                   f"{d.get('grad_comm', '?').split(':{')[0]} | {clk(d.get('clocks'))} | `profiles/{f}` |")
+                   f"{comm_label(d)} | {clk(d.get('clocks'))} | `profiles/{f}` |")
     out.append("")
     out.append("Control runs at 8 GPUs (same box, same call; what the 1 -> 8 growth of the step is made of):\n")
     out.append("| run | ms/step | e2e ms/step | clocks | file |")
@@ -96,7 +112,7 @@ def dp_table(out):
     rows = [(1, "ours (wrapper on one GPU: eager, no graph)", "dp_bench_ours_n1.json"),
             (2, "ours, graph replicas", "dp_bench_ours_n2.json"), (2, "ours, eager thread pool", "dp_bench_ours_eager_n2.json"),
             (2, "reference: nn.DataParallel, bf16 autocast", "dp_bench_reference_n2.json"),
-            (8, "ours, graph replicas", "dp_bench_ours_n8.json"),
+            (4, "ours, graph replicas", "dp_bench_ours_n4.json"), (8, "ours, graph replicas", "dp_bench_ours_n8.json"),
             (8, "reference: nn.DataParallel, bf16 autocast", "dp_bench_reference_n8.json")]
     for n, label, f in rows:
         d = load(f)
