@@ -47,3 +47,45 @@ def test_reducer_tracks_buckets():
     assert _lib.call_ret("ptd_reducer_all_done", rid) == 0 and mark(5) == 2
     assert _lib.call_ret("ptd_reducer_destroy", rid) == 0
     assert _lib.call_ret("ptd_reducer_mark_ready", rid, 0) == -3
+
+
+def test_native_reducer_rejects_bad_bucket_recipes():
+    """ptd_reducer_bind_bucket validates its recipe before it touches CUDA (this box has no GPU)."""
+    import ctypes
+    from pytorchdistributed_b200 import _lib
+    from pytorchdistributed_b200.parallel import ddp  # noqa: F401  (registers the reducer entry points)
+    arr = (ctypes.c_int * 3)(0, 0, 1)
+    rid = _lib.call_ret("ptd_reducer_create", ctypes.cast(arr, ctypes.c_void_p), 3, 2)
+    assert rid > 0
+    c = _lib.BucketComm()
+    c.algo, c.rank, c.world = 7, 0, 2                      # unknown algorithm
+    assert _lib.call_ret("ptd_reducer_bind_bucket", rid, 0, ctypes.addressof(c)) != 0
+    c.algo, c.world = 2, 1                                 # a one-rank group has nothing to reduce
+    assert _lib.call_ret("ptd_reducer_bind_bucket", rid, 0, ctypes.addressof(c)) != 0
+    c.algo, c.world, c.fuse_sgd = 3, 2, 1                  # the fused SGD step needs fp32 on the wire
+    assert _lib.call_ret("ptd_reducer_bind_bucket", rid, 0, ctypes.addressof(c)) != 0
+    assert b"fp32" in _lib.require().ptd_last_error()
+    # an unbound reducer still counts: marking through the launching entry point behaves like the plain one
+    assert _lib.call_ret("ptd_reducer_mark_ready_launch", rid, 2, None, None) == 1      # bucket 1 complete (one parameter)
+    assert _lib.call_ret("ptd_reducer_mark_ready_launch", rid, 0, None, None) == -1
+    assert _lib.call_ret("ptd_reducer_mark_ready_launch", rid, 0, None, None) == -2     # marked twice
+    assert _lib.call_ret("ptd_reducer_mark_ready_launch", rid, 1, None, None) == 0
+    assert _lib.call_ret("ptd_reducer_finalize", rid, None) == 1
+    _lib.call_ret("ptd_reducer_destroy", rid)
+
+
+def test_baseline_tables_match_the_committed_profiles():
+    """BASELINE.md section B is generated from profiles/*.json: the text between the markers must be what the generator
+    prints today (nobody typed a number by hand, and nobody forgot to regenerate)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "benchmarks", "make_baseline_tables.py")],
+                         capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    text = open(os.path.join(root, "BASELINE.md")).read()
+    begin, end = "<!-- BEGIN GENERATED TABLES -->", "<!-- END GENERATED TABLES -->"
+    inside = text[text.index(begin) + len(begin):text.index(end)]
+    assert inside.strip() == out.stdout.strip()
+    assert "REJECTED" not in inside                          # no quoted row ran under a thermal / hardware slowdown
