@@ -116,8 +116,11 @@ class DistributedDataParallel(nn.Module):
         super().__init__()
         if not dist.is_initialized():
             raise RuntimeError("DistributedDataParallel needs an initialised process group (comm.ddp_setup)")
-        if find_unused_parameters:
-            raise NotImplementedError("find_unused_parameters=True is not supported")
+        # find_unused_parameters: parameters that received no gradient in a backward are reported ready at its end
+        # (their bucket views hold zeros), so their buckets are still averaged - every rank must leave the SAME
+        # parameters unused (a static sub-graph), the rank-divergent case of torch's bitmap exchange is not covered.
+        self.find_unused_parameters = bool(find_unused_parameters)
+        self._comm_hook = None
         self.module = module
         self.process_group = process_group
         self.world_size = dist.get_world_size(process_group)
@@ -292,7 +295,7 @@ class DistributedDataParallel(nn.Module):
         native call that also issues the finished bucket's all-reduce (events, stream switch, kernel)."""
         self._native = False
         self._bucket_comms = []
-        if (self.world_size == 1 or self._skip_allreduce or self._comm_stream is None
+        if (self.world_size == 1 or self._skip_allreduce or self._comm_stream is None or self._comm_hook is not None
                 or not hasattr(self.backend, "bucket_comm") or os.environ.get("PTDB200_DDP_NATIVE", "1") == "0"):
             return
         fused = getattr(self, "_fused_opt", None) is not None
@@ -380,6 +383,16 @@ class DistributedDataParallel(nn.Module):
             yield
         finally:
             self.require_backward_grad_sync = old
+
+    def register_comm_hook(self, hook) -> None:
+        """Replace the gradient averaging of a bucket: ``hook(flat)`` is called once per finished bucket (on the
+        communication stream on CUDA) and must leave the averaged gradients in ``flat`` (a 1-D view of the bucket).
+        The analogue of torch DDP's ``register_comm_hook`` for synchronous hooks, e.g. compression or logging around
+        ``ddp.backend.all_reduce_avg``.  Switches the native launch path off (the hook is Python)."""
+        if getattr(self, "_fused_opt", None) is not None:
+            raise RuntimeError("a communication hook cannot be combined with fuse_optimizer()")
+        self._comm_hook = hook
+        self._native = False
 
     def bucket_sizes_bytes(self) -> List[int]:
         return [b.flat.numel() * b.flat.element_size() for b in self._buckets]
@@ -489,12 +502,20 @@ class DistributedDataParallel(nn.Module):
             b.ready_event.record(torch.cuda.current_stream(self.device))
             self._comm_stream.wait_event(b.ready_event)
             with torch.cuda.stream(self._comm_stream), nvtx_range("ddp/bucket_allreduce"):
-                self.backend.all_reduce_avg(b.flat)
+                (self._comm_hook or self.backend.all_reduce_avg)(b.flat)
                 b.done_event.record(self._comm_stream)
         else:
-            self.backend.all_reduce_avg(b.flat)
+            (self._comm_hook or self.backend.all_reduce_avg)(b.flat)
 
     def _finalize_backward(self) -> None:
+        if self.find_unused_parameters and self.require_backward_grad_sync:
+            # whoever got no gradient in this backward is reported now, in registration order (the same on every
+            # rank): their views hold zeros, their buckets complete and are averaged like the others
+            n = len(self._buckets)
+            out = (ctypes.c_int * n)()
+            if _lib.call_ret("ptd_reducer_incomplete", self._reducer_id, ctypes.cast(out, ctypes.c_void_p), n) > 0:
+                for p in self._params:
+                    self.mark_ready(p)              # already-marked parameters are ignored by the reducer (-2)
         self._callback_queued = False
         if self._native:
             rc = _lib.call_ret("ptd_reducer_finalize", self._reducer_id, torch.cuda.current_stream(self.device).cuda_stream)
@@ -508,7 +529,7 @@ class DistributedDataParallel(nn.Module):
             c = _lib.call_ret("ptd_reducer_incomplete", self._reducer_id, ctypes.cast(out, ctypes.c_void_p), n)
             _lib.call_ret("ptd_reducer_reset", self._reducer_id)
             raise RuntimeError(f"{c} gradient bucket(s) did not complete in this backward: some parameter did not "
-                               "receive a gradient (find_unused_parameters is not supported)")
+                               "receive a gradient (pass find_unused_parameters=True)")
         if self._comm_stream is not None:
             cur = torch.cuda.current_stream(self.device)
             for b in self._buckets:

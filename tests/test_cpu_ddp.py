@@ -189,3 +189,65 @@ def test_cli_communication_flags_are_additive(tmp_path):
                               capture_output=True, text=True, timeout=120).stdout
     for flag in ("--max_epochs", "--batch_size", "--backend", "--dtype", "--bucket_cap_mb"):
         assert flag in helptext
+
+
+def _unused_and_hook(rank, world):
+    import torch
+    import torch.distributed as dist
+    import torch.nn.functional as F
+    from pytorchdistributed_b200.parallel import DistributedDataParallel as DDP
+
+    class TwoHeads(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.body = torch.nn.Linear(6, 8)
+            self.used = torch.nn.Linear(8, 3)
+            self.unused = torch.nn.Linear(8, 3)          # never part of the loss
+
+        def forward(self, x):
+            return self.used(torch.relu(self.body(x)))
+
+    torch.manual_seed(0)
+    g = torch.Generator().manual_seed(3)
+    xs, ts = torch.randn(8 * world, 6, generator=g), torch.randn(8 * world, 3, generator=g)
+    x, t = xs[rank * 8:(rank + 1) * 8], ts[rank * 8:(rank + 1) * 8]
+    out = {}
+    # without the flag the missing gradients are an error, with it the step goes through
+    strict = DDP(TwoHeads(), bucket_cap_mb=0.0001, first_bucket_mb=0.0001)
+    try:
+        F.mse_loss(strict(x), t).backward()
+        out["strict_raised"] = False
+    except RuntimeError as e:
+        out["strict_raised"] = "find_unused_parameters" in str(e)
+    torch.manual_seed(0)
+    model = TwoHeads()
+    ddp = DDP(model, bucket_cap_mb=0.0001, first_bucket_mb=0.0001, find_unused_parameters=True)
+    calls = []
+
+    def hook(flat):                                          # a communication hook: count, then average as usual
+        calls.append(flat.numel())
+        dist.all_reduce(flat)
+        flat.div_(world)
+
+    ddp.register_comm_hook(hook)
+    for _ in range(2):
+        for p in model.parameters():
+            p.grad = None
+        F.mse_loss(ddp(x), t).backward()
+    out["hook_calls"] = len(calls)
+    out["buckets"] = len(ddp.bucket_sizes_bytes())
+    out["unused_grad_zero"] = bool((model.unused.weight.grad == 0).all())
+    # the averaged gradient equals the single-process gradient on the whole batch
+    torch.manual_seed(0)
+    ref = TwoHeads()
+    F.mse_loss(ref(xs), ts).backward()
+    out["grad_matches"] = bool(torch.allclose(model.used.weight.grad, ref.used.weight.grad, atol=1e-6)
+                               and torch.allclose(model.body.weight.grad, ref.body.weight.grad, atol=1e-6))
+    return out
+
+
+def test_find_unused_parameters_and_comm_hook():
+    for res in run_ranks(_unused_and_hook, 2):
+        assert res["strict_raised"] is True
+        assert res["unused_grad_zero"] and res["grad_matches"], res
+        assert res["hook_calls"] == 2 * res["buckets"] and res["buckets"] >= 2, res
