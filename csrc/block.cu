@@ -61,15 +61,24 @@ bool dual_bn_enabled() {
     return v == 1;
 }
 // BN-backward reduce pass of conv1's / conv2's BatchNorm fused into the data-gradient kernel that produces their dz
-// (ptd_conv_dgrad_fused).  OFF by default: measured per layer at batch 256 (profiles/fused_bn_reduce_experiment.txt) the
-// fused kernel LOSES 3-144 us against data gradient + separate reduce kernel on every 1x1 and strided layer - those
-// data gradients are epilogue-bound (tiny K), and the reduction doubles the epilogue's load/ALU work, while the separate
-// reduce kernel already streams at ~4 TB/s; only the stride-1 3x3 layers gain 5-20 us.  Whole step: 19.30 ms fused vs
-// 18.95 ms unfused.  PTDB200_FUSE_BN_REDUCE=1 switches it on (A/B testing).
-bool fuse_bn_reduce_enabled() {
+// (ptd_conv_dgrad_fused; the y / mask operands are prefetched one chunk ahead).  Measured per layer at batch 256
+// (profiles/fused_bn_reduce_experiment.txt): it saves 14-24 us where the kernel runs 64-wide tiles (layer1: 8 epilogue
+// warps, registers to spare for the prefetch) and on the stride-1 3x3 of layer2, and LOSES 2-94 us everywhere else (the
+// 128 / 256-wide kernels spill under their 96-register cap, the strided 3x3 runs four short launches).  So:
+// In the whole step the per-layer gains do not show (18.66-18.67 ms with the selective fusion, 18.65-18.67 ms without, same
+// box, 30 steps each, twice): the reduce kernels it removes were overlapping with the weight-gradient side stream.  So:
+//   PTDB200_FUSE_BN_REDUCE = 0 (default) never, 1 only where a layer was measured to win, 2 everywhere (A/B testing).
+int fuse_bn_reduce_mode() {
     static int v = -1;
     if (v < 0) { const char* e = getenv("PTDB200_FUSE_BN_REDUCE"); v = e ? atoi(e) : 0; }
-    return v == 1;
+    return v;
+}
+// `ch` = channels of the gradient tensor (the BatchNorm's channels), `k`/`stride` = the data-gradient convolution
+bool fuse_bn_reduce_here(int ch, int k, int stride) {
+    const int mode = fuse_bn_reduce_mode();
+    if (mode <= 0) return false;
+    if (mode >= 2) return true;
+    return ch == 64 ? (stride == 1) : (ch == 128 && k == 3 && stride == 1);
 }
 bool overlap_enabled() {
     static int v = -1;
@@ -176,7 +185,7 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
 #define DGRAD_BN(i, dx_, j)                                                                                            \
     do {                                                                                                               \
         bool fused = false;                                                                                            \
-        if (fuse_bn && d->mask[j] != nullptr) {                                                                        \
+        if (d->mask[j] != nullptr && fuse_bn_reduce_here(g[i].cin, g[i].k, g[i].stride)) {                                                                        \
             float* sm = d->sums + off[j];                                                                              \
             const float* sv = d->saved + off[j];                                                                       \
             rc = ptd_conv_dgrad_fused(d->dy[i], d->w[i], dx_, nullptr, nullptr, d->y[j], d->mask[j], sv, sv + g[j].cout, \
@@ -226,7 +235,6 @@ extern "C" int ptd_bottleneck_bwd(const PtdBottleneckBwd* d, void* stream) {
     } else {
         BN_BWD(2, d->dz, 1, gate ? nullptr : d->g_id);
     }
-    const bool fuse_bn = fuse_bn_reduce_enabled();
     bool fused_unit[4] = {false, false, false, false};
     DGRAD_BN(2, d->dz2, 1);                 // dz2 = gradient behind bn2 + ReLU: its reduce pass rides on this kernel
     WGRAD(2, d->z[1]);

@@ -636,6 +636,8 @@ def test_kernels_stay_inside_their_outputs():
     (64, 256, 1, 1, 14, 5, False),      # 1x1, 64-wide tiles, M = 980 (not a multiple of 128)
     (256, 1024, 1, 1, 14, 6, False),    # 1x1, K = 1024: CTA-pair kernel, two chunks per epilogue warp
     (128, 128, 3, 1, 14, 5, False),     # 3x3 stride 1: im2col + TMA store
+    (64, 64, 3, 1, 28, 5, False),       # layer1's 3x3: 64-wide tiles, several tiles per CTA (prefetch across tiles)
+    (64, 256, 1, 1, 56, 8, False),      # layer1's conv3 data gradient: 196 tiles, the persistent loop wraps
     (128, 128, 3, 2, 28, 3, False),     # 3x3 stride 2: four parity launches, rows remapped
     (256, 64, 1, 1, 14, 5, True),       # 1x1 with the mask-gated addend (identity-branch gradient)
     (512, 128, 1, 1, 8, 3, True),
