@@ -20,8 +20,8 @@
 #include <string.h>
 #include <unistd.h>
 
+#include <deque>
 #include <mutex>
-#include <vector>
 
 #include "common.cuh"
 #include "ptdb200.h"
@@ -128,7 +128,7 @@ struct Block {
 };
 
 std::mutex g_mu;
-std::vector<Block> g_blocks(1);                             // id 0 is never handed out
+std::deque<Block> g_blocks(1);      // id 0 is never handed out; a deque: references stay valid while blocks are added
 
 Block* get(int id) {
     if (id <= 0 || id >= (int)g_blocks.size() || !g_blocks[id].live) {
