@@ -93,9 +93,7 @@ def allreduce_table(out):
         out.append("|---|---|---|---|---|---|---|---|---|")
         for r in d["rows"]:
             g = lambda k: (f"{r[k]:.1f}" if k in r else "-")  # noqa: E731
-            # the N = 2 file was recorded before the world-size rule existed (its `ours` arm ran the switch kernel);
-            # at two ranks DDP runs the two-shot kernel, so that arm is the one quoted
-            ours = r["two_shot_us"] if n == 2 else r["ours_us"]
+            ours = r["ours_us"]
             bus = 2.0 * (n - 1) / n * r["bytes"] / ours / 1e3
             out.append(f"| {r['bytes']} | {ours:.1f} | {g('two_shot_us')} | {g('nvls_us')} | {g('wire_bf16_us')} | {g('nccl_us')} | "
                        f"{bus:.0f} | {bus / 770.0:.2f} | {r['nccl_us'] / ours:.2f}x |")
