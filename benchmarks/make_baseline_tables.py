@@ -65,6 +65,37 @@ def bench_table(out):
         out.append(f"| {n} | {d['value']:.0f}{eff} | {d['ms_per_step']} | {d['e2e']['value']:.0f} | {d['e2e']['ms_per_step']} | "
                    f"{comm_label(d)} | {clk(d.get('clocks'))} | `profiles/{f}` |")
     out.append("")
+    out.append("Final tree (hot kernels launched as programmatic dependents, `PTDB200_PDL=2`, the default since; each row its "
+               "own box, so no ratio between them):\n")
+    out.append("| GPUs | images/s | ms/step | e2e images/s | e2e ms/step | gradient path | clocks | file |")
+    out.append("|---|---|---|---|---|---|---|---|")
+    for n, f in [(1, "bench_n1_r2_pdl.json"), (2, "bench_n2_r2_pdl.json")]:
+        d = load(f)
+        if d:
+            out.append(f"| {n} | {d['value']:.0f} | {d['ms_per_step']} | {d['e2e']['value']:.0f} | {d['e2e']['ms_per_step']} | "
+                       f"{comm_label(d)} | {clk(d.get('clocks'))} | `profiles/{f}` |")
+    ab = [load("pdl_ab_mode1.json"), load("pdl_ab_mode2.json")]
+    if all(ab):
+        out.append("")
+        out.append("Same-process A/B of that change (two graphs of the same step on the same tensors, alternating blocks of 20 "
+                   "replays, `benchmarks/experiments/pdl_ab.py`):\n")
+        out.append("| arm | median ms/step normal | median ms/step with it | ratio | clocks | file |")
+        out.append("|---|---|---|---|---|---|")
+        for d, label, f in [(ab[0], "`PTDB200_PDL=1`: GEMM kernels release their dependents after their last load", "pdl_ab_mode1.json"),
+                            (ab[1], "`PTDB200_PDL=2`: dependents released when a CTA exits (default)", "pdl_ab_mode2.json")]:
+            out.append(f"| {label} | {d['median_normal_ms']} | {d['median_pdl_ms']} | {d['pdl_over_normal']:.4f} | "
+                       f"{clk(d.get('clocks'))} | `profiles/{f}` |")
+    ks = load("step_knob_sweep.json")
+    if ks:
+        out.append("")
+        out.append("In-step sweep of the tuning knobs (one process per row, same box, back to back; "
+                   "`benchmarks/experiments/step_knob_sweep.py`; taken before the default changed, so `defaults` = no PDL):\n")
+        out.append("| setting | median ms/step | vs defaults | clocks |")
+        out.append("|---|---|---|---|")
+        for r in ks["rows"]:
+            out.append(f"| `{r['setting']}` | {r.get('median_ms', 'failed')} | {r.get('vs_defaults', '-')} | {clk(r.get('clocks'))} |")
+        out.append("\nFile: `profiles/step_knob_sweep.json`.")
+    out.append("")
     out.append("Control runs at 8 GPUs (same box, same call; what the 1 -> 8 growth of the step is made of):\n")
     out.append("| run | ms/step | e2e ms/step | clocks | file |")
     out.append("|---|---|---|---|---|")

@@ -14,8 +14,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "pytorchdistributed_b200", "lib", "libptdb200.so")
 # (demangled-name pattern, instructions that mark the interesting region, context lines)
 WANT = [
-    (r"igemm_f_kernel<256, 2, false, 0, false>", r"UTCHMMA|UTMALDG|UTCBAR|LDTM|UTMASTG", 6),
-    (r"igemm_f_kernel<256, 1, true, 0, true>", r"UTCHMMA|UTMALDG|UTCBAR", 6),          # CTA pair (cta_group::2), dgrad form
+    (r"igemm_f_kernel<256, 2, false, 0, false, false>", r"UTCHMMA|UTMALDG|UTCBAR|LDTM|UTMASTG|ACQBULK|PREEXIT", 6),
+    (r"igemm_f_kernel<256, 1, true, 0, true, false>", r"UTCHMMA|UTMALDG|UTCBAR", 6),          # CTA pair (cta_group::2), dgrad form
     (r"igemm_w_kernel<4, 2, true>", r"UTCHMMA|UTMALDG|UTCBAR|REDG|RED\.", 5),
     (r"allreduce_mc_kernel<false>", r"LDGMC|STG\.E\.128|REDG|MEMBAR|LDG\.E\.STRONG", 4),
     (r"allreduce_wire_bf16_kernel<8, true>", r"LDGMC|STG\.E\.128\.STRONG|REDG", 3),

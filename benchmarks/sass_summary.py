@@ -11,7 +11,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "pytorchdistributed_b200", "lib", "libptdb200.so")
-KEEP = re.compile(r"^(UTC|UTMA|LDTM|STTM|SYNCS|LDGSTS|LDGMC|RED|REDG|UBLKCP|UBLKPF|UCGABAR|ATOM|CCTL|ELECT)|\.SYS")
+KEEP = re.compile(r"^(UTC|UTMA|LDTM|STTM|SYNCS|LDGSTS|LDGMC|RED|REDG|UBLKCP|UBLKPF|UCGABAR|ATOM|CCTL|ELECT|ACQBULK|PREEXIT)|\.SYS")
 
 
 def main():
@@ -32,7 +32,8 @@ def main():
     print("SASS mnemonic counts per kernel (cuobjdump -sass libptdb200.so; sm_100a).")
     print("UTCHMMA = tcgen05.mma (.2CTA = cta_group::2), LDTM = tcgen05.ld, UTMALDG(.IM2COL) = cp.async.bulk.tensor load, "
           "UTMASTG = TMA store,\nUTCBAR = tcgen05.commit, SYNCS = mbarrier, LDGSTS = cp.async, RED/REDG = red.global, "
-          "UCGABAR = cluster barrier, *.SYS loads/stores = peer (NVLink) accesses in the collectives,\nLDGMC = multimem.ld_reduce (the NVSwitch reduction; multimem.st / multimem.red show up as STG / REDG on the multicast address).\n")
+          "UCGABAR = cluster barrier, *.SYS loads/stores = peer (NVLink) accesses in the collectives,\nLDGMC = multimem.ld_reduce (the NVSwitch reduction; multimem.st / multimem.red show up as STG / REDG on the multicast address),\n"
+          "ACQBULK = griddepcontrol.wait, PREEXIT = griddepcontrol.launch_dependents (programmatic dependent launch).\n")
     rows = []
     for (mangled, cnt), name in zip(per.items(), demangled):
         if not cnt:

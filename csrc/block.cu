@@ -49,7 +49,15 @@ SideStream* side_stream() {
     std::lock_guard<std::mutex> lk(mu);
     SideStream& s = per_dev[dev];
     if (s.stream == nullptr) {
-        if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        // PTDB200_SIDE_PRIO=1: lowest priority, so that CTAs of the data-gradient chain are placed first when both
+        // streams have work pending
+        const char* e = getenv("PTDB200_SIDE_PRIO");
+        int lo = 0, hi = 0;
+        if (e && atoi(e) == 1 && cudaDeviceGetStreamPriorityRange(&lo, &hi) == cudaSuccess) {
+            if (cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, lo) != cudaSuccess) return nullptr;
+        } else if (cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess) {
+            return nullptr;
+        }
         for (auto& e : s.ev)
             if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
     }

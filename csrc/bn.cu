@@ -96,6 +96,7 @@ bn_apply_kernel(const bf16* __restrict__ y, const bf16* __restrict__ res, bf16* 
                 const float* __restrict__ beta, float* __restrict__ running_mean, float* __restrict__ running_var,
                 float* __restrict__ save_mean, float* __restrict__ save_invstd, unsigned char* __restrict__ mask,
                 long long M, int C, float eps, float momentum) {
+    pdl_wait();
     const int cg = C >> 3;
     const int rows_per_iter = BN_THREADS / cg;
     const int g = threadIdx.x % cg;
@@ -172,6 +173,7 @@ bn_apply_dual_kernel(const bf16* __restrict__ y, const bf16* __restrict__ y2, bf
                      const float* __restrict__ beta2, float* __restrict__ running_mean2, float* __restrict__ running_var2,
                      float* __restrict__ save_mean2, float* __restrict__ save_invstd2, long long M, int C, float eps,
                      float momentum) {
+    pdl_wait();
     const int cg = C >> 3;
     const int rows_per_iter = BN_THREADS / cg;
     const int g = threadIdx.x % cg;
@@ -273,6 +275,7 @@ __global__ void __launch_bounds__(BN_THREADS, 2)
 bn_bwd_reduce_kernel(const bf16* __restrict__ dz, const void* __restrict__ zm, const bf16* __restrict__ y,
                      const float* __restrict__ mean, const float* __restrict__ invstd, float* __restrict__ sum_g,
                      float* __restrict__ sum_gx, long long M, int C) {
+    pdl_wait();
     const int cg = C >> 3;
     const int rows_per_iter = BN_THREADS / cg;
     const int g = threadIdx.x % cg;
@@ -319,6 +322,7 @@ bn_bwd_reduce_kernel(const bf16* __restrict__ dz, const void* __restrict__ zm, c
             }
         }
     }
+    pdl_trigger();      // what is left is the block-level reduction and one atomic per channel
 #pragma unroll
     for (int i = 0; i < 8; ++i) q[i] *= invstd[g * 8 + i];       // xhat = (x - mean) * invstd, factored out of the loop
     extern __shared__ float sh_red[];
@@ -332,6 +336,7 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dz, const void* __restrict__ zm, co
                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
                     const float* __restrict__ sum_g, const float* __restrict__ sum_gx, bf16* __restrict__ dy,
                     bf16* __restrict__ g_out, long long M, int C) {
+    pdl_wait();
     const int cg = C >> 3;
     const int rows_per_iter = BN_THREADS / cg;
     const int g = threadIdx.x % cg;
@@ -399,6 +404,7 @@ bn_bwd_reduce_dual_kernel(const bf16* __restrict__ dz, const unsigned char* __re
                           const float* __restrict__ mean2, const float* __restrict__ invstd2, float* __restrict__ sum_g,
                           float* __restrict__ sum_gx, float* __restrict__ sum_g2, float* __restrict__ sum_gx2, long long M,
                           int C) {
+    pdl_wait();
     const int cg = C >> 3;
     const int rows_per_iter = BN_THREADS / cg;
     const int g = threadIdx.x % cg;
@@ -440,6 +446,7 @@ bn_bwd_reduce_dual_kernel(const bf16* __restrict__ dz, const unsigned char* __re
             }
         }
     }
+    pdl_trigger();
     float s2[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) { q[i] *= invstd[g * 8 + i]; q2[i] *= invstd2[g * 8 + i]; s2[i] = s[i]; }
@@ -456,6 +463,7 @@ bn_bwd_apply_dual_kernel(const bf16* __restrict__ dz, const unsigned char* __res
                          const float* __restrict__ gamma2, const float* __restrict__ sum_g, const float* __restrict__ sum_gx,
                          const float* __restrict__ sum_g2, const float* __restrict__ sum_gx2, bf16* __restrict__ dy,
                          bf16* __restrict__ dy2, long long M, int C) {
+    pdl_wait();
     const int cg = C >> 3;
     const int rows_per_iter = BN_THREADS / cg;
     const int g = threadIdx.x % cg;
@@ -536,6 +544,7 @@ bn_relu_pool_fwd_kernel(const bf16* __restrict__ y, bf16* __restrict__ p, uint8_
                         const float* __restrict__ beta, float* __restrict__ running_mean, float* __restrict__ running_var,
                         float* __restrict__ save_mean, float* __restrict__ save_invstd, int N, int H, int W, int C,
                         float eps, float momentum) {
+    pdl_wait();
     const int cg = C >> 3;
     const int g = threadIdx.x % cg;
     const int OH = H >> 1, OW = W >> 1;
@@ -644,6 +653,7 @@ bn_relu_pool_bwd_kernel(const bf16* __restrict__ dp, const uint8_t* __restrict__
                         const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
                         float* __restrict__ sum_g, float* __restrict__ sum_gx, bf16* __restrict__ dy, int N, int H, int W,
                         int C) {
+    pdl_wait();
     const int cg = C >> 3;
     const int g = threadIdx.x % cg;
     const int OH = H >> 1, OW = W >> 1;
@@ -748,9 +758,9 @@ extern "C" int ptd_bn_apply_mask(const void* y, const void* residual, void* z, v
     const int grid = bn_grid(M, C, 3);
     cudaStream_t st = (cudaStream_t)stream;
 #define PTD_BN_APPLY(RELU, RES)                                                                                     \
-    bn_apply_kernel<RELU, RES><<<grid, BN_THREADS, 0, st>>>((const bf16*)y, (const bf16*)residual, (bf16*)z, sum, sq, \
-                                                           gamma, beta, running_mean, running_var, save_mean,      \
-                                                           save_invstd, (unsigned char*)mask, M, C, eps, momentum)
+    PTD_CUDA_CHECK(ptd_launch(bn_apply_kernel<RELU, RES>, dim3(grid), dim3(BN_THREADS), 0, st, 1, (const bf16*)y,       \
+                              (const bf16*)residual, (bf16*)z, sum, sq, gamma, beta, running_mean, running_var,     \
+                              save_mean, save_invstd, (unsigned char*)mask, M, C, eps, momentum))
     if (relu && residual) PTD_BN_APPLY(true, true);
     else if (relu) PTD_BN_APPLY(true, false);
     else if (residual) PTD_BN_APPLY(false, true);
@@ -770,13 +780,12 @@ extern "C" int ptd_bn_bwd_dual(const void* dz, const void* mask, const void* y, 
     PTD_REQUIRE(mask != nullptr, "bn_bwd_dual: the forward's ReLU bit mask is required");
     cudaStream_t st = (cudaStream_t)stream;
     const int grid = bn_grid(M, C, 2);
-    bn_bwd_reduce_dual_kernel<<<grid, BN_THREADS, 2 * C * sizeof(float), st>>>(
-        (const bf16*)dz, (const unsigned char*)mask, (const bf16*)y, (const bf16*)y2, mean, invstd, mean2, invstd2, sums,
-        sums + C, sums2, sums2 + C, M, C);
-    PTD_CUDA_CHECK(cudaGetLastError());
-    bn_bwd_apply_dual_kernel<<<grid, BN_THREADS, 0, st>>>(
-        (const bf16*)dz, (const unsigned char*)mask, (const bf16*)y, (const bf16*)y2, mean, invstd, gamma, mean2, invstd2,
-        gamma2, sums, sums + C, sums2, sums2 + C, (bf16*)dy, (bf16*)dy2, M, C);
+    PTD_CUDA_CHECK(ptd_launch(bn_bwd_reduce_dual_kernel, dim3(grid), dim3(BN_THREADS), 2 * C * sizeof(float), st, 1,
+                              (const bf16*)dz, (const unsigned char*)mask, (const bf16*)y, (const bf16*)y2, mean, invstd,
+                              mean2, invstd2, sums, sums + C, sums2, sums2 + C, M, C));
+    PTD_CUDA_CHECK(ptd_launch(bn_bwd_apply_dual_kernel, dim3(grid), dim3(BN_THREADS), 0, st, 1, (const bf16*)dz,
+                              (const unsigned char*)mask, (const bf16*)y, (const bf16*)y2, mean, invstd, gamma, mean2,
+                              invstd2, gamma2, sums, sums + C, sums2, sums2 + C, (bf16*)dy, (bf16*)dy2, M, C));
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }
@@ -789,10 +798,10 @@ extern "C" int ptd_bn_apply_dual(const void* y, const void* y2, void* z, void* m
                                  float* save_mean2, float* save_invstd2, long long M, int C, float eps, float momentum,
                                  void* stream) {
     PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
-    bn_apply_dual_kernel<<<bn_grid(M, C, 3), BN_THREADS, 0, (cudaStream_t)stream>>>(
-        (const bf16*)y, (const bf16*)y2, (bf16*)z, (unsigned char*)mask, sum, sq, gamma, beta, running_mean, running_var,
-        save_mean, save_invstd, sum2, sq2, gamma2, beta2, running_mean2, running_var2, save_mean2, save_invstd2, M, C,
-        eps, momentum);
+    PTD_CUDA_CHECK(ptd_launch(bn_apply_dual_kernel, dim3(bn_grid(M, C, 3)), dim3(BN_THREADS), 0, (cudaStream_t)stream, 1,
+                              (const bf16*)y, (const bf16*)y2, (bf16*)z, (unsigned char*)mask, sum, sq, gamma, beta,
+                              running_mean, running_var, save_mean, save_invstd, sum2, sq2, gamma2, beta2, running_mean2,
+                              running_var2, save_mean2, save_invstd2, M, C, eps, momentum));
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }
@@ -819,12 +828,13 @@ extern "C" int ptd_bn_bwd_reduce(const void* dz, const void* z, const void* y, c
     const int grid = min(bn_grid(M, C), ptd_num_sms() * 2);      // two resident blocks per SM (launch bounds)
     cudaStream_t st = (cudaStream_t)stream;
     const size_t sh = 2 * C * sizeof(float);
-    if (relu == 2)
-        bn_bwd_reduce_kernel<2><<<grid, BN_THREADS, sh, st>>>((const bf16*)dz, z, (const bf16*)y, mean, invstd, sum_g, sum_gx, M, C);
-    else if (relu)
-        bn_bwd_reduce_kernel<1><<<grid, BN_THREADS, sh, st>>>((const bf16*)dz, z, (const bf16*)y, mean, invstd, sum_g, sum_gx, M, C);
-    else
-        bn_bwd_reduce_kernel<0><<<grid, BN_THREADS, sh, st>>>((const bf16*)dz, z, (const bf16*)y, mean, invstd, sum_g, sum_gx, M, C);
+#define PTD_RED(RELU)                                                                                                 \
+    PTD_CUDA_CHECK(ptd_launch(bn_bwd_reduce_kernel<RELU>, dim3(grid), dim3(BN_THREADS), sh, st, 1, (const bf16*)dz, z, \
+                              (const bf16*)y, mean, invstd, sum_g, sum_gx, M, C))
+    if (relu == 2) PTD_RED(2);
+    else if (relu) PTD_RED(1);
+    else PTD_RED(0);
+#undef PTD_RED
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }
@@ -836,8 +846,8 @@ extern "C" int ptd_bn_bwd_apply(const void* dz, const void* z, const void* y, co
     const int grid = bn_grid(M, C, 3);
     cudaStream_t st = (cudaStream_t)stream;
 #define PTD_BWD(RELU, GOUT)                                                                                         \
-    bn_bwd_apply_kernel<RELU, GOUT><<<grid, BN_THREADS, 0, st>>>((const bf16*)dz, z, (const bf16*)y, mean,             \
-                                                                invstd, gamma, sum_g, sum_gx, (bf16*)dy, (bf16*)g_out, M, C)
+    PTD_CUDA_CHECK(ptd_launch(bn_bwd_apply_kernel<RELU, GOUT>, dim3(grid), dim3(BN_THREADS), 0, st, 1, (const bf16*)dz, \
+                              z, (const bf16*)y, mean, invstd, gamma, sum_g, sum_gx, (bf16*)dy, (bf16*)g_out, M, C))
     if (relu == 2 && g_out) PTD_BWD(2, true);
     else if (relu == 2) PTD_BWD(2, false);
     else if (relu && g_out) PTD_BWD(1, true);
@@ -857,9 +867,9 @@ extern "C" int ptd_bn_relu_maxpool_fwd(const void* y, void* p, void* idx, const 
     PTD_REQUIRE(bn_shape_ok(C), "bn: C (%d) must be a power of two in [64, 2048]", C);
     PTD_REQUIRE(H % 2 == 0 && W % 2 == 0, "bn_relu_maxpool: H (%d) and W (%d) must be even", H, W);
     const int grid = bn_grid((long long)N * (H / 2) * (W / 2), C, 4);
-    bn_relu_pool_fwd_kernel<<<grid, BN_THREADS, 0, (cudaStream_t)stream>>>(
-        (const bf16*)y, (bf16*)p, (uint8_t*)idx, sum, sq, gamma, beta, running_mean, running_var, save_mean, save_invstd,
-        N, H, W, C, eps, momentum);
+    PTD_CUDA_CHECK(ptd_launch(bn_relu_pool_fwd_kernel, dim3(grid), dim3(BN_THREADS), 0, (cudaStream_t)stream, 1,
+                              (const bf16*)y, (bf16*)p, (uint8_t*)idx, sum, sq, gamma, beta, running_mean, running_var,
+                              save_mean, save_invstd, N, H, W, C, eps, momentum));
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }
@@ -873,11 +883,12 @@ extern "C" int ptd_bn_relu_maxpool_bwd(const void* dp, const void* idx, const vo
     PTD_REQUIRE(H % 2 == 0 && W % 2 == 0, "bn_relu_maxpool: H (%d) and W (%d) must be even", H, W);
     const int grid = bn_grid((long long)N * (H / 2) * (W / 2), C, 2);
     cudaStream_t st = (cudaStream_t)stream;
-    bn_relu_pool_bwd_kernel<0><<<grid, BN_THREADS, 2 * C * sizeof(float), st>>>(
-        (const bf16*)dp, (const uint8_t*)idx, (const bf16*)y, mean, invstd, gamma, sums, sums + C, nullptr, N, H, W, C);
-    PTD_CUDA_CHECK(cudaGetLastError());
-    bn_relu_pool_bwd_kernel<1><<<grid, BN_THREADS, 0, st>>>(
-        (const bf16*)dp, (const uint8_t*)idx, (const bf16*)y, mean, invstd, gamma, sums, sums + C, (bf16*)dy, N, H, W, C);
+    PTD_CUDA_CHECK(ptd_launch(bn_relu_pool_bwd_kernel<0>, dim3(grid), dim3(BN_THREADS), 2 * C * sizeof(float), st, 1,
+                              (const bf16*)dp, (const uint8_t*)idx, (const bf16*)y, mean, invstd, gamma, sums, sums + C,
+                              (bf16*)nullptr, N, H, W, C));
+    PTD_CUDA_CHECK(ptd_launch(bn_relu_pool_bwd_kernel<1>, dim3(grid), dim3(BN_THREADS), 0, st, 1, (const bf16*)dp,
+                              (const uint8_t*)idx, (const bf16*)y, mean, invstd, gamma, sums, sums + C, (bf16*)dy, N, H,
+                              W, C));
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }

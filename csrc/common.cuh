@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <string.h>
 
 // ---------------------------------------------------------------------------------------------
 // Error reporting: entry points return 0 on success, a negative ptd error otherwise; the last
@@ -43,6 +44,10 @@ typedef __nv_bfloat16 bf16;
 static inline int ceil_div_i(long long a, long long b) { return (int)((a + b - 1) / b); }
 
 int ptd_num_sms();   // SM count of the current device (cached per device)
+// PTDB200_PDL: 0 = plain launches; 2 (default) = the hot kernels are launched as programmatic dependents of their
+// predecessor; 1 = same, and the GEMM kernels release their dependents as soon as their last operands are requested
+// (measured slower in the ResNet-50 step: profiles/pdl_ab_mode1.json vs pdl_ab_mode2.json)
+int ptd_pdl_mode();
 
 // ---------------------------------------------------------------------------------------------
 // Device-side PTX wrappers
@@ -58,6 +63,14 @@ __device__ __forceinline__ uint32_t lane_id() {
     asm volatile("mov.u32 %0, %%laneid;" : "=r"(l));
     return l;
 }
+
+// ---- programmatic dependent launch ---------------------------------------------------------
+// pdl_wait(): everything the preceding kernel of the stream wrote is visible after it (no-op when the kernel was not
+// launched as a programmatic dependent).  EVERY kernel launched through ptd_launch() executes it before its first global
+// access: completion of kernel N then implies completion of N-1, N-2, ...
+// pdl_trigger(): this CTA no longer objects to the next kernel's CTAs becoming resident (they stop at their own wait).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred = 0;
@@ -331,6 +344,36 @@ __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
+}
+
+// Host side: launch `kern` on `st`, as a programmatic dependent of the kernel before it unless PTDB200_PDL=0 (the kernel
+// must call pdl_wait(); see above).  Extra attributes (a cluster dimension) go in front of ours.
+template <class... KArgs, class... Args>
+inline cudaError_t ptd_launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster_x,
+                              Args&&... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (cluster_x > 1) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = cluster_x;
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        ++na;
+    }
+    if (ptd_pdl_mode() >= 1) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 
 #endif  // __CUDACC__

@@ -353,6 +353,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
     if (PAIR) cluster_sync_all();         // the peer's barriers exist before anything signals them
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_base;
+    pdl_wait();     // barriers, TMEM and descriptor prefetch above overlap the previous kernel's tail (ptd_launch)
 
     if (warp == Cfg::TMA_WARP) {
         // ===================== TMA producer (one lane) =====================
@@ -424,6 +425,7 @@ igemm_f_kernel(const __grid_constant__ FParams p) {
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
+            if (!(p.dbg & 16)) pdl_trigger();      // last operands requested: what is left is the final epilogue
         }
     } else if (warp == Cfg::MMA_WARP) {
         // ===================== MMA issuer (one lane) =====================
@@ -856,6 +858,7 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_ke
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = bars->tmem_base;
+    pdl_wait();
 
     if (warp == TMA_WARP) {
         if (lane == 0) {
@@ -912,6 +915,7 @@ __global__ void __launch_bounds__(WCfg<NSUB, B_MODE, M2>::THREADS, 1) igemm_w_ke
                 }
                 if (++stage == STAGES) { stage = 0; phase ^= 1; }
             }
+            if (!(p.dbg & 16)) pdl_trigger();
         }
     } else if (warp == MMA_WARP) {
         if (lane == 0) {
@@ -987,7 +991,7 @@ int launch_f(FParams& p, cudaStream_t stream) {
     }
     p.m_blocks = ceil_div_i(p.M, BLOCK_M);
     p.n_blocks = ceil_div_i(p.N, BLOCK_N);
-    { const char* e = getenv("PTD_IGEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
+    { const char* e = getenv("PTD_IGEMM_DBG"); p.dbg = (e ? atoi(e) : 0) | (ptd_pdl_mode() == 2 ? 16 : 0); }
     {   // PTD_STATS_SMEM_KB: largest K loop (in k-blocks) that still uses the shared-memory column sums
         static int kb_max = -1;
         if (kb_max < 0) { const char* e = getenv("PTD_STATS_SMEM_KB"); kb_max = e ? atoi(e) : 4; }
@@ -998,7 +1002,7 @@ int launch_f(FParams& p, cudaStream_t stream) {
     grid = (grid / p.n_blocks) * p.n_blocks;      // fixed n block per CTA (register-resident BN partial sums)
     if (grid < p.n_blocks) grid = p.n_blocks;
     if (grid > tiles) grid = tiles;               // tiles is a multiple of n_blocks
-    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>(p);
+    PTD_CUDA_CHECK(ptd_launch(kern, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, stream, 1, p));
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }
@@ -1017,27 +1021,14 @@ int launch_f_pair(FParams& p, cudaStream_t stream) {
     }
     p.m_blocks = ceil_div_i(p.M, 2 * BLOCK_M);
     p.n_blocks = ceil_div_i(p.N, BLOCK_N);
-    { const char* e = getenv("PTD_IGEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
+    { const char* e = getenv("PTD_IGEMM_DBG"); p.dbg = (e ? atoi(e) : 0) | (ptd_pdl_mode() == 2 ? 16 : 0); }
     p.stats_smem = 0;
     const int tiles = p.m_blocks * p.n_blocks;
     int workers = ptd_num_sms() / 2;
     workers = (workers / p.n_blocks) * p.n_blocks;      // fixed n block per worker
     if (workers < p.n_blocks) workers = p.n_blocks;
     if (workers > tiles) workers = tiles;
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3(2 * workers);
-    cfg.blockDim = dim3(Cfg::THREADS);
-    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = 2;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    PTD_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p));
+    PTD_CUDA_CHECK(ptd_launch(kern, dim3(2 * workers), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, stream, 2, p));
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }
@@ -1105,14 +1096,14 @@ int launch_w_impl(WParams& p, int grid, cudaStream_t stream) {
         PTD_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM_BYTES));
         configured[dev & 63] = true;
     }
-    kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, stream>>>(p);
+    PTD_CUDA_CHECK(ptd_launch(kern, dim3(grid), dim3(Cfg::THREADS), Cfg::SMEM_BYTES, stream, 1, p));
     PTD_CUDA_CHECK(cudaGetLastError());
     return PTD_OK;
 }
 
 template <int NSUB, int B_MODE>
 int launch_w(WParams& p, cudaStream_t stream) {
-    { const char* e = getenv("PTD_IGEMM_DBG"); p.dbg = e ? atoi(e) : 0; }
+    { const char* e = getenv("PTD_IGEMM_DBG"); p.dbg = (e ? atoi(e) : 0) | (ptd_pdl_mode() == 2 ? 16 : 0); }
     static int dual_m = -1;
     if (dual_m < 0) { const char* e = getenv("PTD_WGRAD_M2"); dual_m = e ? atoi(e) : 1; }
     // measured per layer: im2col weight gradients 99 -> 72 us; plain 1x1 ones lose a few us (fewer stages), so only im2col

@@ -2,6 +2,7 @@
 // (driver entry point fetched at run time so the library links without libcuda and loads on a
 // CPU-only box for the plumbing tests).
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -35,6 +36,19 @@ int ptd_num_sms() {
 }
 
 extern "C" int ptd_device_sm_count() { return ptd_num_sms(); }
+
+static int g_pdl_mode = -1;
+int ptd_pdl_mode() {
+    // default 2: measured in the ResNet-50 step (profiles/pdl_ab_mode{1,2}.json) - 2 is 0.6 % faster than 0, 1 is 0.7 % slower
+    if (g_pdl_mode < 0) { const char* e = getenv("PTDB200_PDL"); g_pdl_mode = e ? atoi(e) : 2; }
+    return g_pdl_mode;
+}
+// Overrides PTDB200_PDL for launches issued from now on (A/B runs inside one process); returns the previous mode.
+extern "C" int ptd_set_pdl_mode(int mode) {
+    const int old = ptd_pdl_mode();
+    g_pdl_mode = mode < 0 ? 0 : (mode > 2 ? 2 : mode);
+    return old;
+}
 
 // ---------------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,

@@ -19,6 +19,11 @@ extern "C" {
 const char* ptd_last_error(void);
 int ptd_version(void);
 int ptd_device_sm_count(void);
+/* Programmatic dependent launch of the hot kernels (convolution and BatchNorm kernels start their prologue while the
+ * previous kernel of the stream drains; each waits with griddepcontrol.wait before its first global access).
+ * 0 = off, 2 = on (default, or PTDB200_PDL), 1 = on + early release of dependents by the GEMM kernels; returns the
+ * previous mode. */
+int ptd_set_pdl_mode(int mode);
 
 /* ---- convolution as implicit GEMM on tcgen05/TMEM (R/03 模型并行/03_model_parallel.ipynb#cell4-5:
  *      every Conv2d of ResNet(Bottleneck,[3,4,6,3]); cuDNN in the reference) --------------------- */

@@ -21,6 +21,7 @@ P, I, L, F = c_void_p, c_int, c_longlong, c_float
 _SIGS: dict[str, list] = {
     "ptd_version": [],
     "ptd_device_sm_count": [],
+    "ptd_set_pdl_mode": [I],
     "ptd_conv_fprop": [P, P, P, P, P, I, I, I, I, I, I, I, I, I, P],
     "ptd_conv_dgrad": [P, P, P, P, I, I, I, I, I, I, I, I, I, P],
     "ptd_conv_dgrad_accum": [P, P, P, I, I, I, I, I, I, I, I, I, P],
