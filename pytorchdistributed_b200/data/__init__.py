@@ -1,5 +1,6 @@
-from .datasets import MyTrainDataset, SimpleDataset, SyntheticImageDataset, generate_random_data
+from .datasets import (DeviceSyntheticBatches, MyTrainDataset, SimpleDataset, SyntheticImageDataset,
+                       generate_random_data)
 from .sampler import DistributedSampler, ShardedSampler
 
-__all__ = ["MyTrainDataset", "SimpleDataset", "SyntheticImageDataset", "generate_random_data",
+__all__ = ["DeviceSyntheticBatches", "MyTrainDataset", "SimpleDataset", "SyntheticImageDataset", "generate_random_data",
            "DistributedSampler", "ShardedSampler"]

@@ -8,6 +8,8 @@
   ``randn(B,3,H,W)`` and float one-hot labels ``[B, num_classes]``.
 * ``SyntheticImageDataset`` is an addition for the ResNet-50 runs of the CLI scripts (no dataset can be
   downloaded on the bench box).
+* ``DeviceSyntheticBatches`` generates whole batches on the training device (no host memory, no copies): for kernel-side
+  benchmarks where the input pipeline must not be part of the measurement.
 """
 from __future__ import annotations
 
@@ -70,3 +72,33 @@ class SyntheticImageDataset(Dataset):
     def __getitem__(self, index: int):
         j = index % self.pool
         return self.images[j], self.labels[j]
+
+
+class DeviceSyntheticBatches:
+    """``steps`` batches ``(images [B,3,H,W] fp32, labels [B] int64)`` living on ``device``.
+
+    A small pool of batches is generated once with the device's own generator (seeded, so every run and every rank
+    with the same seed sees the same data) and then cycled: iterating costs nothing on the host or on the device.
+    ``len()`` is the number of steps, so it can stand in for a ``DataLoader`` in ``Trainer`` (``batch_size`` is there
+    for the epoch banner).  Works on CPU too (tests)."""
+
+    def __init__(self, steps: int, batch_size: int, img_size: Tuple[int, int] = (224, 224), num_classes: int = 1000,
+                 device: Optional[torch.device] = None, seed: int = 0, pool: int = 2, one_hot: bool = False) -> None:
+        self.steps, self.batch_size = int(steps), int(batch_size)
+        self.device = torch.device(device) if device is not None else (
+            torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu"))
+        g = torch.Generator(device=self.device).manual_seed(seed)
+        self._pool = []
+        for _ in range(max(1, min(pool, steps))):
+            x = torch.randn(batch_size, 3, img_size[0], img_size[1], device=self.device, generator=g)
+            y = torch.randint(0, num_classes, (batch_size,), device=self.device, generator=g)
+            if one_hot:
+                y = torch.zeros(batch_size, num_classes, device=self.device).scatter_(1, y[:, None], 1.0)
+            self._pool.append((x, y))
+
+    def __len__(self) -> int:
+        return self.steps
+
+    def __iter__(self):
+        for i in range(self.steps):
+            yield self._pool[i % len(self._pool)]
