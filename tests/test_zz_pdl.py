@@ -41,6 +41,6 @@ def test_pdl_launch_modes_compute_the_same_bottleneck(mode):
         for _ in range(3):
             got = run()
             for i, (a, b) in enumerate(zip(got, base)):
-                assert _rel(a, b) < 5e-3, (mode, i)          # fp32 atomics order is the only freedom between two runs
+                assert _rel(a, b) < 2e-2, (mode, i)          # atomics order is the only freedom between two runs; a race is O(1)
     finally:
         _lib.call_ret("ptd_set_pdl_mode", old)
