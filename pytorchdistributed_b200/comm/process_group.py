@@ -23,6 +23,8 @@ from typing import Optional
 import torch
 import torch.distributed as dist
 
+from ..utils.numa import bind_to_gpu_node
+
 DEFAULT_ADDR = "127.0.0.1"      # the reference hard-codes "localhost" (ddp_gpus.py:18); same host, resolvable everywhere
 DEFAULT_PORT = "12355"          # ddp_gpus.py:19
 
@@ -57,12 +59,14 @@ def ddp_setup(rank: Optional[int] = None, world_size: Optional[int] = None, back
         if torch.cuda.is_available():
             torch.cuda.set_device(dev)
             kw["device_id"] = torch.device("cuda", dev)
+            bind_to_gpu_node(dev)          # host threads and pinned staging memory next to this rank's GPU
         dist.init_process_group(rank=rank, world_size=world_size, **kw)
     else:
         dev = local_rank()
         if torch.cuda.is_available():
             torch.cuda.set_device(dev)
             kw["device_id"] = torch.device("cuda", dev)
+            bind_to_gpu_node(dev)
         dist.init_process_group(**kw)
     return dev
 

@@ -79,3 +79,36 @@ def test_fd_channel_passes_descriptors_between_ranks():
         for round_ in range(2):
             assert out[("a2a", round_)] == [None if r == rank else 10 * round_ + r for r in range(world)]
         assert out["root"] == (None if rank == 0 else 77)
+
+
+def test_numa_binding_reads_sysfs_and_is_conservative(tmp_path, monkeypatch):
+    """utils/numa.py: CPUs of the GPU's NUMA node from a (fake) sysfs tree; no change when that is nothing new, too
+    little, unknown, or switched off."""
+    import os
+    from pytorchdistributed_b200.utils import numa
+    assert numa.parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert numa.parse_cpulist("") == set()
+    assert numa.pci_address(0, 0x1b, 0) == "0000:1b:00.0"
+    dev = tmp_path / "bus" / "pci" / "devices" / "0000:1b:00.0"
+    dev.mkdir(parents=True)
+    (dev / "numa_node").write_text("1\n")
+    node = tmp_path / "devices" / "system" / "node" / "node1"
+    node.mkdir(parents=True)
+    (node / "cpulist").write_text("56-111,168-223\n")
+    cpus = numa.gpu_numa_cpus("0000:1b:00.0", str(tmp_path))
+    assert cpus == set(range(56, 112)) | set(range(168, 224))
+    assert numa.gpu_numa_cpus("0000:99:00.0", str(tmp_path)) is None            # unknown device
+    (dev / "numa_node").write_text("-1\n")
+    assert numa.gpu_numa_cpus("0000:1b:00.0", str(tmp_path)) is None            # platform without NUMA information
+    allowed = set(range(224))
+    assert numa.choose_affinity(cpus, allowed) == cpus
+    assert numa.choose_affinity(cpus, cpus) is None                             # already there
+    assert numa.choose_affinity(cpus, {0, 1, 2, 3, 56}) is None                 # one usable CPU: too little
+    assert numa.choose_affinity(cpus, set(range(50, 60))) == {56, 57, 58, 59}   # a cpuset that overlaps the node
+    assert numa.choose_affinity(None, allowed) is None
+    before = os.sched_getaffinity(0)
+    monkeypatch.setenv("PTDB200_NUMA_BIND", "0")
+    assert numa.bind_to_gpu_node(0) is None
+    monkeypatch.delenv("PTDB200_NUMA_BIND")
+    assert numa.bind_to_gpu_node(0) is None                                     # no GPU here: nothing happens, nothing raised
+    assert os.sched_getaffinity(0) == before
