@@ -28,6 +28,7 @@ from __future__ import annotations
 import contextlib
 import ctypes
 import os
+import time
 from typing import Dict, List, Optional
 
 import torch
@@ -95,7 +96,7 @@ class _TorchCollectives:
 
 
 class _Bucket:
-    __slots__ = ("flat", "params", "views", "offsets", "ready_event", "done_event", "launched")
+    __slots__ = ("flat", "params", "views", "offsets", "ready_event", "done_event", "launched", "t0", "t1")
 
     def __init__(self) -> None:
         self.params: List[nn.Parameter] = []
@@ -105,6 +106,7 @@ class _Bucket:
         self.ready_event = None
         self.done_event = None
         self.launched = False
+        self.t0 = self.t1 = None            # communication timing (enable_comm_timing): events on CUDA, seconds on CPU
 
 
 class DistributedDataParallel(nn.Module):
@@ -121,6 +123,9 @@ class DistributedDataParallel(nn.Module):
         # parameters unused (a static sub-graph), the rank-divergent case of torch's bitmap exchange is not covered.
         self.find_unused_parameters = bool(find_unused_parameters)
         self._comm_hook = None
+        self._time_comm = False
+        self._comm_ms: List[float] = []
+        self._timed_order: List[_Bucket] = []
         self.module = module
         self.process_group = process_group
         self.world_size = dist.get_world_size(process_group)
@@ -296,7 +301,8 @@ class DistributedDataParallel(nn.Module):
         self._native = False
         self._bucket_comms = []
         if (self.world_size == 1 or self._skip_allreduce or self._comm_stream is None or self._comm_hook is not None
-                or not hasattr(self.backend, "bucket_comm") or os.environ.get("PTDB200_DDP_NATIVE", "1") == "0"):
+                or self._time_comm or not hasattr(self.backend, "bucket_comm")
+                or os.environ.get("PTDB200_DDP_NATIVE", "1") == "0"):
             return
         fused = getattr(self, "_fused_opt", None) is not None
         for bi, b in enumerate(self._buckets):
@@ -393,6 +399,22 @@ class DistributedDataParallel(nn.Module):
             raise RuntimeError("a communication hook cannot be combined with fuse_optimizer()")
         self._comm_hook = hook
         self._native = False
+
+    def enable_comm_timing(self, on: bool = True) -> None:
+        """Time every bucket's gradient averaging (CUDA events on the communication stream; host clock on CPU) - the
+        communication-time counter next to ``utils.metrics.StepMeter``.  ``comm_times_ms()`` returns the last
+        backward's numbers.  Eager steps only (timing events cannot be read out of a replayed CUDA graph); while it is
+        on, buckets are launched from Python instead of by the native reducer."""
+        if on and getattr(self, "_fused_opt", None) is not None:
+            raise RuntimeError("communication timing cannot be combined with fuse_optimizer()")
+        self._time_comm = bool(on)
+        self._comm_ms = []
+        self._bind_native()
+
+    def comm_times_ms(self) -> List[float]:
+        """Milliseconds the averaging of each bucket took in the last synchronised backward, in launch order
+        (waits for the communication stream)."""
+        return list(self._comm_ms)
 
     def bucket_sizes_bytes(self) -> List[int]:
         return [b.flat.numel() * b.flat.element_size() for b in self._buckets]
@@ -502,10 +524,21 @@ class DistributedDataParallel(nn.Module):
             b.ready_event.record(torch.cuda.current_stream(self.device))
             self._comm_stream.wait_event(b.ready_event)
             with torch.cuda.stream(self._comm_stream), nvtx_range("ddp/bucket_allreduce"):
+                if self._time_comm:
+                    b.t0, b.t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    b.t0.record(self._comm_stream)
                 (self._comm_hook or self.backend.all_reduce_avg)(b.flat)
+                if self._time_comm:
+                    b.t1.record(self._comm_stream)
                 b.done_event.record(self._comm_stream)
+            if self._time_comm:
+                self._timed_order.append(b)
         else:
+            t0 = time.perf_counter()
             (self._comm_hook or self.backend.all_reduce_avg)(b.flat)
+            if self._time_comm:
+                b.t0, b.t1 = t0, time.perf_counter()
+                self._timed_order.append(b)
 
     def _finalize_backward(self) -> None:
         if self.find_unused_parameters and self.require_backward_grad_sync:
@@ -537,6 +570,15 @@ class DistributedDataParallel(nn.Module):
                     cur.wait_event(b.done_event)
         for b in self._buckets:
             b.launched = False
+        if self._time_comm:
+            ms = []
+            for b in self._timed_order:
+                if self._comm_stream is not None:
+                    b.t1.synchronize()
+                    ms.append(b.t0.elapsed_time(b.t1))
+                else:
+                    ms.append((b.t1 - b.t0) * 1e3)
+            self._comm_ms, self._timed_order = ms, []
         if not self._rebuilt:
             n = len(self._params)
             out = (ctypes.c_int * n)()

@@ -22,6 +22,7 @@ def _train(rank, world, steps, use_no_sync):
     g = torch.Generator().manual_seed(7)
     xs, ts = torch.randn(steps, 8 * world, 10, generator=g), torch.randn(steps, 8 * world, 5, generator=g)
     init = {k: v.clone() for k, v in model.state_dict().items()}
+    ddp.enable_comm_timing()                 # per-bucket communication-time counter (host clock on the gloo path)
     for s in range(steps):
         x, t = xs[s, rank * 8:(rank + 1) * 8], ts[s, rank * 8:(rank + 1) * 8]
         opt.zero_grad()
@@ -31,7 +32,8 @@ def _train(rank, world, steps, use_no_sync):
             continue
         F.mse_loss(ddp(x), t).backward()
         opt.step()
-    return init, {k: v.clone() for k, v in ddp.state_dict().items()}, len(ddp.bucket_sizes_bytes()), dict(ddp.stats)
+    stats = dict(ddp.stats, comm_ms=ddp.comm_times_ms())
+    return init, {k: v.clone() for k, v in ddp.state_dict().items()}, len(ddp.bucket_sizes_bytes()), stats
 
 
 def test_ddp_matches_single_process():
@@ -42,6 +44,7 @@ def test_ddp_matches_single_process():
     init0, final0, nb, stats = res[0]
     init1, final1, _, _ = res[1]
     assert nb > 1 and stats["iterations"] == steps
+    assert len(stats["comm_ms"]) == nb and all(t >= 0.0 for t in stats["comm_ms"])     # one timing per bucket of the last backward
     for k in init0:
         assert torch.equal(init0[k], init1[k])                  # rank 0's weights were broadcast
     assert all(k.startswith("module.") for k in final0)         # reference quirk 6
