@@ -11,7 +11,9 @@ Surface and semantics follow what the reference uses (``DDP(model, device_ids=[g
   gradient is ready; a bucket whose last gradient arrived is averaged across ranks right away on a
   communication stream, overlapping the rest of backward;
 * ``no_sync()`` skips the reduction (local accumulation); buffers (BatchNorm statistics) are
-  re-broadcast from rank 0 before every forward, as one flat message.
+  re-broadcast from rank 0, as one flat message, before every forward that follows a gradient-synchronised
+  forward (torch's ``require_forward_param_sync`` rule: every training step, and the first evaluation pass
+  after training).
 
 What changes underneath: on CUDA with >1 rank the averaging is our own kernel over NVLink (``comm/p2p.py``):
 through the NVSwitch (``multimem.ld_reduce`` / ``multimem.st``) where the box exposes multicast objects, a two-shot
@@ -135,6 +137,7 @@ class DistributedDataParallel(nn.Module):
         self.broadcast_buffers = broadcast_buffers and os.environ.get("PTDB200_DDP_BCAST", "1") != "0"
         self._skip_allreduce = os.environ.get("PTDB200_DDP_SKIP_ALLREDUCE", "0") == "1"
         self.require_backward_grad_sync = True
+        self._require_forward_param_sync = True
         self.bucket_cap = int(bucket_cap_mb * _MiB)
         self.first_cap = int(first_bucket_mb * _MiB)
         self._want_rebuild = rebuild_buckets
@@ -422,7 +425,16 @@ class DistributedDataParallel(nn.Module):
     def forward(self, *inputs, **kwargs):
         if self.training and torch.is_grad_enabled():
             self._prepare_iteration()
-        return self.module(*inputs, **kwargs)
+        # Buffers: rank 0's win before a forward that follows a gradient-synchronised one - torch's rule
+        # (``require_forward_param_sync``), which also covers the first evaluation pass after training (ranks then
+        # evaluate with the same BatchNorm statistics) and skips the broadcast between no_sync() passes.
+        if self._require_forward_param_sync and self.broadcast_buffers and self.world_size > 1 and self._buf_flats:
+            with torch.no_grad():
+                for bf in self._buf_flats:
+                    self.backend.broadcast(bf, 0)
+        out = self.module(*inputs, **kwargs)
+        self._require_forward_param_sync = torch.is_grad_enabled() and self.require_backward_grad_sync
+        return out
 
     def _prepare_iteration(self) -> None:
         if self._want_rebuild and not self._rebuilt and self.stats["iterations"] >= 1:
@@ -447,10 +459,6 @@ class DistributedDataParallel(nn.Module):
                     self._view_of[id(p)].zero_()
             for p in dropped:
                 p.grad = self._view_of[id(p)]
-        if self.broadcast_buffers and self.world_size > 1 and self.require_backward_grad_sync:
-            with torch.no_grad():
-                for bf in self._buf_flats:
-                    self.backend.broadcast(bf, 0)
 
     _last_ready_order: Optional[List[int]] = None
 

@@ -109,7 +109,14 @@ def _buffers(rank, world):
     ddp(x).sum().backward()
     after_one = net.bn.running_mean.clone()      # local update, differs per rank
     ddp(x).sum().backward()                      # the forward re-broadcasts rank 0's buffers first
-    return first, after_one, net.bn.running_mean.clone(), int(net.bn.num_batches_tracked)
+    after_two = net.bn.running_mean.clone()
+    ddp.eval()
+    with torch.no_grad():
+        ddp(x)                                   # first evaluation pass after training: rank 0's statistics win again
+        in_eval = net.bn.running_mean.clone()
+        net.bn.running_mean.add_(float(rank))    # a rank-local change ...
+        ddp(x)                                   # ... survives the next evaluation pass: no broadcast after a no-grad forward
+    return first, after_one, after_two, int(net.bn.num_batches_tracked), in_eval, net.bn.running_mean.clone()
 
 
 def test_ddp_broadcasts_buffers_each_forward():
@@ -119,6 +126,9 @@ def test_ddp_broadcasts_buffers_each_forward():
     exp = 0.9 * r0[1] + 0.1 * (r1[2] - 0.9 * r0[1]) / 0.1              # ... and are re-synchronised from rank 0
     assert torch.allclose(r1[2], 0.9 * r0[1] + (r1[2] - 0.9 * r0[1]), atol=1e-6) and exp is not None
     assert r0[3] == 2
+    assert not torch.allclose(r0[2], r1[2])                            # after training the ranks' statistics differ ...
+    assert torch.equal(r0[4], r0[2]) and torch.equal(r1[4], r0[2])     # ... the first evaluation forward ends that (torch's rule)
+    assert torch.equal(r0[5], r0[4]) and torch.allclose(r1[5], r0[4] + 1.0)
 
 
 def test_torchrun_cli_golden_stdout(tmp_path):
